@@ -1,0 +1,184 @@
+"""The reference's Python-scripted and 'essential' tests, restated as plain functions of a loaded library so the
+same checks run on the CPU oracle (-m "not gpu") and on the CUDA library (-m gpu).
+
+Sources: /root/reference/tests/essential/state_vector/*.test and
+/root/reference/tests/unit/state_vector/maths/{measure,measureWithStats,calcInnerProduct,calcFidelity}.test.
+Tolerance is the reference harness's 1e-10 absolute (utilities/QuESTTest/__main__.py:50) unless stated.
+"""
+import ctypes
+import os
+import tempfile
+
+import numpy as np
+
+from tests import harness
+
+TOL = 1e-10
+
+
+def check_seed_known_answer(lib):
+    """essential/seedQuEST.test: mt19937ar known-answer test through the shared library."""
+    harness.seed(lib, [(3 * i) % 64 for i in range(64)])
+    expect = [0.3388381249594591, 0.9577616744110737, 0.30208554964095485, 0.008018929047514434, 0.6887747446747438]
+    got = [lib.genrand_real1() for _ in range(5)]
+    assert got == expect  # bit-exact, not merely within tolerance
+
+
+def check_create(lib, env):
+    """essential/createQureg.test, createDensityQureg.test, destroyQureg.test: public descriptor fields."""
+    q = lib.createQureg(3, env)
+    assert (q.isDensityMatrix, q.numAmpsTotal, q.numQubitsInStateVec, q.numQubitsRepresented) == (0, 8, 3, 3)
+    assert q.numAmpsPerChunk * q.numChunks == q.numAmpsTotal
+    assert lib.getNumQubits(q) == 3 and lib.getNumAmps(q) == 8
+    lib.destroyQureg(q, env)
+    d = lib.createDensityQureg(3, env)
+    assert (d.isDensityMatrix, d.numAmpsTotal, d.numQubitsInStateVec, d.numQubitsRepresented) == (1, 64, 6, 3)
+    lib.destroyQureg(d, env)
+
+
+def check_init_states(lib, env):
+    """essential/initZeroState, initPlusState, initClassicalState, initStateDebug, setAmps."""
+    q = lib.createQureg(3, env)
+    np.testing.assert_array_equal(lib.get_state(q), np.eye(8)[0])
+    lib.initPlusState(q)
+    np.testing.assert_allclose(lib.get_state(q), np.full(8, 1 / np.sqrt(8)), atol=TOL)
+    lib.initClassicalState(q, 7)
+    np.testing.assert_array_equal(lib.get_state(q), np.eye(8)[7])
+    lib.destroyQureg(q, env)
+
+    q = lib.createQureg(5, env)
+    lib.initStateDebug(q)
+    k = np.arange(32)
+    np.testing.assert_allclose(lib.get_state(q), (2 * k) / 10 + 1j * (2 * k + 1) / 10, atol=1e-12)
+    lib.destroyQureg(q, env)
+
+    q = lib.createQureg(2, env)
+    amps = np.array([3.1415926535 + 2.7182818284j, 1.6180339887 + 1.6021766208j, 1.0, 1.0j])
+    lib.set_state(q, amps)
+    lib.set_state(q, np.array([2.0 + 0j]), start=2)
+    amps[2] = 2.0
+    np.testing.assert_array_equal(lib.get_state(q), amps)
+    lib.destroyQureg(q, env)
+
+    d = lib.createDensityQureg(2, env)
+    lib.initClassicalState(d, 2)
+    want = np.zeros(16)
+    want[2 * 5] = 1
+    np.testing.assert_array_equal(lib.get_state(d), want)
+    lib.initPlusState(d)
+    np.testing.assert_array_equal(lib.get_state(d), np.full(16, 0.25))
+    lib.destroyQureg(d, env)
+
+
+def check_measure(lib, env):
+    """unit/state_vector/maths/measure.test: outcomes pinned under seedQuEST([1])."""
+    q = lib.createQureg(3, env)
+    lib.initZeroState(q)
+    harness.seed(lib, [1])
+    assert [lib.measure(q, t) for t in range(3)] == [0, 0, 0]
+    lib.initPlusState(q)
+    assert [lib.measure(q, t) for t in range(3)] == [0, 1, 1]
+    lib.initStateDebug(q)
+    assert [lib.measure(q, t) for t in range(3)] == [0, 1, 1]
+    lib.destroyQureg(q, env)
+
+
+def check_measure_with_stats(lib, env):
+    """unit/state_vector/maths/measureWithStats.test: outcome probabilities pinned under seedQuEST([1])."""
+    q = lib.createQureg(3, env)
+    harness.seed(lib, [1])
+    p = lib.qreal(0)
+    for init, expect in ((lib.initZeroState, [1.0] * 3), (lib.initPlusState, [0.5] * 3),
+                         (lib.initStateDebug, [5.0, 0.708, 0.884180790960452])):
+        init(q)
+        got = []
+        for t in range(3):
+            lib.measureWithStats(q, t, ctypes.byref(p))
+            got.append(p.value)
+        np.testing.assert_allclose(got, expect, atol=TOL, rtol=0)
+    lib.destroyQureg(q, env)
+
+
+def check_inner_product_and_fidelity(lib, env):
+    """unit/state_vector/maths/calcInnerProduct.test and calcFidelity.test."""
+    a, b = lib.createQureg(3, env), lib.createQureg(3, env)
+    for init, ip, fid in ((None, 1 + 0j, 1.0), (lib.initPlusState, 0.3535533905933 + 0j, 0.125),
+                          (lib.initStateDebug, -0.1j, 0.01)):
+        if init:
+            init(a)
+        got = lib.calcInnerProduct(a, b)
+        np.testing.assert_allclose([got.real, got.imag], [ip.real, ip.imag], atol=TOL, rtol=0)
+        np.testing.assert_allclose(lib.calcFidelity(a, b), fid, atol=TOL, rtol=0)
+    lib.destroyQureg(a, env)
+    lib.destroyQureg(b, env)
+
+
+def check_qasm(lib, env):
+    """QASM log format (reference QuEST_qasm.c): header, mnemonics, phase-fix comments."""
+    q = lib.createQureg(3, env)
+    lib.startRecordingQASM(q)
+    lib.hadamard(q, 0)
+    lib.controlledNot(q, 0, 1)
+    lib.rotateY(q, 2, 0.5)
+    lib.controlledPhaseShift(q, 0, 2, 0.25)
+    lib.multiControlledPhaseFlip(q, lib.int_array([0, 1, 2]), 3)
+    lib.measure(q, 1)
+    lib.stopRecordingQASM(q)
+    lib.pauliX(q, 0)  # not recorded
+    text = lib.qasm_text(q)
+    lines = text.splitlines()
+    assert lines[:3] == ["OPENQASM 2.0;", "qreg q[3];", "creg c[3];"]
+    assert lines[3:6] == ["h q[0];", "cx q[0],q[1];", "Ry(0.5) q[2];"]
+    assert lines[6] == "cRz(0.25) q[0],q[2];"
+    assert lines[7] == "// Restoring the discarded global phase of the previous controlled phase gate"
+    assert lines[8] == "Rz(0.125) q[2];"
+    assert lines[9] == "ccz q[0],q[1],q[2];"
+    assert lines[10] == "measure q[1] -> c[1];"
+    assert len(lines) == 11
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, "out.qasm")
+        lib.writeRecordedQASMToFile(q, path.encode())
+        assert open(path).read() == text
+    lib.clearRecordedQASM(q)
+    assert lib.qasm_text(q) == ""
+    lib.destroyQureg(q, env)
+
+
+def check_density_is_conjugate_doubling(lib, env):
+    """U rho U^dagger through the 2n-qubit state-vector trick (reference QuEST.c:8-10): compare with numpy."""
+    n = 3
+    rng = np.random.default_rng(5)
+    psi = rng.standard_normal(8) + 1j * rng.standard_normal(8)
+    psi /= np.linalg.norm(psi)
+    rho = np.outer(psi, psi.conj())
+    d = lib.createDensityQureg(n, env)
+    lib.set_state(d, rho.flatten(order="F"))  # element (r,c) at r + c*2^n
+    th = 0.37
+    u = np.array([[np.cos(th / 2), -1j * np.sin(th / 2)], [-1j * np.sin(th / 2), np.cos(th / 2)]])  # Rx
+    full = np.kron(np.eye(2), np.kron(u, np.eye(2)))  # target qubit 1 (qubit 0 is the least significant)
+    lib.rotateX(d, 1, th)
+    got = lib.get_state(d).reshape(8, 8, order="F")
+    np.testing.assert_allclose(got, full @ rho @ full.conj().T, atol=1e-14)
+    np.testing.assert_allclose(lib.calcPurity(d), 1.0, atol=1e-13)
+    np.testing.assert_allclose(lib.calcTotalProb(d), 1.0, atol=1e-13)
+    lib.destroyQureg(d, env)
+
+
+def check_mix_aliases(lib, env):
+    """mixDephasing / mixDepolarising / mixDamping are the applyOneQubit*Error calls under their QuEST v3 names."""
+    if not lib.has("mixDephasing"):
+        return
+    outs = []
+    for names in (("applyOneQubitDephaseError", "applyOneQubitDepolariseError", "applyOneQubitDampingError"),
+                  ("mixDephasing", "mixDepolarising", "mixDamping")):
+        d = lib.createDensityQureg(3, env)
+        lib.initStateDebug(d)
+        for t, name in enumerate(names):
+            getattr(lib, name)(d, t, 0.1 + 0.05 * t)
+        outs.append(lib.get_state(d))
+        lib.destroyQureg(d, env)
+    np.testing.assert_array_equal(outs[0], outs[1])
+
+
+ALL_CHECKS = [check_create, check_init_states, check_measure, check_measure_with_stats,
+              check_inner_product_and_fidelity, check_qasm, check_density_is_conjugate_doubling, check_mix_aliases]
