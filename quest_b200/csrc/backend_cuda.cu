@@ -1,0 +1,856 @@
+// quest-b200 product backend: the statevec_* / densmatr_* seam (quest_internal.h) on B200 HBM.
+//
+// Replaces the reference's QuEST/src/GPU/QuEST_gpu.cu and QuEST/src/CPU/QuEST_cpu*.c for the gate path.
+// One process drives one GPU (its shard of the state).  There is NO CPU fallback: if no CUDA device can be
+// initialised the library prints the CUDA error and exits, following the reference's print-and-exit convention
+// (QuEST_validation.c:82-88, QuEST_cpu.c:1216-1217).
+//
+// Each entry point below decides, on the host, which bits of the amplitude index are special for the gate
+// (target, controls, density-matrix column partner), builds a qb::BitPlan, picks the kernel instantiation
+// (vector width VEC, and where the target falls relative to the vector) and enqueues ONE kernel on the engine's
+// stream.  Gate calls do not synchronise; value-returning calls do.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <type_traits>
+#include <vector>
+
+#include "qb_comm.h"
+#include "qb_kernels.cuh"
+#include "quest_b200.h"
+#include "quest_internal.h"
+
+using namespace qb;
+typedef long long int idx_t;
+typedef unsigned long long u64;
+
+// ---------------------------------------------------------------------------------------------------------
+// engine state
+// ---------------------------------------------------------------------------------------------------------
+
+namespace {
+
+#define CUDA_OK(call)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) {                                                                        \
+            std::printf("!!!\nquest-b200 CUDA failure: %s (%s) at %s:%d\n!!!\nexiting..\n",              \
+                        cudaGetErrorString(e_), #call, __FILE__, __LINE__);                             \
+            std::fflush(stdout);                                                                        \
+            std::exit(EXIT_FAILURE);                                                                    \
+        }                                                                                               \
+    } while (0)
+
+constexpr int kMaxReduceBlocks = 4096;  // per-block partial sums kept in scratch: 2 * kMaxReduceBlocks doubles
+
+struct Engine {
+    bool up = false;
+    int device = 0;
+    int numSMs = 148;
+    int rank = 0, world = 1;
+    cudaStream_t stream = nullptr;
+    bool ownsStream = false;
+    double* dPartials = nullptr;    // [2 * kMaxReduceBlocks]
+    unsigned int* dTicket = nullptr;
+    double* dResult = nullptr;      // [4]
+    double* hResult = nullptr;      // pinned [4]
+    int vecCap = 4;                 // QUEST_B200_VEC: upper bound on amplitudes per vector (1, 2 or 4)
+    unsigned long long launches = 0;
+} g;
+
+struct QuregRec {
+    qreal* re;
+    qreal* im;
+    idx_t n;       // amplitudes in this shard
+    int localBits; // log2 n
+};
+
+inline QuregRec* rec(const Qureg& q) { return reinterpret_cast<QuregRec*>(q.pairStateVec.real); }
+
+inline int log2i(u64 x) {
+    int l = 0;
+    while ((1ull << l) < x) ++l;
+    return l;
+}
+
+void requireEngine() {
+    if (!g.up) {
+        std::printf("!!!\nquest-b200: createQuESTEnv() must be called before any other QuEST function\n!!!\nexiting..\n");
+        std::exit(EXIT_FAILURE);
+    }
+}
+
+inline void launched() {
+    ++g.launches;
+    CUDA_OK(cudaGetLastError());
+}
+
+inline unsigned int blocksFor(u64 tasks) { return (unsigned int)((tasks + kBlock - 1) / kBlock); }
+
+// reductions: enough blocks to fill the chip several times over, never more than the scratch holds
+inline unsigned int reduceBlocks(u64 tasks) {
+    u64 want = (tasks + kBlock - 1) / kBlock;
+    u64 cap = std::min<u64>(kMaxReduceBlocks, (u64)g.numSMs * 16);
+    return (unsigned int)std::max<u64>(1, std::min(want, cap));
+}
+
+// widest vector (in amplitudes) allowed for a shard of n amplitudes; `limit` adds a per-call bound
+inline int pickVec(idx_t n, idx_t limit = 4) {
+    int v = g.vecCap;
+    while (v > 1 && (v > n || v > limit)) v >>= 1;
+    return v;
+}
+
+// ---- plan construction ----------------------------------------------------------------------------------
+// zeroBits: amplitude-index bits that the task enumeration must hold at 0 (the kernel ORs them in itself);
+// oneMask : amplitude-index bits that must be 1 (controls).  Bits below log2(VEC) never enter the plan: a low
+// zero-bit is the kernel's TLO, low one-bits become the lane predicate.
+struct Planned {
+    BitPlan plan;
+    u64 nTasks;
+};
+
+Planned makePlan(idx_t n, int vec, std::initializer_list<int> zeroBits, u64 oneMask) {
+    const int v = log2i(vec);
+    Planned out;
+    std::memset(&out.plan, 0, sizeof out.plan);
+    std::vector<int> pos;
+    for (int b : zeroBits)
+        if (b >= v) pos.push_back(b - v);
+    out.plan.loMask = (unsigned int)(oneMask & (u64)(vec - 1));
+    for (int b = v; b < 63; ++b) {
+        if (!((oneMask >> b) & 1)) continue;
+        if ((int)pos.size() < kMaxInsert) {
+            pos.push_back(b - v);
+            out.plan.setMask |= 1ull << (b - v);
+        } else {
+            out.plan.skipMask |= 1ull << (b - v);
+        }
+    }
+    std::sort(pos.begin(), pos.end());
+    out.plan.nIns = (int)pos.size();
+    for (int i = 0; i < out.plan.nIns; ++i) out.plan.pos[i] = pos[i];
+    out.nTasks = ((u64)n / vec) >> out.plan.nIns;
+    return out;
+}
+
+// compile-time dispatch on (VEC, TLO): TLO = target lane bit when the target is inside the vector, else -1
+template <class F>
+void dispatchVT(int vec, int target, F&& f) {
+    const int v = log2i(vec);
+    const int tlo = target < v ? target : -1;
+    if (vec == 4) {
+        if (tlo < 0) f(std::integral_constant<int, 4>(), std::integral_constant<int, -1>());
+        else if (tlo == 0) f(std::integral_constant<int, 4>(), std::integral_constant<int, 0>());
+        else f(std::integral_constant<int, 4>(), std::integral_constant<int, 1>());
+    } else if (vec == 2) {
+        if (tlo < 0) f(std::integral_constant<int, 2>(), std::integral_constant<int, -1>());
+        else f(std::integral_constant<int, 2>(), std::integral_constant<int, 0>());
+    } else {
+        f(std::integral_constant<int, 1>(), std::integral_constant<int, -1>());
+    }
+}
+
+template <class F>
+void dispatchV(int vec, F&& f) {
+    if (vec == 4) f(std::integral_constant<int, 4>());
+    else if (vec == 2) f(std::integral_constant<int, 2>());
+    else f(std::integral_constant<int, 1>());
+}
+
+// Controls on qubits that select the shard cost nothing: this rank either satisfies them (drop the bits) or
+// holds no selected amplitude (skip the launch).  Mirrors the global-index tests of QuEST_cpu.c:1841,2694.
+// Returns false when this shard has nothing to do.
+bool localiseControls(const Qureg& q, u64& mask) {
+    const QuregRec* r = rec(q);
+    const u64 globalBits = mask >> r->localBits;
+    if (globalBits) {
+        if (((u64)q.chunkId & globalBits) != globalBits) return false;
+        mask &= (1ull << r->localBits) - 1ull;
+    }
+    return true;
+}
+
+u64 maskOf(const int* qubits, int n) {
+    u64 m = 0;
+    for (int i = 0; i < n; ++i) m |= 1ull << qubits[i];
+    return m;
+}
+
+// ---- the two gate launchers ------------------------------------------------------------------------------
+
+// Target qubit selects the shard: fused exchange+combine over the partner's peer mapping (see k_pairsPeer).
+// The pairs are split between the two GPUs on the highest local bit that is not a control; the rank whose
+// global bit is 0 ("upper", QuEST_cpu_distributed.c:231-237) takes the 0 half.
+template <class Op>
+void launchPairsAcrossShards(const Qureg& q, int target, u64 ctrlMask, const Op& op) {
+    QuregRec* r = rec(q);
+    const int gbit = target - r->localBits;
+    const comm::Partner peer = comm::partnerOf(q, gbit);
+    const bool amUpper = ((q.chunkId >> gbit) & 1) == 0;
+    const int vec = pickVec(r->n);
+    const int v = log2i(vec);
+    int split = -1;
+    for (int b = r->localBits - 1; b >= v; --b)
+        if (!((ctrlMask >> b) & 1)) { split = b; break; }
+    comm::pairBarrier(peer.rank, g.stream);  // partner has finished everything enqueued before this gate
+    if (split >= 0 || amUpper) {
+        Planned p = split >= 0 ? makePlan(r->n, vec, {split}, ctrlMask) : makePlan(r->n, vec, {}, ctrlMask);
+        if (split >= 0 && !amUpper) p.plan.setMask |= 1ull << (split - v);
+        qreal* upRe = amUpper ? r->re : peer.re;
+        qreal* upIm = amUpper ? r->im : peer.im;
+        qreal* loRe = amUpper ? peer.re : r->re;
+        qreal* loIm = amUpper ? peer.im : r->im;
+        if (p.nTasks) {
+            dispatchV(vec, [&](auto V) {
+                k_pairsPeer<Op, decltype(V)::value>
+                    <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(upRe, upIm, loRe, loIm, p.nTasks, p.plan, op);
+            });
+            launched();
+        }
+    }
+    comm::pairBarrier(peer.rank, g.stream);  // partner's remote writes into this shard have landed
+}
+
+template <class Op>
+void launchPairs(const Qureg& q, int target, u64 ctrlMask, const Op& op) {
+    QuregRec* r = rec(q);
+    if (!localiseControls(q, ctrlMask)) return;
+    if (target >= r->localBits) {
+        launchPairsAcrossShards(q, target, ctrlMask, op);
+        return;
+    }
+    const int vec = pickVec(r->n);
+    const Planned p = makePlan(r->n, vec, {target}, ctrlMask);
+    if (p.nTasks == 0) return;
+    const int tvb = target - log2i(vec);
+    dispatchVT(vec, target, [&](auto V, auto T) {
+        k_pairs<Op, decltype(V)::value, decltype(T)::value>
+            <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(r->re, r->im, p.nTasks, p.plan, tvb, op);
+    });
+    launched();
+}
+
+template <class Op>
+void launchDiag(const Qureg& q, u64 mask, const Op& op) {
+    QuregRec* r = rec(q);
+    if (!localiseControls(q, mask)) return;
+    const int vec = pickVec(r->n);
+    const Planned p = makePlan(r->n, vec, {}, mask);
+    if (p.nTasks == 0) return;
+    dispatchV(vec, [&](auto V) {
+        k_diag<Op, decltype(V)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(r->re, r->im, p.nTasks, p.plan, op);
+    });
+    launched();
+}
+
+OpMatrix asOp(ComplexMatrix2 u) {
+    return OpMatrix{u.r0c0.real, u.r0c0.imag, u.r0c1.real, u.r0c1.imag, u.r1c0.real, u.r1c0.imag, u.r1c1.real, u.r1c1.imag};
+}
+OpCompact asOp(Complex a, Complex b) { return OpCompact{a.real, a.imag, b.real, b.imag}; }
+
+// ---- reductions --------------------------------------------------------------------------------------------
+
+// device result[0..nv) -> (sum over shards) -> host.  The only synchronisation point of a reduction.
+void fetchResult(int nv, double* out) {
+    if (g.world > 1) comm::allReduceSum(g.dResult, nv, g.stream);
+    CUDA_OK(cudaMemcpyAsync(g.hResult, g.dResult, nv * sizeof(double), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+    for (int i = 0; i < nv; ++i) out[i] = g.hResult[i];
+}
+
+void zeroResult(int nv) { CUDA_OK(cudaMemsetAsync(g.dResult, 0, nv * sizeof(double), g.stream)); }
+
+void fillShard(const Qureg& q, qreal vr, qreal vi) {
+    QuregRec* r = rec(q);
+    const int vec = pickVec(r->n);
+    const u64 nVec = (u64)r->n / vec;
+    dispatchV(vec, [&](auto V) {
+        k_fill<decltype(V)::value><<<blocksFor(nVec), kBlock, 0, g.stream>>>(r->re, r->im, nVec, vr, vi);
+    });
+    launched();
+}
+
+// set the amplitude with GLOBAL index gi, if this shard owns it
+void setOneGlobal(const Qureg& q, idx_t gi, qreal vr, qreal vi) {
+    QuregRec* r = rec(q);
+    const idx_t off = (idx_t)q.chunkId * r->n;
+    if (gi < off || gi >= off + r->n) return;
+    k_setOne<<<1, 1, 0, g.stream>>>(r->re, r->im, (u64)(gi - off), vr, vi);
+    launched();
+}
+
+// ---- helpers shared by several entry points ------------------------------------------------------------
+
+qreal readOne(const Qureg& q, idx_t index, bool imag) {
+    QuregRec* r = rec(q);
+    const int owner = (int)(index / r->n);
+    qreal v = 0;
+    if (owner == q.chunkId) {
+        const qreal* src = (imag ? r->im : r->re) + (index - (idx_t)owner * r->n);
+        CUDA_OK(cudaMemcpyAsync(&v, src, sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
+        CUDA_OK(cudaStreamSynchronize(g.stream));
+    }
+    if (g.world > 1) comm::broadcastBytes(&v, sizeof v, owner);  // replaces MPI_Bcast, QuEST_cpu_distributed.c:208
+    return v;
+}
+
+double sumSquares(const Qureg& q) {
+    QuregRec* r = rec(q);
+    const int vec = pickVec(r->n);
+    const u64 nVec = (u64)r->n / vec;
+    dispatchV(vec, [&](auto V) {
+        k_sumSquares<decltype(V)::value><<<reduceBlocks(nVec), kBlock, 0, g.stream>>>(r->re, r->im, nVec, g.dPartials,
+                                                                                     g.dTicket, g.dResult);
+    });
+    launched();
+    double s;
+    fetchResult(1, &s);
+    return s;
+}
+
+double probOfZero(const Qureg& q, int t) {
+    QuregRec* r = rec(q);
+    if (t >= r->localBits) {
+        // the measured qubit selects the shard: shards with the bit set contribute 0, the others everything
+        // (QuEST_cpu_distributed.c:1227-1247)
+        if ((q.chunkId >> (t - r->localBits)) & 1) {
+            zeroResult(1);
+            double s;
+            fetchResult(1, &s);
+            return s;
+        }
+        return sumSquares(q);
+    }
+    const int vec = pickVec(r->n);
+    const Planned p = makePlan(r->n, vec, {t}, 0);
+    dispatchVT(vec, t, [&](auto V, auto T) {
+        k_probZero<decltype(V)::value, decltype(T)::value><<<reduceBlocks(p.nTasks), kBlock, 0, g.stream>>>(
+            r->re, r->im, p.nTasks, p.plan, g.dPartials, g.dTicket, g.dResult);
+    });
+    launched();
+    double s;
+    fetchResult(1, &s);
+    return s;
+}
+
+double densDiagSum(const Qureg& q, int bit) {
+    QuregRec* r = rec(q);
+    const u64 dim = 1ull << q.numQubitsRepresented;
+    k_densDiagSum<<<reduceBlocks(dim), kBlock, 0, g.stream>>>(r->re, dim, bit, (u64)q.chunkId * r->n, (u64)r->n,
+                                                             g.dPartials, g.dTicket, g.dResult);
+    launched();
+    double s;
+    fetchResult(1, &s);
+    return s;
+}
+
+template <int KIND>
+void launchNoise1(const Qureg& q, int t, qreal p0, qreal p1, qreal p2) {
+    if (g.world > 1) comm::unsupported("one-qubit noise on a sharded density matrix");
+    QuregRec* r = rec(q);
+    const int n = q.numQubitsRepresented;
+    const int vec = pickVec(r->n, 1LL << n);
+    const int v = log2i(vec);
+    const Planned p = makePlan(r->n, vec, {t, t + n}, 0);
+    dispatchVT(vec, t, [&](auto V, auto T) {
+        k_noise1<KIND, decltype(V)::value, decltype(T)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(
+            r->re, r->im, p.nTasks, p.plan, t - v, t + n - v, p0, p1, p2);
+    });
+    launched();
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------
+// environment                               (replaces QuEST_gpu.cu:234-290 / QuEST_cpu_distributed.c:135-197)
+// ---------------------------------------------------------------------------------------------------------
+
+extern "C" {
+
+QuESTEnv createQuESTEnv(void) {
+    QuESTEnv env;
+    env.rank = 0;
+    env.numRanks = 1;
+    if (g.up) {
+        std::printf("ERROR: Trying to initialize QuESTEnv multiple times. Ignoring...\n");
+        env.rank = g.rank;
+        env.numRanks = g.world;
+        return env;
+    }
+    // one process per GPU: rank / world size / local device come from the launcher's environment
+    // (torchrun: RANK, WORLD_SIZE, LOCAL_RANK; overridable with QUEST_B200_RANK / _WORLD / _DEVICE)
+    comm::Launch ln = comm::readLaunchEnv();
+    int nDev = 0;
+    cudaError_t e = cudaGetDeviceCount(&nDev);
+    if (e != cudaSuccess || nDev == 0) {
+        std::printf("!!!\nquest-b200: no CUDA device available (%s). This library has no CPU fallback.\n!!!\nexiting..\n",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+        std::fflush(stdout);
+        std::exit(EXIT_FAILURE);
+    }
+    g.device = ln.device % nDev;
+    CUDA_OK(cudaSetDevice(g.device));
+    cudaDeviceProp prop;
+    CUDA_OK(cudaGetDeviceProperties(&prop, g.device));
+    g.numSMs = prop.multiProcessorCount;
+    CUDA_OK(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    g.ownsStream = true;
+    CUDA_OK(cudaMalloc(&g.dPartials, 2 * kMaxReduceBlocks * sizeof(double)));
+    CUDA_OK(cudaMalloc(&g.dTicket, sizeof(unsigned int)));
+    CUDA_OK(cudaMemset(g.dTicket, 0, sizeof(unsigned int)));
+    CUDA_OK(cudaMalloc(&g.dResult, 4 * sizeof(double)));
+    CUDA_OK(cudaHostAlloc(&g.hResult, 4 * sizeof(double), cudaHostAllocDefault));
+    if (const char* s = std::getenv("QUEST_B200_VEC")) {
+        int v = std::atoi(s);
+        if (v == 1 || v == 2 || v == 4) g.vecCap = v;
+    }
+    g.rank = ln.rank;
+    g.world = ln.world;
+    g.up = true;
+    if (g.world > 1) comm::init(ln, g.device, g.stream);
+    env.rank = g.rank;
+    env.numRanks = g.world;
+    seedQuESTDefault();
+    return env;
+}
+
+void destroyQuESTEnv(QuESTEnv env) {
+    (void)env;
+    if (!g.up) {
+        std::printf("ERROR: Trying to close QuESTEnv multiple times. Ignoring\n");
+        return;
+    }
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+    if (g.world > 1) comm::shutdown();
+    cudaFree(g.dPartials);
+    cudaFree(g.dTicket);
+    cudaFree(g.dResult);
+    cudaFreeHost(g.hResult);
+    if (g.ownsStream) cudaStreamDestroy(g.stream);
+    g = Engine();
+}
+
+void syncQuESTEnv(QuESTEnv env) {
+    (void)env;
+    requireEngine();
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+    if (g.world > 1) comm::hostBarrier();
+}
+
+int syncQuESTSuccess(int successCode) {
+    if (g.world > 1) return comm::allAnd(successCode);
+    return successCode;
+}
+
+void reportQuESTEnv(QuESTEnv env) {
+    if (env.rank != 0) return;
+    cudaDeviceProp prop;
+    CUDA_OK(cudaGetDeviceProperties(&prop, g.device));
+    std::printf("EXECUTION ENVIRONMENT:\n");
+    std::printf("Running on %d GPU%s (quest-b200, one process per GPU), device %d: %s, %d SMs\n", env.numRanks,
+                env.numRanks > 1 ? "s" : "", g.device, prop.name, prop.multiProcessorCount);
+    std::printf("Number of ranks is %d\n", env.numRanks);
+    std::printf("OpenMP disabled\n");
+    std::printf("Precision: size of qreal is %ld bytes\n", sizeof(qreal));
+}
+
+void getEnvironmentString(QuESTEnv env, Qureg qureg, char str[200]) {
+    std::snprintf(str, 200, "%dqubits_GPU_%dranks_b200", qureg.numQubitsInStateVec, env.numRanks);
+}
+
+// every rank must draw the same random numbers: rank 0's key is shared (QuEST_cpu_distributed.c:1294-1305)
+void seedQuESTDefault(void) {
+    unsigned long int key[2];
+    getQuESTDefaultSeedKey(key);
+    if (g.up && g.world > 1) comm::broadcastBytes(key, sizeof key, 0);
+    init_by_array(key, 2);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// registers                                                              (replaces QuEST_gpu.cu:156-232)
+// ---------------------------------------------------------------------------------------------------------
+
+void statevec_createQureg(Qureg* qureg, int numQubits, QuESTEnv env) {
+    requireEngine();
+    std::memset(qureg, 0, sizeof *qureg);
+    const idx_t total = 1LL << numQubits;
+    const idx_t per = total / env.numRanks;
+    if (per < 1) {
+        std::printf("!!!\nquest-b200: %d qubits cannot be sharded over %d GPUs\n!!!\nexiting..\n", numQubits, env.numRanks);
+        std::exit(EXIT_FAILURE);
+    }
+    QuregRec* r = new QuregRec();
+    r->n = per;
+    r->localBits = log2i((u64)per);
+    // no host mirror and no pair buffer: the shard (2 * per * sizeof(qreal) bytes) is the only allocation
+    cudaError_t e1 = cudaMalloc(&r->re, per * sizeof(qreal));
+    cudaError_t e2 = e1 == cudaSuccess ? cudaMalloc(&r->im, per * sizeof(qreal)) : e1;
+    if (e1 != cudaSuccess || e2 != cudaSuccess) {
+        std::printf("Could not allocate memory!");  // reference text, QuEST_cpu.c:1216
+        std::printf(" (%lld amplitudes of %zu bytes on device %d: %s)\n", per, 2 * sizeof(qreal), g.device,
+                    cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+        std::fflush(stdout);
+        std::exit(EXIT_FAILURE);
+    }
+    qureg->numQubitsInStateVec = numQubits;
+    qureg->numAmpsTotal = total;
+    qureg->numAmpsPerChunk = per;
+    qureg->chunkId = env.rank;
+    qureg->numChunks = env.numRanks;
+    qureg->isDensityMatrix = 0;
+    qureg->deviceStateVec.real = r->re;
+    qureg->deviceStateVec.imag = r->im;
+    qureg->pairStateVec.real = reinterpret_cast<qreal*>(r);
+    qureg->firstLevelReduction = reinterpret_cast<qreal*>(g.dPartials);
+    if (g.world > 1) comm::registerShard(*qureg, r->re, r->im, per);
+}
+
+void statevec_destroyQureg(Qureg qureg, QuESTEnv env) {
+    (void)env;
+    QuregRec* r = rec(qureg);
+    if (!r) return;
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+    if (g.world > 1) comm::unregisterShard(qureg);
+    CUDA_OK(cudaFree(r->re));
+    CUDA_OK(cudaFree(r->im));
+    delete r;
+}
+
+// host -> device slice copy; complete on return, as in the reference (QuEST_gpu.cu:34-49)
+void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, idx_t numAmps) {
+    QuregRec* r = rec(qureg);
+    const idx_t off = (idx_t)qureg.chunkId * r->n;
+    idx_t lo = std::max<idx_t>(startInd - off, 0), hi = std::min<idx_t>(startInd - off + numAmps, r->n);
+    if (hi > lo) {
+        const idx_t src = lo + off - startInd;
+        CUDA_OK(cudaMemcpyAsync(r->re + lo, reals + src, (hi - lo) * sizeof(qreal), cudaMemcpyHostToDevice, g.stream));
+        CUDA_OK(cudaMemcpyAsync(r->im + lo, imags + src, (hi - lo) * sizeof(qreal), cudaMemcpyHostToDevice, g.stream));
+    }
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+}
+
+void qb200_copyAmpsToHost(Qureg qureg, idx_t start, idx_t n, qreal* reals, qreal* imags) {
+    QuregRec* r = rec(qureg);
+    CUDA_OK(cudaMemcpyAsync(reals, r->re + start, n * sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_OK(cudaMemcpyAsync(imags, r->im + start, n * sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+}
+
+void statevec_cloneQureg(Qureg dst, Qureg src) {
+    QuregRec *d = rec(dst), *s = rec(src);
+    CUDA_OK(cudaMemcpyAsync(d->re, s->re, d->n * sizeof(qreal), cudaMemcpyDeviceToDevice, g.stream));
+    CUDA_OK(cudaMemcpyAsync(d->im, s->im, d->n * sizeof(qreal), cudaMemcpyDeviceToDevice, g.stream));
+}
+
+
+qreal statevec_getRealAmp(Qureg qureg, idx_t index) { return readOne(qureg, index, false); }
+qreal statevec_getImagAmp(Qureg qureg, idx_t index) { return readOne(qureg, index, true); }
+
+int statevec_compareStates(Qureg a, Qureg b, qreal precision) {
+    QuregRec *ra = rec(a), *rb = rec(b);
+    const int vec = pickVec(ra->n);
+    const u64 nVec = (u64)ra->n / vec;
+    dispatchV(vec, [&](auto V) {
+        k_countDiffs<decltype(V)::value><<<reduceBlocks(nVec), kBlock, 0, g.stream>>>(
+            ra->re, ra->im, rb->re, rb->im, nVec, precision, g.dPartials, g.dTicket, g.dResult);
+    });
+    launched();
+    double cnt;
+    fetchResult(1, &cnt);
+    return cnt == 0.0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// initial states                                                          (replaces QuEST_gpu.cu:346-466)
+// ---------------------------------------------------------------------------------------------------------
+
+void statevec_initZeroState(Qureg q) {
+    QuregRec* r = rec(q);
+    CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
+    CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
+    setOneGlobal(q, 0, 1, 0);
+}
+
+void statevec_initPlusState(Qureg q) {
+    const idx_t total = q.numAmpsPerChunk * q.numChunks;
+    fillShard(q, 1.0 / sqrt((qreal)total), 0);
+}
+
+void statevec_initClassicalState(Qureg q, idx_t stateInd) {
+    QuregRec* r = rec(q);
+    CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
+    CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
+    setOneGlobal(q, stateInd, 1, 0);
+}
+
+void statevec_initStateDebug(Qureg q) {
+    QuregRec* r = rec(q);
+    k_initDebug<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n);
+    launched();
+}
+
+void statevec_initStateOfSingleQubit(Qureg* q, int qubitId, int outcome) {
+    QuregRec* r = rec(*q);
+    const idx_t total = q->numAmpsPerChunk * q->numChunks;
+    const qreal norm = 1.0 / sqrt((qreal)total / 2.0);
+    k_initSingleQubit<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q->chunkId * r->n,
+                                                                    qubitId, outcome, norm);
+    launched();
+}
+
+void densmatr_initPlusState(Qureg q) {
+    const idx_t dim = 1LL << q.numQubitsRepresented;
+    fillShard(q, 1.0 / ((qreal)dim), 0);
+}
+
+void densmatr_initClassicalState(Qureg q, idx_t stateInd) {
+    QuregRec* r = rec(q);
+    const idx_t dim = 1LL << q.numQubitsRepresented;
+    CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
+    CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
+    setOneGlobal(q, (dim + 1) * stateInd, 1, 0);
+}
+
+void densmatr_initPureState(Qureg rho, Qureg psi) {
+    if (g.world > 1) comm::unsupported("initPureState on a sharded density matrix");
+    QuregRec *d = rec(rho), *p = rec(psi);
+    k_outerProduct<<<blocksFor((u64)d->n), kBlock, 0, g.stream>>>(d->re, d->im, p->re, p->im, (u64)psi.numAmpsTotal,
+                                                                 (u64)d->n);
+    launched();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// gates                                                                  (replaces QuEST_gpu.cu:531-1330)
+// ---------------------------------------------------------------------------------------------------------
+
+void statevec_compactUnitary(Qureg q, const int t, Complex alpha, Complex beta) { launchPairs(q, t, 0, asOp(alpha, beta)); }
+void statevec_controlledCompactUnitary(Qureg q, const int c, const int t, Complex alpha, Complex beta) {
+    launchPairs(q, t, 1ull << c, asOp(alpha, beta));
+}
+void statevec_unitary(Qureg q, const int t, ComplexMatrix2 u) { launchPairs(q, t, 0, asOp(u)); }
+void statevec_controlledUnitary(Qureg q, const int c, const int t, ComplexMatrix2 u) { launchPairs(q, t, 1ull << c, asOp(u)); }
+void statevec_multiControlledUnitary(Qureg q, int* ctrls, const int n, const int t, ComplexMatrix2 u) {
+    launchPairs(q, t, maskOf(ctrls, n), asOp(u));
+}
+void statevec_hadamard(Qureg q, const int t) { launchPairs(q, t, 0, OpHadamard{(qreal)(1.0 / sqrt(2))}); }
+void statevec_pauliX(Qureg q, const int t) { launchPairs(q, t, 0, OpSwap{}); }
+void statevec_controlledNot(Qureg q, const int c, const int t) { launchPairs(q, t, 1ull << c, OpSwap{}); }
+void statevec_pauliY(Qureg q, const int t) { launchPairs(q, t, 0, OpPauliY{1}); }
+void statevec_pauliYConj(Qureg q, const int t) { launchPairs(q, t, 0, OpPauliY{-1}); }
+void statevec_controlledPauliY(Qureg q, const int c, const int t) { launchPairs(q, t, 1ull << c, OpPauliY{1}); }
+void statevec_controlledPauliYConj(Qureg q, const int c, const int t) { launchPairs(q, t, 1ull << c, OpPauliY{-1}); }
+
+void statevec_phaseShiftByTerm(Qureg q, const int t, Complex term) { launchDiag(q, 1ull << t, DiagPhase{term.real, term.imag}); }
+void statevec_controlledPhaseShift(Qureg q, const int q1, const int q2, qreal angle) {
+    launchDiag(q, (1ull << q1) | (1ull << q2), DiagPhase{(qreal)cos(angle), (qreal)sin(angle)});
+}
+void statevec_multiControlledPhaseShift(Qureg q, int* ctrls, int n, qreal angle) {
+    launchDiag(q, maskOf(ctrls, n), DiagPhase{(qreal)cos(angle), (qreal)sin(angle)});
+}
+void statevec_controlledPhaseFlip(Qureg q, const int q1, const int q2) { launchDiag(q, (1ull << q1) | (1ull << q2), DiagFlip{}); }
+void statevec_multiControlledPhaseFlip(Qureg q, int* ctrls, int n) { launchDiag(q, maskOf(ctrls, n), DiagFlip{}); }
+
+// ---------------------------------------------------------------------------------------------------------
+// reductions                                                             (replaces QuEST_gpu.cu:1111-1164,1335-1840)
+// ---------------------------------------------------------------------------------------------------------
+
+
+// The reference sums on the host (serial Kahan, QuEST_cpu_local.c:123-151; its GPU build copies the whole state
+// back, QuEST_gpu.cu:1134-1164).  Here it is one read-only pass in HBM with double accumulators.
+qreal statevec_calcTotalProb(Qureg q) { return (qreal)sumSquares(q); }
+qreal densmatr_calcPurity(Qureg q) { return (qreal)sumSquares(q); }
+
+
+qreal statevec_calcProbOfOutcome(Qureg q, const int t, int outcome) {
+    qreal p = (qreal)probOfZero(q, t);
+    if (outcome == 1) p = 1.0 - p;  // defined this way also for unnormalised states (QuEST_cpu_local.c:271)
+    return p;
+}
+
+Complex statevec_calcInnerProduct(Qureg bra, Qureg ket) {
+    QuregRec *b = rec(bra), *k = rec(ket);
+    const int vec = pickVec(b->n);
+    const u64 nVec = (u64)b->n / vec;
+    dispatchV(vec, [&](auto V) {
+        k_innerProduct<decltype(V)::value><<<reduceBlocks(nVec), kBlock, 0, g.stream>>>(
+            b->re, b->im, k->re, k->im, nVec, g.dPartials, g.dTicket, g.dResult);
+    });
+    launched();
+    double s[2];
+    fetchResult(2, s);
+    Complex out;
+    out.real = (qreal)s[0];
+    out.imag = (qreal)s[1];
+    return out;
+}
+
+
+qreal densmatr_calcTotalProb(Qureg q) { return (qreal)densDiagSum(q, -1); }
+
+qreal densmatr_calcProbOfOutcome(Qureg q, const int t, int outcome) {
+    qreal p = (qreal)densDiagSum(q, t);
+    if (outcome == 1) p = 1.0 - p;
+    return p;
+}
+
+qreal densmatr_calcFidelity(Qureg rho, Qureg psi) {
+    if (g.world > 1) comm::unsupported("calcFidelity on a sharded density matrix");
+    QuregRec *d = rec(rho), *p = rec(psi);
+    const u64 dim = (u64)psi.numAmpsTotal;
+    k_densFidelity<<<reduceBlocks(dim), kBlock, 0, g.stream>>>(d->re, d->im, p->re, p->im, dim, g.dPartials, g.dTicket,
+                                                              g.dResult);
+    launched();
+    double s;
+    fetchResult(1, &s);
+    return (qreal)s;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// collapse                                                               (replaces QuEST_gpu.cu:1847-1966)
+// ---------------------------------------------------------------------------------------------------------
+
+void statevec_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qreal prob) {
+    QuregRec* r = rec(q);
+    const qreal renorm = 1 / sqrt(prob);
+    const int vec = pickVec(r->n);
+    if (t >= r->localBits) {
+        // whole shard is either kept (renormalised) or cleared (QuEST_cpu_distributed.c:1274-1292)
+        const int bit = (q.chunkId >> (t - r->localBits)) & 1;
+        if (bit == outcome) {
+            const u64 nVec = (u64)r->n / vec;
+            dispatchV(vec, [&](auto V) {
+                k_scaleAll<decltype(V)::value><<<blocksFor(nVec), kBlock, 0, g.stream>>>(r->re, r->im, nVec, renorm);
+            });
+            launched();
+        } else {
+            CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
+            CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
+        }
+        return;
+    }
+    const Planned p = makePlan(r->n, vec, {t}, 0);
+    const int tvb = t - log2i(vec);
+    dispatchVT(vec, t, [&](auto V, auto T) {
+        k_collapse<decltype(V)::value, decltype(T)::value>
+            <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(r->re, r->im, p.nTasks, p.plan, tvb, outcome, renorm);
+    });
+    launched();
+}
+
+void densmatr_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qreal prob) {
+    if (g.world > 1) comm::unsupported("collapse of a sharded density matrix");
+    QuregRec* r = rec(q);
+    const int n = q.numQubitsRepresented;
+    const int vec = pickVec(r->n, 1LL << n);
+    const int v = log2i(vec);
+    const Planned p = makePlan(r->n, vec, {t, t + n}, 0);
+    dispatchVT(vec, t, [&](auto V, auto T) {
+        k_densCollapse<decltype(V)::value, decltype(T)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(
+            r->re, r->im, p.nTasks, p.plan, t - v, t + n - v, outcome, prob);
+    });
+    launched();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// density-matrix noise                                                   (replaces QuEST_gpu.cu:1997-2275)
+// ---------------------------------------------------------------------------------------------------------
+
+
+void densmatr_oneQubitDephase(Qureg q, const int t, qreal dephase) {
+    const qreal retain = 1 - dephase;
+    launchNoise1<kDephase>(q, t, retain, 0, 0);
+}
+
+void densmatr_oneQubitDepolarise(Qureg q, const int t, qreal level) {
+    if (level == 0) return;
+    const qreal retain = 1 - level;
+    launchNoise1<kDepolarise>(q, t, retain, level, retain);
+}
+
+void densmatr_oneQubitDamping(Qureg q, const int t, qreal damping) {
+    if (damping == 0) return;
+    const qreal retain = 1 - damping;
+    const qreal dephase = sqrt(retain);
+    launchNoise1<kDamping>(q, t, dephase, damping, retain);
+}
+
+void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase) {
+    QuregRec* r = rec(q);
+    const int n = q.numQubitsRepresented;
+    const qreal retain = 1 - dephase;
+    k_dephase2<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n, 1ull << q1,
+                                                             1ull << (q1 + n), 1ull << q2, 1ull << (q2 + n), retain);
+    launched();
+}
+
+void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
+    if (level == 0) return;
+    if (g.world > 1) comm::unsupported("two-qubit depolarising on a sharded density matrix");
+    QuregRec* r = rec(q);
+    const int n = q.numQubitsRepresented;
+    // host scalars exactly as QuEST_cpu_local.c:43-48
+    qreal eta = 2 / level;
+    qreal delta = eta - 1 - sqrt((eta - 1) * (eta - 1) - 1);
+    qreal gamma = 1 + delta;
+    gamma = 1 / (gamma * gamma * gamma);
+    densmatr_twoQubitDephase(q, q1, q2, level);
+    const u64 tot1 = (1ull << q1) | (1ull << (q1 + n)), tot2 = (1ull << q2) | (1ull << (q2 + n));
+    const unsigned int nb = blocksFor((u64)r->n);
+    k_depol2Sweep<<<nb, kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, tot1, tot2, 0, delta, 1);
+    launched();
+    k_depol2Sweep<<<nb, kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, tot2, tot1, 0, delta, 1);
+    launched();
+    k_depol2Sweep<<<nb, kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, tot2, tot1, tot1, delta, gamma);
+    launched();
+}
+
+void densmatr_addDensityMatrix(Qureg a, qreal p, Qureg b) {
+    QuregRec *ra = rec(a), *rb = rec(b);
+    const int vec = pickVec(ra->n);
+    const u64 nVec = (u64)ra->n / vec;
+    dispatchV(vec, [&](auto V) {
+        k_mixDensity<decltype(V)::value><<<blocksFor(nVec), kBlock, 0, g.stream>>>(ra->re, ra->im, rb->re, rb->im, nVec, p);
+    });
+    launched();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// quest_b200.h extension entry points
+// ---------------------------------------------------------------------------------------------------------
+
+void* qb200_getStream(void) { return (void*)g.stream; }
+
+void qb200_setStream(void* stream) {
+    requireEngine();
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+    if (g.ownsStream) cudaStreamDestroy(g.stream);
+    g.stream = (cudaStream_t)stream;
+    g.ownsStream = false;
+}
+
+unsigned long long qb200_getLaunchCount(void) { return g.launches; }
+
+int qb200_getDevice(void) { return g.device; }
+
+void qb200_getDevicePointers(Qureg qureg, void** real, void** imag) {
+    QuregRec* r = rec(qureg);
+    *real = r->re;
+    *imag = r->im;
+}
+
+}  // extern "C"
+
+// shared with qb_comm.cu
+namespace qb {
+namespace hostapi {
+cudaStream_t stream() { return g.stream; }
+int numSMs() { return g.numSMs; }
+int vecFor(long long n) { return pickVec(n); }
+void countLaunch() { launched(); }
+}  // namespace hostapi
+}  // namespace qb

@@ -1,0 +1,184 @@
+"""GPU parity: the CUDA library (through its C ABI) against the reference's golden vectors, the CPU oracle and
+the reference's own CPU build, on the same seeded inputs.
+
+Bars (BASELINE.json north_star): amplitudes within 1e-12 relative in double, measurement outcomes bit-exact
+under the same seed.  Gate kernels are compiled without FMA contraction and written with the reference's
+operand order, so measurement-free circuits are additionally required to match BIT FOR BIT.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from quest_b200 import circuits
+from tests import harness, scripted
+
+pytestmark = pytest.mark.gpu
+
+CASES = harness.load_golden_cases()
+REF_OUT = np.load(os.path.join(harness.GOLDEN_DIR, "ref_unit_outputs.npz"))
+REF_CIRC = np.load(os.path.join(harness.GOLDEN_DIR, "ref_circuits.npz"))
+REL = 1e-12
+
+
+def test_native_library_is_the_one_loaded(product, product_env):
+    assert product.path.endswith("quest_b200/lib/libQuEST.so")
+    before = product.lib.qb200_getLaunchCount()
+    q = product.createQureg(10, product_env)
+    product.hadamard(q, 3)
+    product.destroyQureg(q, product_env)
+    product.lib.qb200_getLaunchCount.restype = __import__("ctypes").c_ulonglong
+    assert product.lib.qb200_getLaunchCount() > before
+
+
+def test_reference_golden_vectors(product, product_env):
+    """All 768 standard-format cases of the reference suite (3 qubits, every gate x target x start state)."""
+    for case in CASES:
+        harness.check_golden_case(case, harness.run_golden_case(product, product_env, case))
+
+
+def test_reference_golden_outputs_bit_exact(product, product_env):
+    n = 0
+    for i, case in enumerate(CASES):
+        if f"s{i}" not in REF_OUT.files:
+            continue
+        got = harness.run_golden_case(product, product_env, case)["S"]
+        ref = REF_OUT[f"s{i}"]
+        if case["func"] == "collapseToOutcome":
+            np.testing.assert_allclose(got, ref, atol=1e-14, rtol=1e-14)
+        else:
+            assert np.array_equal(got.view(np.float64), ref.view(np.float64)), case["file"]
+            n += 1
+    assert n >= 500
+
+
+def test_seed_known_answer(product):
+    scripted.check_seed_known_answer(product)
+
+
+@pytest.mark.parametrize("check", scripted.ALL_CHECKS, ids=lambda f: f.__name__)
+def test_reference_scripted(product, product_env, check):
+    check(product, product_env)
+
+
+@pytest.mark.parametrize("name,nq,dens,depth,seed", [("sv12", 12, False, 120, 11), ("sv16", 16, False, 160, 12),
+                                                     ("dm6", 6, True, 90, 13), ("dm8", 8, True, 120, 14)])
+def test_reference_circuit_fixtures(product, product_env, name, nq, dens, depth, seed):
+    """Committed outputs of the reference library for seeded circuits over every gate family."""
+    ops = circuits.random_circuit(nq, depth, seed, density=dens)
+    q = product.createDensityQureg(nq, product_env) if dens else product.createQureg(nq, product_env)
+    circuits.prepare(product, q, seed)
+    scal = circuits.run_circuit(product, q, ops, seed=seed)
+    st = product.get_state(q)
+    product.destroyQureg(q, product_env)
+    np.testing.assert_allclose(scal, REF_CIRC[name + "_scalars"], rtol=REL, atol=1e-13)
+    sub = st if st.size <= 1 << 16 else st[:: st.size >> 16]
+    np.testing.assert_allclose(sub, REF_CIRC[name + "_state"], rtol=0, atol=REL * np.abs(REF_CIRC[name + "_state"]).max())
+    np.testing.assert_allclose(circuits.state_digest(st), REF_CIRC[name + "_digest"], rtol=1e-11, atol=1e-12)
+
+
+def _side_by_side(gpu, genv, cpu, cenv, nq, dens, ops, seed):
+    out = []
+    for lib, env in ((gpu, genv), (cpu, cenv)):
+        q = lib.createDensityQureg(nq, env) if dens else lib.createQureg(nq, env)
+        circuits.prepare(lib, q, seed)
+        scal = circuits.run_circuit(lib, q, ops, seed=seed)
+        out.append((lib.get_state(q), np.array(scal)))
+        lib.destroyQureg(q, env)
+    return out
+
+
+@pytest.mark.parametrize("nq,dens,seed", [(1, False, 1), (2, False, 2), (3, False, 3), (5, False, 4), (9, False, 5),
+                                          (13, False, 6), (18, False, 7), (22, False, 8), (1, True, 9), (2, True, 10),
+                                          (4, True, 11), (7, True, 12), (10, True, 13), (11, True, 14)])
+def test_bit_exact_vs_oracle_measurement_free(product, product_env, oracle, oracle_env, nq, dens, seed):
+    """Every gate family, every target position (inside the vector, mid, top), 1 to 22 qubits: identical bits."""
+    ops = circuits.random_circuit(nq, 220, seed, density=dens, measure=False)
+    (gs, gv), (cs, cv) = _side_by_side(product, product_env, oracle, oracle_env, nq, dens, ops, seed)
+    assert np.array_equal(gs.view(np.float64), cs.view(np.float64))
+    np.testing.assert_allclose(gv, cv, rtol=REL, atol=1e-13)
+
+
+@pytest.mark.parametrize("nq,dens,seed", [(14, False, 21), (20, False, 22), (24, False, 23), (6, True, 24), (12, True, 25)])
+def test_vs_live_reference_with_measurement(product, product_env, reference, reference_env, nq, dens, seed):
+    """The reference's own CPU/OpenMP library side by side, measurements included: same outcomes, amplitudes to
+    1e-12 relative."""
+    ops = circuits.random_circuit(nq, 150, seed, density=dens, measure=True)
+    (gs, gv), (cs, cv) = _side_by_side(product, product_env, reference, reference_env, nq, dens, ops, seed)
+    np.testing.assert_allclose(gv, cv, rtol=REL, atol=1e-13)  # includes the integer measurement outcomes
+    np.testing.assert_allclose(gs, cs, rtol=0, atol=REL * np.abs(cs).max())
+
+
+@pytest.mark.parametrize("vec", ["1", "2", "4"])
+def test_every_vector_width_is_bit_exact(vec, oracle, oracle_env):
+    """QUEST_B200_VEC forces 8-, 16- and 32-byte vectors: each instantiation must give the same bits.
+    Runs in a subprocess because the width is read once at createQuESTEnv."""
+    import subprocess
+    import sys
+
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "from quest_b200 import capi, circuits\n"
+        "gpu = capi.load_product(); cpu = capi.load(capi.ORACLE_LIB)\n"
+        "ge = gpu.createQuESTEnv(); ce = cpu.createQuESTEnv()\n"
+        "for nq, dens, seed in [(3, False, 1), (11, False, 2), (3, True, 3), (6, True, 4)]:\n"
+        "    ops = circuits.random_circuit(nq, 200, seed, density=dens, measure=False)\n"
+        "    st = []\n"
+        "    for lib, env in ((gpu, ge), (cpu, ce)):\n"
+        "        q = lib.createDensityQureg(nq, env) if dens else lib.createQureg(nq, env)\n"
+        "        circuits.prepare(lib, q, seed); circuits.run_circuit(lib, q, ops, seed=seed)\n"
+        "        st.append(lib.get_state(q)); lib.destroyQureg(q, env)\n"
+        "    assert np.array_equal(st[0].view(np.float64), st[1].view(np.float64)), (nq, dens)\n"
+        "print('ok')\n" % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    env = dict(os.environ, QUEST_B200_VEC=vec)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_many_controls_overflow_the_insertion_plan(product, product_env, oracle, oracle_env):
+    """More than 7 controls: the extra ones are checked by predicate instead of index insertion."""
+    nq = 14
+    ops = [("multiControlledUnitary", list(range(1, 12)), 0, circuits._unitary(__import__("random").Random(3))),
+           ("multiControlledPhaseShift", list(range(0, 12)), 0.37),
+           ("multiControlledPhaseFlip", list(range(2, 14)))]
+    ops = [("hadamard", t) for t in range(nq)] + ops
+    (gs, _), (cs, _) = _side_by_side(product, product_env, oracle, oracle_env, nq, False, ops, 5)
+    assert np.array_equal(gs.view(np.float64), cs.view(np.float64))
+
+
+# ---- full-size properties (BASELINE configs are 30 qubits; the oracle cannot follow there) -------------------
+
+def test_config2_properties_at_28_qubits(product, product_env):
+    """Size-independent properties at a size the CPU cannot check element-wise in test time: unitarity (norm
+    kept), H*H = identity bit pattern on a basis state, CNOT involution, P(0)+P(1)=1 on every qubit."""
+    nq = 28
+    q = product.createQureg(nq, product_env)
+    product.initPlusState(q)
+    for t in range(nq):
+        product.compactUnitary(q, t, product.complex(circuits.SWEEP_ALPHA), product.complex(circuits.SWEEP_BETA))
+    assert abs(product.calcTotalProb(q) - 1.0) < 1e-12
+    probs = [product.calcProbOfOutcome(q, t, 0) for t in range(nq)]
+    # each qubit was rotated independently from |+>: P(0) is the same closed form for every target
+    a, b = circuits.SWEEP_ALPHA, circuits.SWEEP_BETA
+    expect = abs((a - b.conjugate()) / np.sqrt(2)) ** 2
+    np.testing.assert_allclose(probs, expect, rtol=1e-12)
+    # involutions restore the exact state: X X, CNOT CNOT, and H H up to rounding
+    before = [product.getAmp(q, i) for i in (0, 1, 12345, (1 << nq) - 1)]
+    for t in (0, 1, 2, 13, nq - 1):
+        product.pauliX(q, t); product.pauliX(q, t)
+        product.controlledNot(q, (t + 1) % nq, t); product.controlledNot(q, (t + 1) % nq, t)
+    after = [product.getAmp(q, i) for i in (0, 1, 12345, (1 << nq) - 1)]
+    assert [(z.real, z.imag) for z in before] == [(z.real, z.imag) for z in after]
+    product.destroyQureg(q, product_env)
+
+
+def test_qft_of_basis_state_is_uniform(product, product_env):
+    """configs[2] at 24 qubits: QFT of a computational basis state has |amp|^2 = 2^-n everywhere, so every
+    per-qubit probability is exactly one half."""
+    nq = 24
+    q = product.createQureg(nq, product_env)
+    product.initClassicalState(q, 0x2AAAAA & ((1 << nq) - 1))
+    scal = circuits.run_circuit(product, q, circuits.config3_qft(nq))
+    np.testing.assert_allclose(scal, 0.5, atol=1e-12)
+    assert abs(product.calcTotalProb(q) - 1) < 1e-12
+    product.destroyQureg(q, product_env)
