@@ -1,0 +1,315 @@
+#!/usr/bin/env python3
+"""bench.py — gate throughput of the quest-b200 engine on BASELINE.json's headline workload.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+N = 1 : configs[1] — 30-qubit double-precision state-vector, one step = the single-gate sweep (every target
+        0..29 for hadamard, compactUnitary, controlledNot, multiControlledPhaseShift = 120 gate calls).
+N > 1 : one process per GPU (torchrun), the state sharded by its top log2(N) qubits; weak scaling: each GPU
+        keeps a 2^30-amplitude shard (30+log2 N qubits) and one step = a seeded random circuit in which >=25 % of
+        the gates hit shard-crossing qubits (configs[4] recipe).  value = shard-gates/s summed over GPUs.
+
+The JSON line carries: value (inputs resident in HBM, CUDA events on the engine's stream, max over ranks), e2e
+(the same through the public C API with the state uploaded from pinned host memory and a scalar read back every
+step), roofline (dominant kernel: algorithmic bytes / measured launch time against MEASURED_PEAKS.json), and
+cpu_baseline (the reference's own CPU/OpenMP library, oracle/_ref, timed on this box's host cores on a bounded
+sample of the same sweep).  ``--impl reference`` runs only that CPU library and prints the same line shape.
+Nothing here reads /root/reference.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from quest_b200 import capi, circuits  # noqa: E402
+
+BYTES_PER_AMP = {"hadamard": 32, "compactUnitary": 32, "rotateY": 32, "controlledNot": 16,
+                 "multiControlledPhaseShift": 4, "measure": 32}  # algorithmic, double precision
+
+
+def read_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons every 200 ms while the timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.proc, self.lines = device, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the reference's own CPU library on a bounded sample of the sweep
+# ------------------------------------------------------------------------------------------------------------
+
+def cpu_sample_ops(nq, targets):
+    ops = []
+    for t in targets:
+        ops.append(("hadamard", t))
+        ops.append(("compactUnitary", t, circuits.SWEEP_ALPHA, circuits.SWEEP_BETA))
+        ops.append(("controlledNot", (t + 1) % nq, t))
+        ops.append(("multiControlledPhaseShift", [t, (t + 1) % nq, (t + 2) % nq], 0.7))
+    return ops
+
+
+def load_cpu_library():
+    if os.path.isfile(capi.REFERENCE_LIB):
+        return capi.load(capi.REFERENCE_LIB), "reference"
+    if not os.path.isfile(capi.ORACLE_LIB):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True, stdout=subprocess.DEVNULL)
+    return capi.load(capi.ORACLE_LIB), "port"
+
+
+def time_cpu(nq, targets, steps, warmup):
+    """Wall-clock the CPU library on `steps` repetitions of the sample; returns (gates/s, cores, kind, seconds)."""
+    lib, kind = load_cpu_library()
+    env = lib.createQuESTEnv()
+    q = lib.createQureg(nq, env)
+    lib.initPlusState(q)
+    ops = cpu_sample_ops(nq, targets)
+    for _ in range(warmup):
+        circuits.run_circuit(lib, q, ops[:4])
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        circuits.run_circuit(lib, q, ops)
+    dt = time.perf_counter() - t0
+    lib.destroyQureg(q, env)
+    cores = int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
+    return steps * len(ops) / dt, cores, kind, dt, len(ops)
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    nq = args.qubits
+    targets = [0, 15, nq - 1]
+    value, cores, kind, dt, per_step = time_cpu(nq, targets, args.steps, min(args.warmup, 1))
+    sample = (f"{per_step} gates per step: config-2 sweep restricted to targets {targets} at {nq} qubits, "
+              f"{args.steps} steps, wall clock {dt:.1f} s")
+    line = {
+        "impl": "reference", "metric": "gates/sec (30q double state-vector single-gate sweep)", "value": value,
+        "unit": "gates/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"configs[1] sweep, bounded sample on host CPU ({nq} qubits)", "qubits": nq},
+        "cpu_baseline": {"value": value, "unit": "gates/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "gates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------------------
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="quest_b200", choices=["quest_b200", "reference"])
+    ap.add_argument("--qubits", type=int, default=30, help="qubits per 1-GPU shard (default 30 = BASELINE config)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the quest-b200 arm has no CPU fallback")
+    warmup = max(args.warmup, 3)
+    lib = capi.load_product()
+    lib.lib.qb200_getStream.restype = ctypes.c_void_p
+    lib.lib.qb200_getLaunchCount.restype = ctypes.c_ulonglong
+    env = lib.createQuESTEnv()
+    device = lib.lib.qb200_getDevice()
+    torch.cuda.set_device(device)
+    stream = torch.cuda.ExternalStream(lib.lib.qb200_getStream(), device=device)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", device))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    shard_bits = args.qubits
+    nq = shard_bits + int(math.log2(world))
+    if world == 1:
+        ops = circuits.config2_sweep(nq)
+        workload = f"configs[1]: {nq}-qubit state-vector single-gate sweep, every target, 4 gate classes (120 gates/step)"
+    else:
+        ops = [op for op in circuits.config5_sharded(nq, layers=3, seed=34) if op[0] != "measure"]
+        workload = (f"configs[4] recipe, weak scaling: {nq}-qubit random circuit sharded over {world} GPUs "
+                    f"(2^{shard_bits} amplitudes per GPU), >=25% of gates on shard-crossing qubits ({len(ops)} gates/step)")
+    q = lib.createQureg(nq, env)
+    n_local = int(q.numAmpsPerChunk)
+    lib.initPlusState(q)
+    # a dense, non-trivial state: one rotation per qubit (same recipe on the CPU arm)
+    for t in range(nq):
+        lib.rotateY(q, t, 0.1 * (t + 1))
+
+    def step():
+        for op in ops:
+            circuits.apply_op(lib, q, op)
+
+    for _ in range(warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(device)
+    sampler.start()
+    launches0 = lib.lib.qb200_getLaunchCount()
+    # one event before every gate call + one at the end: per-launch device times inside the timed region
+    marks = []
+    barrier()
+    for _ in range(args.steps):
+        for op in ops:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(stream)
+            marks.append((op[0], op[1] if isinstance(op[1], int) else -1, ev))
+            circuits.apply_op(lib, q, op)
+    end = torch.cuda.Event(enable_timing=True)
+    end.record(stream)
+    barrier()
+    total_ms = marks[0][2].elapsed_time(end)
+    launches = lib.lib.qb200_getLaunchCount() - launches0
+    clocks = sampler.stop()
+    if world > 1:
+        t = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    gates = args.steps * len(ops)
+    value = world * gates / (total_ms * 1e-3)
+
+    # roofline of the dominant kernel (dense one-target pass, qb::k_pairs): algorithmic bytes 32*N per launch
+    peak, peak_src = read_peaks()
+    evs = [m[2] for m in marks] + [end]
+    durs = {}
+    for i, (name, _, _) in enumerate(marks):
+        durs.setdefault(name, []).append(evs[i].elapsed_time(evs[i + 1]))
+    dense = [d for name in ("hadamard", "compactUnitary", "rotateY") for d in durs.get(name, [])]
+    dense_ms = sum(dense) / max(len(dense), 1)
+    achieved = 32.0 * n_local / (dense_ms * 1e-3) / 1e9 if dense else None
+    traffic = None
+    prof = os.path.join(ROOT, "profiles", "dominant_kernel.json")
+    if os.path.isfile(prof):
+        traffic = json.load(open(prof)).get("dram_bytes_per_launch")
+    roofline = {"bound": "hbm", "kernel": "qb::k_pairs (dense one-target gate: hadamard/compactUnitary)",
+                "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                "frac": achieved / peak if achieved else None, "traffic": traffic,
+                "algorithmic_bytes_per_launch": 32.0 * n_local, "launches_timed": len(dense), "ms_per_launch": dense_ms,
+                "per_class_ms": {k: sum(v) / len(v) for k, v in durs.items()},
+                "share_of_step": sum(dense) / total_ms if dense else None}
+
+    # e2e: every step uploads the state from pinned host memory through initStateFromAmps, runs the same gates and
+    # reads a scalar back through calcTotalProb (host wall clock, max over ranks)
+    e2e = None
+    if not args.no_e2e and world == 1:
+        re = torch.empty(n_local, dtype=torch.float64, pin_memory=True)
+        im = torch.empty(n_local, dtype=torch.float64, pin_memory=True)
+        re.fill_(1.0 / math.sqrt(float(q.numAmpsTotal)))
+        im.zero_()
+        pre = ctypes.cast(re.data_ptr(), ctypes.POINTER(ctypes.c_double))
+        pim = ctypes.cast(im.data_ptr(), ctypes.POINTER(ctypes.c_double))
+
+        def e2e_step():
+            lib.initStateFromAmps(q, pre, pim)
+            step()
+            return lib.calcTotalProb(q)
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            prob = e2e_step()
+        barrier()
+        dt = time.perf_counter() - t0
+        assert abs(prob - 1.0) < 1e-9, prob
+        e2e = {"value": gates / dt, "unit": "gates/s", "h2d_bytes_per_step": 16 * n_local, "d2h_bytes_per_step": 8,
+               "ms_per_step": 1e3 * dt / args.steps,
+               "what": "initStateFromAmps(pinned host) + 120 gate calls + calcTotalProb per step, host wall clock"}
+        del re, im
+    lib.destroyQureg(q, env)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        targets = [0, 15, nq - 1]
+        v, cores, kind, dt, per_step = time_cpu(nq, targets, 1, 1)
+        cpu = {"value": v, "unit": "gates/s", "cores": cores, "kind": kind,
+               "sample": f"{per_step} gates: config-2 sweep restricted to targets {targets} at {nq} qubits, wall clock {dt:.1f} s"}
+
+    if rank == 0:
+        line = {
+            "metric": "gates/sec (30q double state-vector single-gate sweep)" if world == 1 else
+                      "shard-gates/sec summed over GPUs (2^30-amplitude shards, sharded random circuit)",
+            "value": value, "unit": "gates/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload, "qubits": nq, "amps_per_gpu": n_local, "gates_per_step": len(ops),
+                       "l2": "state (16 GiB per GPU) is far larger than L2: every pass streams from HBM"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    lib.destroyQuESTEnv(env)
+
+
+if __name__ == "__main__":
+    main()
