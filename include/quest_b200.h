@@ -33,6 +33,20 @@ void qb200_getDevicePointers(Qureg qureg, void** real, void** imag);
  * Stands in for direct reads of Qureg.stateVec (QuEST_common.c:174-177). */
 void qb200_copyAmpsToHost(Qureg qureg, long long int start, long long int n, qreal* reals, qreal* imags);
 
+/* Sum of |amplitude|^2 over numAmps amplitudes held in device arrays dReal/dImag, written as one double to device
+ * memory at dSumOut, enqueued on cudaStream (0 = default stream).  Returns 0 on success, non-zero after printing the
+ * reason to stderr.  This entry point has no counterpart in the reference: it exists for hosts that must not
+ * allocate device memory (another runtime owns all of HBM, a fixed MPS/MIG quota, a service loop that cannot
+ * afford cudaMalloc's device-wide synchronisation, or callers that hold only raw amplitude pointers and no QuESTEnv).
+ * It calls no allocator; its working memory is a fixed 256 KiB + 256 B array inside the library image, one per GPU,
+ * kept until the process exits.  Limits: numAmps <= QB200_NOALLOC_MAX_AMPS (2^31), larger sizes are refused.  All
+ * calls on a GPU share that array (the call clears the counter it needs itself): calls that overlap in time on
+ * one GPU race and must be serialised by the caller.  The first call on each GPU performs a one-time address
+ * look-up and should be made outside of any stream capture. */
+#define QB200_NOALLOC_MAX_AMPS (1LL << 31)
+int qb200_calcTotalProbNoAlloc(const qreal* dReal, const qreal* dImag, long long int numAmps, double* dSumOut,
+                               void* cudaStream);
+
 #ifdef __cplusplus
 }
 #endif
