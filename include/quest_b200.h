@@ -33,6 +33,13 @@ void qb200_getDevicePointers(Qureg qureg, void** real, void** imag);
  * Stands in for direct reads of Qureg.stateVec (QuEST_common.c:174-177). */
 void qb200_copyAmpsToHost(Qureg qureg, long long int start, long long int n, qreal* reals, qreal* imags);
 
+/* Test hook (host logic only, makes no CUDA call): the plan rank `chunkId` of a register with 2^localBits amplitudes
+ * per shard would execute for a one-target gate.  Stands in for the reference's per-gate local/distributed decision
+ * (halfMatrixBlockFitsInChunk / chunkIsUpper / getChunkPairId, QuEST_cpu_distributed.c:231-365).  Layout of `out`
+ * (18 words) is documented at the definition. */
+void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long long ctrlMask, int vec,
+                         unsigned long long* out);
+
 /* Sum of |amplitude|^2 over numAmps amplitudes held in device arrays dReal/dImag, written as one double to device
  * memory at dSumOut, enqueued on cudaStream (0 = default stream).  Returns 0 on success, non-zero after printing the
  * reason to stderr.  This entry point has no counterpart in the reference: it exists for hosts that must not

@@ -71,11 +71,7 @@ struct QuregRec {
 
 inline QuregRec* rec(const Qureg& q) { return reinterpret_cast<QuregRec*>(q.pairStateVec.real); }
 
-inline int log2i(u64 x) {
-    int l = 0;
-    while ((1ull << l) < x) ++l;
-    return l;
-}
+inline int log2i(u64 x) { return qb::log2u(x); }
 
 void requireEngine() {
     if (!g.up) {
@@ -105,39 +101,6 @@ inline int pickVec(idx_t n, idx_t limit = 4) {
     return v;
 }
 
-// ---- plan construction ----------------------------------------------------------------------------------
-// zeroBits: amplitude-index bits that the task enumeration must hold at 0 (the kernel ORs them in itself);
-// oneMask : amplitude-index bits that must be 1 (controls).  Bits below log2(VEC) never enter the plan: a low
-// zero-bit is the kernel's TLO, low one-bits become the lane predicate.
-struct Planned {
-    BitPlan plan;
-    u64 nTasks;
-};
-
-Planned makePlan(idx_t n, int vec, std::initializer_list<int> zeroBits, u64 oneMask) {
-    const int v = log2i(vec);
-    Planned out;
-    std::memset(&out.plan, 0, sizeof out.plan);
-    std::vector<int> pos;
-    for (int b : zeroBits)
-        if (b >= v) pos.push_back(b - v);
-    out.plan.loMask = (unsigned int)(oneMask & (u64)(vec - 1));
-    for (int b = v; b < 63; ++b) {
-        if (!((oneMask >> b) & 1)) continue;
-        if ((int)pos.size() < kMaxInsert) {
-            pos.push_back(b - v);
-            out.plan.setMask |= 1ull << (b - v);
-        } else {
-            out.plan.skipMask |= 1ull << (b - v);
-        }
-    }
-    std::sort(pos.begin(), pos.end());
-    out.plan.nIns = (int)pos.size();
-    for (int i = 0; i < out.plan.nIns; ++i) out.plan.pos[i] = pos[i];
-    out.nTasks = ((u64)n / vec) >> out.plan.nIns;
-    return out;
-}
-
 // compile-time dispatch on (VEC, TLO): TLO = target lane bit when the target is inside the vector, else -1
 template <class F>
 void dispatchVT(int vec, int target, F&& f) {
@@ -162,18 +125,7 @@ void dispatchV(int vec, F&& f) {
     else f(std::integral_constant<int, 1>());
 }
 
-// Controls on qubits that select the shard cost nothing: this rank either satisfies them (drop the bits) or
-// holds no selected amplitude (skip the launch).  Mirrors the global-index tests of QuEST_cpu.c:1841,2694.
-// Returns false when this shard has nothing to do.
-bool localiseControls(const Qureg& q, u64& mask) {
-    const QuregRec* r = rec(q);
-    const u64 globalBits = mask >> r->localBits;
-    if (globalBits) {
-        if (((u64)q.chunkId & globalBits) != globalBits) return false;
-        mask &= (1ull << r->localBits) - 1ull;
-    }
-    return true;
-}
+bool localiseControls(const Qureg& q, u64& mask) { return qb::localiseControls(rec(q)->localBits, q.chunkId, mask); }
 
 u64 maskOf(const int* qubits, int n) {
     u64 m = 0;
@@ -183,56 +135,42 @@ u64 maskOf(const int* qubits, int n) {
 
 // ---- the two gate launchers ------------------------------------------------------------------------------
 
-// Target qubit selects the shard: fused exchange+combine over the partner's peer mapping (see k_pairsPeer).
-// The pairs are split between the two GPUs on the highest local bit that is not a control; the rank whose
-// global bit is 0 ("upper", QuEST_cpu_distributed.c:231-237) takes the 0 half.
-template <class Op>
-void launchPairsAcrossShards(const Qureg& q, int target, u64 ctrlMask, const Op& op) {
-    QuregRec* r = rec(q);
-    const int gbit = target - r->localBits;
-    const comm::Partner peer = comm::partnerOf(q, gbit);
-    const bool amUpper = ((q.chunkId >> gbit) & 1) == 0;
-    const int vec = pickVec(r->n);
-    const int v = log2i(vec);
-    int split = -1;
-    for (int b = r->localBits - 1; b >= v; --b)
-        if (!((ctrlMask >> b) & 1)) { split = b; break; }
-    comm::pairBarrier(peer.rank, g.stream);  // partner has finished everything enqueued before this gate
-    if (split >= 0 || amUpper) {
-        Planned p = split >= 0 ? makePlan(r->n, vec, {split}, ctrlMask) : makePlan(r->n, vec, {}, ctrlMask);
-        if (split >= 0 && !amUpper) p.plan.setMask |= 1ull << (split - v);
-        qreal* upRe = amUpper ? r->re : peer.re;
-        qreal* upIm = amUpper ? r->im : peer.im;
-        qreal* loRe = amUpper ? peer.re : r->re;
-        qreal* loIm = amUpper ? peer.im : r->im;
-        if (p.nTasks) {
-            dispatchV(vec, [&](auto V) {
-                k_pairsPeer<Op, decltype(V)::value>
-                    <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(upRe, upIm, loRe, loIm, p.nTasks, p.plan, op);
-            });
-            launched();
-        }
-    }
-    comm::pairBarrier(peer.rank, g.stream);  // partner's remote writes into this shard have landed
-}
-
+// One-target gate on a (possibly sharded) register.  qb::planShardedGate (qb_plan.h) decides what this rank does:
+//   skip  - a control on a shard-selecting qubit is 0 for this shard;
+//   local - one k_pairs launch over the shard;
+//   cross - the target qubit selects the shard: fused exchange+combine over the partner's peer mapping
+//           (k_pairsPeer); this rank processes its half of the pairs between two stream-ordered handshakes.
 template <class Op>
 void launchPairs(const Qureg& q, int target, u64 ctrlMask, const Op& op) {
     QuregRec* r = rec(q);
-    if (!localiseControls(q, ctrlMask)) return;
-    if (target >= r->localBits) {
-        launchPairsAcrossShards(q, target, ctrlMask, op);
+    const int vec = pickVec(r->n);
+    const ShardedGate sg = planShardedGate(r->localBits, q.chunkId, target, ctrlMask, vec);
+    if (sg.action == kShardSkip) return;
+    const Planned& p = sg.planned;
+    if (sg.action == kShardLocal) {
+        if (p.nTasks == 0) return;
+        const int tvb = target - log2i(vec);
+        dispatchVT(vec, target, [&](auto V, auto T) {
+            k_pairs<Op, decltype(V)::value, decltype(T)::value>
+                <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(r->re, r->im, p.nTasks, p.plan, tvb, op);
+        });
+        launched();
         return;
     }
-    const int vec = pickVec(r->n);
-    const Planned p = makePlan(r->n, vec, {target}, ctrlMask);
-    if (p.nTasks == 0) return;
-    const int tvb = target - log2i(vec);
-    dispatchVT(vec, target, [&](auto V, auto T) {
-        k_pairs<Op, decltype(V)::value, decltype(T)::value>
-            <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(r->re, r->im, p.nTasks, p.plan, tvb, op);
-    });
-    launched();
+    const comm::Partner peer = comm::partnerOf(q, target - r->localBits);
+    comm::pairBarrier(peer.rank, g.stream);  // partner has finished everything enqueued before this gate
+    if (sg.launches) {
+        qreal* upRe = sg.amUpper ? r->re : peer.re;
+        qreal* upIm = sg.amUpper ? r->im : peer.im;
+        qreal* loRe = sg.amUpper ? peer.re : r->re;
+        qreal* loIm = sg.amUpper ? peer.im : r->im;
+        dispatchV(vec, [&](auto V) {
+            k_pairsPeer<Op, decltype(V)::value>
+                <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(upRe, upIm, loRe, loIm, p.nTasks, p.plan, op);
+        });
+        launched();
+    }
+    comm::pairBarrier(peer.rank, g.stream);  // partner's remote writes into this shard have landed
 }
 
 template <class Op>
@@ -841,6 +779,20 @@ void qb200_getDevicePointers(Qureg qureg, void** real, void** imag) {
     QuregRec* r = rec(qureg);
     *real = r->re;
     *imag = r->im;
+}
+
+// Host planning logic exposed for CPU-only tests (no CUDA call is made): what would rank `chunkId` of a register
+// with 2^localBits amplitudes per shard do for a one-target gate?  out[0..7] = action, partner, amUpper, launches,
+// nTasks, nIns, setMask, loMask; out[8..15] = insertion positions; out[16] = skipMask; out[17] = local ctrlMask.
+void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long long ctrlMask, int vec,
+                         unsigned long long* out) {
+    const ShardedGate sg = planShardedGate(localBits, chunkId, target, ctrlMask, vec);
+    out[0] = sg.action; out[1] = sg.partner; out[2] = sg.amUpper; out[3] = sg.launches;
+    out[4] = sg.planned.nTasks; out[5] = sg.planned.plan.nIns; out[6] = sg.planned.plan.setMask;
+    out[7] = sg.planned.plan.loMask;
+    for (int i = 0; i < kMaxInsert; ++i) out[8 + i] = sg.planned.plan.pos[i];
+    out[16] = sg.planned.plan.skipMask;
+    out[17] = sg.ctrlMask;
 }
 
 }  // extern "C"

@@ -10,20 +10,9 @@
 #include <cstdint>
 
 #include "QuEST_precision.h"
+#include "qb_plan.h"
 
 namespace qb {
-
-constexpr int kMaxInsert = 8;  // target + up to 7 controls by insertion; further controls by predicate
-
-// Host-built description of which vectors a launch visits: dense task k -> vector index.
-// Insert a 0 bit at each pos[i] (ascending, vector-index space), then OR setMask.
-struct BitPlan {
-    int nIns;
-    int pos[kMaxInsert];
-    unsigned long long setMask;   // control bits forced to 1 (vector-index space)
-    unsigned long long skipMask;  // overflow controls: task is skipped unless all are 1 (vector-index space)
-    unsigned int loMask;          // control bits that fall inside a vector (lane space)
-};
 
 __device__ __forceinline__ unsigned long long expand(unsigned long long k, const BitPlan& p) {
 #pragma unroll

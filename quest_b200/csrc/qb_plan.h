@@ -1,0 +1,137 @@
+// quest-b200 host planning logic, free of any CUDA dependency so it can be unit-tested on a CPU-only machine
+// (tests/test_shard_plan.py drives it through qb200_debugPlanGate with world_size-2/4 gloo processes).
+//
+//   BitPlan      - which vectors a launch visits (dense task index -> vector index by bit insertion)
+//   ShardedGate  - for a register sharded over G GPUs by its top log2(G) qubits (reference model:
+//                  QuEST/src/CPU/QuEST_cpu_distributed.c), what THIS rank does for a one-target gate:
+//                  nothing, a local pass, or its half of a pass shared with the partner rank.
+#pragma once
+
+#include <algorithm>
+#include <cstring>
+#include <initializer_list>
+#include <vector>
+
+namespace qb {
+
+constexpr int kMaxInsert = 8;  // target + up to 7 controls by insertion; further controls by predicate
+
+// Insert a 0 bit at each pos[i] (ascending, vector-index space), then OR setMask.
+struct BitPlan {
+    int nIns;
+    int pos[kMaxInsert];
+    unsigned long long setMask;   // control bits forced to 1 (vector-index space)
+    unsigned long long skipMask;  // overflow controls: task is skipped unless all are 1 (vector-index space)
+    unsigned int loMask;          // control bits that fall inside a vector (lane space)
+};
+
+struct Planned {
+    BitPlan plan;
+    unsigned long long nTasks;
+};
+
+inline int log2u(unsigned long long x) {
+    int l = 0;
+    while ((1ull << l) < x) ++l;
+    return l;
+}
+
+// zeroBits: amplitude-index bits the enumeration holds at 0 (the kernel addresses their 1-partners itself);
+// oneMask : amplitude-index bits that must be 1 (controls).  Bits below log2(vec) never enter the plan: a low
+// zero-bit is handled inside the vector by the kernel (TLO), low one-bits become the lane predicate loMask.
+inline Planned makePlan(long long n, int vec, std::initializer_list<int> zeroBits, unsigned long long oneMask) {
+    const int v = log2u((unsigned long long)vec);
+    Planned out;
+    std::memset(&out.plan, 0, sizeof out.plan);
+    std::vector<int> pos;
+    for (int b : zeroBits)
+        if (b >= v) pos.push_back(b - v);
+    out.plan.loMask = (unsigned int)(oneMask & (unsigned long long)(vec - 1));
+    for (int b = v; b < 63; ++b) {
+        if (!((oneMask >> b) & 1)) continue;
+        if ((int)pos.size() < kMaxInsert) {
+            pos.push_back(b - v);
+            out.plan.setMask |= 1ull << (b - v);
+        } else {
+            out.plan.skipMask |= 1ull << (b - v);
+        }
+    }
+    std::sort(pos.begin(), pos.end());
+    out.plan.nIns = (int)pos.size();
+    for (int i = 0; i < out.plan.nIns; ++i) out.plan.pos[i] = pos[i];
+    out.nTasks = ((unsigned long long)n / vec) >> out.plan.nIns;
+    return out;
+}
+
+// host twin of the device-side qb::expand (qb_device.cuh)
+inline unsigned long long expandHost(unsigned long long k, const BitPlan& p) {
+    for (int i = 0; i < p.nIns; ++i) {
+        const int b = p.pos[i];
+        const unsigned long long low = k & ((1ull << b) - 1ull);
+        k = ((k >> b) << (b + 1)) | low;
+    }
+    return k | p.setMask;
+}
+
+// Controls on qubits that select the shard cost nothing: this rank either satisfies them (the bits are dropped)
+// or holds no selected amplitude (nothing to do).  Mirrors the global-index tests of QuEST_cpu.c:1841,2694.
+inline bool localiseControls(int localBits, int chunkId, unsigned long long& mask) {
+    const unsigned long long globalBits = mask >> localBits;
+    if (globalBits) {
+        if (((unsigned long long)chunkId & globalBits) != globalBits) return false;
+        mask &= (1ull << localBits) - 1ull;
+    }
+    return true;
+}
+
+enum ShardAction { kShardSkip = 0, kShardLocal = 1, kShardCross = 2 };
+
+struct ShardedGate {
+    int action;           // ShardAction
+    int partner;          // kShardCross: rank holding the other half of every pair (chunkId XOR 2^(t-L))
+    int amUpper;          // kShardCross: this rank's amplitudes are the target-bit-0 halves
+    int launches;         // kShardCross: 0 if this rank has no pairs to process (all local bits are controls)
+    unsigned long long ctrlMask;  // local control bits that remain
+    Planned planned;      // kShardLocal: plan over {target}; kShardCross: plan over this rank's half of the pairs
+};
+
+// local iff 2^target < shard size (halfMatrixBlockFitsInChunk, QuEST_cpu_distributed.c:360-365); otherwise the
+// pairs are split between the two ranks on the highest local bit that is not a control, the upper rank
+// (chunkIsUpper, :231-237) taking the half where that bit is 0.
+inline ShardedGate planShardedGate(int localBits, int chunkId, int target, unsigned long long ctrlMask, int vec) {
+    ShardedGate g;
+    std::memset(&g, 0, sizeof g);
+    const long long n = 1LL << localBits;
+    if (!localiseControls(localBits, chunkId, ctrlMask)) {
+        g.action = kShardSkip;
+        return g;
+    }
+    g.ctrlMask = ctrlMask;
+    if (target < localBits) {
+        g.action = kShardLocal;
+        g.planned = makePlan(n, vec, {target}, ctrlMask);
+        return g;
+    }
+    g.action = kShardCross;
+    const int gbit = target - localBits;
+    g.partner = chunkId ^ (1 << gbit);
+    g.amUpper = ((chunkId >> gbit) & 1) == 0;
+    const int v = log2u((unsigned long long)vec);
+    int split = -1;
+    for (int b = localBits - 1; b >= v; --b)
+        if (!((ctrlMask >> b) & 1)) {
+            split = b;
+            break;
+        }
+    if (split >= 0) {
+        g.planned = makePlan(n, vec, {split}, ctrlMask);
+        if (!g.amUpper) g.planned.plan.setMask |= 1ull << (split - v);
+        g.launches = g.planned.nTasks ? 1 : 0;
+    } else {
+        g.planned = makePlan(n, vec, {}, ctrlMask);
+        g.launches = (g.amUpper && g.planned.nTasks) ? 1 : 0;
+    }
+    return g;
+}
+
+}  // namespace qb

@@ -1,0 +1,224 @@
+"""CPU-only coverage of the multi-GPU path's host logic.
+
+The product decides per gate and per rank whether to skip, run a local pass, or process its half of the pairs of a
+shard-crossing gate (qb_plan.h: planShardedGate, exported for tests as qb200_debugPlanGate; no CUDA call is made).
+Here that REAL plan is executed by a small numpy stand-in for the kernels:
+
+* in one process, emulating every rank of a 2/4/8-way sharded register, against a dense numpy reference — checks that
+  every amplitude pair is owned by exactly one task of exactly one rank;
+* in world_size-2 and -4 gloo process groups, one shard per process, with the partner's amplitudes moved by
+  torch.distributed send/recv where the GPUs would use NVLink peer access — checks the SPMD protocol (partner choice,
+  upper/lower roles, half split, control localisation) end to end against the CPU oracle.
+"""
+import ctypes
+import os
+import random
+
+import numpy as np
+import pytest
+
+from quest_b200 import capi, circuits
+
+ACT_SKIP, ACT_LOCAL, ACT_CROSS = 0, 1, 2
+
+
+def _plan_fn():
+    if not os.path.isfile(capi.PRODUCT_LIB):
+        from quest_b200 import build
+        build.build_product(2)
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    fn = lib.qb200_debugPlanGate
+    fn.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_ulonglong, ctypes.c_int, ctypes.POINTER(ctypes.c_ulonglong)]
+    fn.restype = None
+    return fn
+
+
+def plan_gate(fn, local_bits, chunk, target, ctrl_mask, vec):
+    out = (ctypes.c_ulonglong * 18)()
+    fn(local_bits, chunk, target, ctrl_mask, vec, out)
+    o = list(out)
+    return dict(action=o[0], partner=o[1], upper=bool(o[2]), launches=o[3], n_tasks=o[4], pos=o[8:8 + o[5]],
+                set_mask=o[6], lo_mask=o[7], skip_mask=o[16], ctrl=o[17])
+
+
+def selected_indices(p, vec, target_lane=None):
+    """Amplitude indices of the 'up' element of every pair a launch with plan `p` visits (numpy twin of
+    qb::expand + the lane predicate of k_pairs / k_pairsPeer)."""
+    k = np.arange(p["n_tasks"], dtype=np.uint64)
+    for b in p["pos"]:
+        b = np.uint64(b)
+        low = k & ((np.uint64(1) << b) - np.uint64(1))
+        k = ((k >> b) << (b + np.uint64(1))) | low
+    k |= np.uint64(p["set_mask"])
+    k = k[(k & np.uint64(p["skip_mask"])) == np.uint64(p["skip_mask"])]
+    lanes = [e for e in range(vec) if (e & p["lo_mask"]) == p["lo_mask"] and (target_lane is None or not (e >> target_lane) & 1)]
+    return (k[:, None] * np.uint64(vec) + np.array(lanes, dtype=np.uint64)[None, :]).ravel().astype(np.int64)
+
+
+def apply_2x2(u, up, lo):
+    return u[0, 0] * up + u[0, 1] * lo, u[1, 0] * up + u[1, 1] * lo
+
+
+def dense_reference(state, nq, target, ctrl_mask, u):
+    idx = np.arange(state.size)
+    sel = ((idx & ctrl_mask) == ctrl_mask) & ((idx >> target) & 1 == 0)
+    up = idx[sel]
+    lo = up | (1 << target)
+    out = state.copy()
+    out[up], out[lo] = apply_2x2(u, state[up], state[lo])
+    return out
+
+
+def rand_u(rng):
+    m = np.array(circuits._unitary(rng)).reshape(2, 2)
+    return m
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("vec", [1, 2, 4])
+def test_plan_covers_every_pair_exactly_once(world, vec):
+    fn = _plan_fn()
+    rng = random.Random(100 * world + vec)
+    nq = 9
+    gbits = world.bit_length() - 1
+    L = nq - gbits
+    n = 1 << L
+    v = vec.bit_length() - 1
+    for trial in range(60):
+        target = rng.randrange(nq)
+        others = [q for q in range(nq) if q != target]
+        ctrls = rng.sample(others, rng.choice([0, 0, 1, 2, 3, 8]))
+        cm = sum(1 << c for c in ctrls)
+        u = rand_u(rng)
+        state = np.random.default_rng(trial).standard_normal(1 << nq) + 1j * np.random.default_rng(trial + 1).standard_normal(1 << nq)
+        want = dense_reference(state, nq, target, cm, u)
+        shards = [state[r * n:(r + 1) * n].copy() for r in range(world)]
+        new = [s.copy() for s in shards]
+        touched = [np.zeros(n, dtype=int) for _ in range(world)]
+        for r in range(world):
+            p = plan_gate(fn, L, r, target, cm, vec)
+            if p["action"] == ACT_SKIP:
+                continue
+            if p["action"] == ACT_LOCAL:
+                up = selected_indices(p, vec, target if target < v else None)
+                lo = up | (1 << target)
+                new[r][up], new[r][lo] = apply_2x2(u, shards[r][up], shards[r][lo])
+                touched[r][up] += 1
+                touched[r][lo] += 1
+            else:
+                assert p["partner"] == r ^ (1 << (target - L)) and p["upper"] == (((r >> (target - L)) & 1) == 0)
+                if not p["launches"]:
+                    continue
+                idx = selected_indices(p, vec)
+                ur, lr = (r, p["partner"]) if p["upper"] else (p["partner"], r)
+                new[ur][idx], new[lr][idx] = apply_2x2(u, shards[ur][idx], shards[lr][idx])
+                touched[ur][idx] += 1
+                touched[lr][idx] += 1
+        got = np.concatenate(new)
+        np.testing.assert_allclose(got, want, atol=1e-13)
+        # exactly the selected amplitudes were written, each once
+        idx = np.arange(1 << nq)
+        expect_touch = ((idx & cm) == cm).astype(int)
+        assert np.array_equal(np.concatenate(touched), expect_touch), (world, vec, target, ctrls)
+
+
+# ---- gloo process groups: one shard per process ------------------------------------------------------------------
+
+def _worker(rank, world, port, nq, seed, result_path):
+    import torch
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    fn = _plan_fn()
+    gbits = world.bit_length() - 1
+    L = nq - gbits
+    n = 1 << L
+    vec = 4
+    v = 2
+    full = circuits.random_state(1 << nq, seed)
+    shard = full[rank * n:(rank + 1) * n].copy()
+    rng = random.Random(seed)
+    ops = []
+    for _ in range(40):
+        target = rng.randrange(nq) if rng.random() < 0.5 else rng.randrange(L, nq)  # half the gates cross shards
+        others = [q for q in range(nq) if q != target]
+        ctrls = rng.sample(others, rng.choice([0, 0, 1, 2]))
+        ops.append((target, ctrls, circuits._unitary(rng)))
+    for target, ctrls, mat in ops:
+        u = np.array(mat).reshape(2, 2)
+        cm = sum(1 << c for c in ctrls)
+        p = plan_gate(fn, L, rank, target, cm, vec)
+        if p["action"] == ACT_SKIP:
+            continue
+        if p["action"] == ACT_LOCAL:
+            up = selected_indices(p, vec, target if target < v else None)
+            lo = up | (1 << target)
+            shard[up], shard[lo] = apply_2x2(u, shard[up], shard[lo])
+            continue
+        # cross-shard: what the GPUs do with peer loads/stores is done here with send/recv of the touched slices
+        partner = p["partner"]
+        mine = selected_indices(p, vec) if p["launches"] else np.zeros(0, dtype=np.int64)
+        # the partner processes the complementary half: it needs my amplitudes at ITS indices
+        theirs = selected_indices(plan_gate(fn, L, partner, target, cm, vec), vec) \
+            if plan_gate(fn, L, partner, target, cm, vec)["launches"] else np.zeros(0, dtype=np.int64)
+        send_buf = torch.from_numpy(np.ascontiguousarray(shard[theirs]).view(np.float64).copy())
+        recv_buf = torch.empty(2 * mine.size, dtype=torch.float64)
+        reqs = []
+        if send_buf.numel():
+            reqs.append(dist.isend(send_buf, partner))
+        if recv_buf.numel():
+            reqs.append(dist.irecv(recv_buf, partner))
+        for r in reqs:
+            r.wait()
+        remote = recv_buf.numpy().view(np.complex128)
+        if p["upper"]:
+            new_mine, new_remote = apply_2x2(u, shard[mine], remote)
+        else:
+            new_remote, new_mine = apply_2x2(u, remote, shard[mine])
+        shard[mine] = new_mine
+        # "remote write": return the partner's updated amplitudes
+        back = torch.from_numpy(np.ascontiguousarray(new_remote).view(np.float64).copy())
+        got_back = torch.empty(2 * theirs.size, dtype=torch.float64)
+        reqs = []
+        if back.numel():
+            reqs.append(dist.isend(back, partner))
+        if got_back.numel():
+            reqs.append(dist.irecv(got_back, partner))
+        for r in reqs:
+            r.wait()
+        shard[theirs] = got_back.numpy().view(np.complex128)
+    gathered = [torch.empty(2 * n, dtype=torch.float64) for _ in range(world)] if rank == 0 else None
+    dist.gather(torch.from_numpy(shard.view(np.float64).copy()), gathered, dst=0)
+    if rank == 0:
+        np.save(result_path, np.concatenate([g.numpy().view(np.complex128) for g in gathered]))
+        np.save(result_path + ".ops.npy", np.array([(t, sum(1 << c for c in cs)) for t, cs, _ in ops]))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_protocol_over_gloo_matches_oracle(world, oracle, oracle_env, tmp_path):
+    import torch.multiprocessing as mp
+
+    nq, seed = 10, 77 + world
+    port = 29600 + world + (os.getpid() % 200)
+    result = str(tmp_path / "state.npy")
+    mp.spawn(_worker, args=(world, port, nq, seed, result), nprocs=world, join=True)
+    got = np.load(result)
+    # the same gate sequence through the CPU oracle on one unsharded register
+    rng = random.Random(seed)
+    L = nq - (world.bit_length() - 1)
+    q = oracle.createQureg(nq, oracle_env)
+    oracle.set_state(q, circuits.random_state(1 << nq, seed))
+    for _ in range(40):
+        target = rng.randrange(nq) if rng.random() < 0.5 else rng.randrange(L, nq)
+        others = [x for x in range(nq) if x != target]
+        ctrls = rng.sample(others, rng.choice([0, 0, 1, 2]))
+        mat = circuits._unitary(rng)
+        if ctrls:
+            oracle.multiControlledUnitary(q, oracle.int_array(ctrls), len(ctrls), target, oracle.matrix(mat))
+        else:
+            oracle.unitary(q, target, oracle.matrix(mat))
+    want = oracle.get_state(q)
+    oracle.destroyQureg(q, oracle_env)
+    np.testing.assert_allclose(got, want, atol=1e-13)

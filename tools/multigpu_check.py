@@ -1,0 +1,83 @@
+#!/usr/bin/env python3
+"""Multi-GPU parity check, run under torchrun on N GPUs of one box:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
+        tools/multigpu_check.py [--qubits 22]
+
+Every rank drives its shard through the CUDA library; rank 0 gathers the shards and compares with the CPU oracle
+running the same circuit on one unsharded register: measurement-free circuits must match bit for bit, circuits with
+measurements must give the same outcomes and amplitudes to 1e-12 relative (north_star)."""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from quest_b200 import capi, circuits  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--qubits", type=int, default=22)
+    ap.add_argument("--depth", type=int, default=300)
+    args = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    lib = capi.load_product()
+    env = lib.createQuESTEnv()
+    assert (env.rank, env.numRanks) == (rank, world)
+    torch.cuda.set_device(lib.lib.qb200_getDevice())
+    dist.init_process_group("gloo")
+    cpu = capi.load(capi.ORACLE_LIB) if rank == 0 else None
+    cenv = cpu.createQuESTEnv() if rank == 0 else None
+    ok = True
+    for case, (nq, measure, seed) in enumerate([(args.qubits, False, 301), (args.qubits, True, 302), (args.qubits - 5, False, 303),
+                                                 (args.qubits - 3, True, 304)]):
+        ops = circuits.random_circuit(nq, args.depth, seed, measure=measure)
+        # bias: add gates on the shard-selecting qubits so the exchange path is hit hard
+        g = int(np.log2(world))
+        extra = []
+        for t in range(nq - g, nq):
+            extra += [("hadamard", t), ("compactUnitary", t, circuits.SWEEP_ALPHA, circuits.SWEEP_BETA), ("controlledNot", 0, t),
+                      ("controlledNot", t, 1), ("pauliY", t), ("multiControlledUnitary", [2, (t - 1)], t, circuits._unitary(__import__("random").Random(t))),
+                      ("calcProbOfOutcome", t, 1), ("phaseShift", t, 0.3), ("controlledPhaseShift", t, 3, 0.2)]
+        ops = extra + ops + extra
+        q = lib.createQureg(nq, env)
+        assert q.numChunks == world and q.chunkId == rank and q.numAmpsPerChunk * world == q.numAmpsTotal
+        full = circuits.random_state(1 << nq, seed)
+        lib.set_state(q, full)  # every rank passes the full vector; each keeps its slice (reference setAmps semantics)
+        scal = circuits.run_circuit(lib, q, ops, seed=seed)
+        amp = lib.getAmp(q, (1 << nq) - 3)
+        shard = lib.get_state(q)
+        lib.destroyQureg(q, env)
+        gathered = [torch.empty(2 * shard.size, dtype=torch.float64) for _ in range(world)] if rank == 0 else None
+        dist.gather(torch.from_numpy(shard.view(np.float64).copy()), gathered, dst=0)
+        if rank == 0:
+            got = np.concatenate([t.numpy().view(np.complex128) for t in gathered])
+            cq = cpu.createQureg(nq, cenv)
+            cpu.set_state(cq, full)
+            cscal = circuits.run_circuit(cpu, cq, ops, seed=seed)
+            want = cpu.get_state(cq)
+            camp = cpu.getAmp(cq, (1 << nq) - 3)
+            cpu.destroyQureg(cq, cenv)
+            same_bits = np.array_equal(got.view(np.float64), want.view(np.float64))
+            err = np.abs(got - want).max() / np.abs(want).max()
+            scal_ok = np.allclose(scal, cscal, rtol=1e-12, atol=1e-13)
+            amp_ok = abs(complex(amp.real, amp.imag) - complex(camp.real, camp.imag)) <= 1e-12
+            good = scal_ok and amp_ok and (same_bits if not measure else err < 1e-12)
+            ok = ok and good
+            print(f"case {case}: {nq} qubits over {world} GPUs, {len(ops)} ops, measure={measure}: bit-exact={same_bits} "
+                  f"rel.err={err:.2e} scalars_ok={scal_ok} getAmp_ok={amp_ok} -> {'PASS' if good else 'FAIL'}", flush=True)
+    flag = torch.tensor([1 if ok else 0])
+    dist.broadcast(flag, 0)
+    lib.destroyQuESTEnv(env)
+    dist.destroy_process_group()
+    if rank == 0:
+        print("MULTIGPU PARITY", "PASS" if ok else "FAIL", flush=True)
+    sys.exit(0 if flag.item() else 1)
+
+
+if __name__ == "__main__":
+    main()
