@@ -5,9 +5,11 @@
 
 N = 1 : configs[1] — 30-qubit double-precision state-vector, one step = the single-gate sweep (every target
         0..29 for hadamard, compactUnitary, controlledNot, multiControlledPhaseShift = 120 gate calls).
-N > 1 : one process per GPU (torchrun), the state sharded by its top log2(N) qubits; weak scaling: each GPU
-        keeps a 2^30-amplitude shard (30+log2 N qubits) and one step = a seeded random circuit in which >=25 % of
-        the gates hit shard-crossing qubits (configs[4] recipe).  value = shard-gates/s summed over GPUs.
+N > 1 : one process per GPU (torchrun), the state sharded by its top log2(N) qubits; weak scaling of the same
+        sweep: each GPU keeps a 2^30-amplitude shard, the register has 30+log2 N qubits and one step sweeps every
+        target again, so log2 N of the targets select the GPU and run as fused NVLink exchange+combine gates.
+        value = shard-gates/s summed over GPUs (gates/s x N).  For N >= 2 the line also carries
+        "circuit_34q": seconds for the configs[4] 34-qubit random circuit with measurements.
 
 The JSON line carries: value (inputs resident in HBM, CUDA events on the engine's stream, max over ranks), e2e
 (the same through the public C API with the state uploaded from pinned host memory and a scalar read back every
@@ -36,6 +38,16 @@ from quest_b200 import capi, circuits  # noqa: E402
 
 BYTES_PER_AMP = {"hadamard": 32, "compactUnitary": 32, "rotateY": 32, "controlledNot": 16,
                  "multiControlledPhaseShift": 4, "measure": 32}  # algorithmic, double precision
+
+
+def target_of(op):
+    """Target qubit of a circuit op (controlledNot carries its control first)."""
+    name = op[0]
+    if name in ("controlledNot", "controlledPauliY") or name.startswith("controlledRotate") or name in ("controlledCompactUnitary", "controlledUnitary"):
+        return op[2]
+    if name.startswith("multiControlled"):
+        return op[2] if name == "multiControlledUnitary" else -1
+    return op[1] if len(op) > 1 and isinstance(op[1], int) else -1
 
 
 def read_peaks():
@@ -131,6 +143,8 @@ def time_cpu(nq, targets, steps, warmup):
 def run_reference_arm(args, rank, world):
     if rank != 0:
         return
+    # torchrun pins OMP_NUM_THREADS=1 for its workers; the CPU arm is meant to use every host core
+    os.environ["OMP_NUM_THREADS"] = os.environ.get("QUEST_BENCH_THREADS", str(os.cpu_count() or 1))
     nq = args.qubits
     targets = [0, 15, nq - 1]
     value, cores, kind, dt, per_step = time_cpu(nq, targets, args.steps, min(args.warmup, 1))
@@ -161,9 +175,12 @@ def main():
     ap.add_argument("--qubits", type=int, default=30, help="qubits per 1-GPU shard (default 30 = BASELINE config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-34q", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL prints its version banner there)
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
@@ -195,9 +212,10 @@ def main():
         ops = circuits.config2_sweep(nq)
         workload = f"configs[1]: {nq}-qubit state-vector single-gate sweep, every target, 4 gate classes (120 gates/step)"
     else:
-        ops = [op for op in circuits.config5_sharded(nq, layers=3, seed=34) if op[0] != "measure"]
-        workload = (f"configs[4] recipe, weak scaling: {nq}-qubit random circuit sharded over {world} GPUs "
-                    f"(2^{shard_bits} amplitudes per GPU), >=25% of gates on shard-crossing qubits ({len(ops)} gates/step)")
+        ops = circuits.config2_sweep(nq)
+        workload = (f"configs[1] sweep weak-scaled: {nq}-qubit state-vector sharded over {world} GPUs (2^{shard_bits} "
+                    f"amplitudes per GPU), every target, 4 gate classes ({len(ops)} gates/step, "
+                    f"{4 * int(math.log2(world))} of them on shard-selecting qubits)")
     q = lib.createQureg(nq, env)
     n_local = int(q.numAmpsPerChunk)
     lib.initPlusState(q)
@@ -222,7 +240,7 @@ def main():
         for op in ops:
             ev = torch.cuda.Event(enable_timing=True)
             ev.record(stream)
-            marks.append((op[0], op[1] if isinstance(op[1], int) else -1, ev))
+            marks.append((op[0], target_of(op), ev))
             circuits.apply_op(lib, q, op)
     end = torch.cuda.Event(enable_timing=True)
     end.record(stream)
@@ -241,8 +259,13 @@ def main():
     peak, peak_src = read_peaks()
     evs = [m[2] for m in marks] + [end]
     durs = {}
-    for i, (name, _, _) in enumerate(marks):
-        durs.setdefault(name, []).append(evs[i].elapsed_time(evs[i + 1]))
+    cross = {}  # gates whose target qubit selects the GPU: exchange fused into the gate kernel over NVLink
+    for i, (name, tgt, _) in enumerate(marks):
+        d = evs[i].elapsed_time(evs[i + 1])
+        if world > 1 and tgt >= shard_bits:
+            cross.setdefault(name, []).append(d)
+        else:
+            durs.setdefault(name, []).append(d)
     dense = [d for name in ("hadamard", "compactUnitary", "rotateY") for d in durs.get(name, [])]
     dense_ms = sum(dense) / max(len(dense), 1)
     achieved = 32.0 * n_local / (dense_ms * 1e-3) / 1e9 if dense else None
@@ -257,10 +280,26 @@ def main():
                 "per_class_ms": {k: sum(v) / len(v) for k, v in durs.items()},
                 "share_of_step": sum(dense) / total_ms if dense else None}
 
+    nvlink = None
+    if world > 1:
+        # rank 0's view of a global gate includes waiting for a partner that was busy with a gate rank 0 could skip
+        # (controls on shard-selecting qubits); the dense class with the smallest mean is free of that skew
+        means = {k: sum(v) / len(v) for k, v in cross.items() if k in ("hadamard", "compactUnitary", "rotateY")}
+        dense_cross = cross[min(means, key=means.get)] if means else []
+        if dense_cross:
+            ms = sum(dense_cross) / len(dense_cross)
+            per_dir = 16.0 * n_local / (ms * 1e-3) / 1e9  # bytes each GPU sends AND receives per dense global gate
+            nvlink = {"kernel": "qb::k_pairsPeer (dense gate on a shard-selecting qubit, exchange fused over peer memory)",
+                      "ms_per_gate": ms, "gates_timed": len(dense_cross), "bytes_each_way_per_gpu": 16.0 * n_local,
+                      "achieved_GBps_per_direction": per_dir, "peak_measured_peer_copy": 770.0, "peak_nominal": 900.0,
+                      "frac_of_measured": per_dir / 770.0, "frac_of_nominal": per_dir / 900.0,
+                      "per_class_ms": {k: sum(v) / len(v) for k, v in cross.items()},
+                      "includes": "two stream-ordered pair handshakes (NCCL send/recv of 4 bytes) per gate"}
+
     # e2e: every step uploads the state from pinned host memory through initStateFromAmps, runs the same gates and
     # reads a scalar back through calcTotalProb (host wall clock, max over ranks)
     e2e = None
-    if not args.no_e2e and world == 1:
+    if not args.no_e2e:
         re = torch.empty(n_local, dtype=torch.float64, pin_memory=True)
         im = torch.empty(n_local, dtype=torch.float64, pin_memory=True)
         re.fill_(1.0 / math.sqrt(float(q.numAmpsTotal)))
@@ -269,7 +308,8 @@ def main():
         pim = ctypes.cast(im.data_ptr(), ctypes.POINTER(ctypes.c_double))
 
         def e2e_step():
-            lib.initStateFromAmps(q, pre, pim)
+            # each rank uploads its own shard (setAmps keeps the slice that falls into the caller's shard)
+            lib.setAmps(q, rank * n_local, pre, pim, n_local)
             step()
             return lib.calcTotalProb(q)
 
@@ -280,12 +320,38 @@ def main():
             prob = e2e_step()
         barrier()
         dt = time.perf_counter() - t0
+        if world > 1:
+            tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = float(tt.item())
         assert abs(prob - 1.0) < 1e-9, prob
-        e2e = {"value": gates / dt, "unit": "gates/s", "h2d_bytes_per_step": 16 * n_local, "d2h_bytes_per_step": 8,
-               "ms_per_step": 1e3 * dt / args.steps,
-               "what": "initStateFromAmps(pinned host) + 120 gate calls + calcTotalProb per step, host wall clock"}
+        e2e = {"value": world * gates / dt, "unit": "gates/s", "h2d_bytes_per_step": 16 * n_local * world,
+               "d2h_bytes_per_step": 8 * world, "ms_per_step": 1e3 * dt / args.steps,
+               "what": "setAmps(shard from pinned host) + the step's gate calls + calcTotalProb per step, host wall "
+                       "clock, max over ranks"}
         del re, im
     lib.destroyQureg(q, env)
+
+    # configs[4]: the 34-qubit random circuit with measurements, sharded over all GPUs (does not fit one GPU)
+    circuit34 = None
+    if world > 1 and not args.no_34q and (16 << 34) / world < 150e9:
+        q34 = lib.createQureg(34, env)
+        lib.initPlusState(q34)
+        ops34 = circuits.config5_sharded(34, layers=3, seed=34)
+        circuits.run_circuit(lib, q34, ops34[:8])  # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        out34 = circuits.run_circuit(lib, q34, ops34, seed=34)
+        barrier()
+        dt34 = time.perf_counter() - t0
+        tt = torch.tensor([dt34], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        n_global = sum(1 for op in ops34 if target_of(op) >= 34 - int(math.log2(world)))
+        circuit34 = {"seconds": float(tt.item()), "gates": len(ops34), "gates_on_shard_selecting_qubits": n_global,
+                     "measurement_outcomes": [int(x) for x in out34[:3]], "total_prob_after": out34[-1],
+                     "what": "configs[4]: 34-qubit random circuit (hadamard/rotateY/controlledNot/compactUnitary, 30% of "
+                             "targets on the top 3 qubits) + 3 measurements, wall clock incl. scalar read-backs"}
+        lib.destroyQureg(q34, env)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -297,7 +363,7 @@ def main():
     if rank == 0:
         line = {
             "metric": "gates/sec (30q double state-vector single-gate sweep)" if world == 1 else
-                      "shard-gates/sec summed over GPUs (2^30-amplitude shards, sharded random circuit)",
+                      "shard-gates/sec summed over GPUs (configs[1] sweep weak-scaled, 2^30-amplitude shards)",
             "value": value, "unit": "gates/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
@@ -305,6 +371,10 @@ def main():
                        "l2": "state (16 GiB per GPU) is far larger than L2: every pass streams from HBM"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
         }
+        if nvlink:
+            line["nvlink"] = nvlink
+        if circuit34:
+            line["circuit_34q"] = circuit34
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

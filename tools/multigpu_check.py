@@ -44,6 +44,8 @@ def main():
                       ("controlledNot", t, 1), ("pauliY", t), ("multiControlledUnitary", [2, (t - 1)], t, circuits._unitary(__import__("random").Random(t))),
                       ("calcProbOfOutcome", t, 1), ("phaseShift", t, 0.3), ("controlledPhaseShift", t, 3, 0.2)]
         ops = extra + ops + extra
+        if measure:  # a measurement whose qubit selects the shard: whole shards are kept or cleared
+            ops += [("measure", nq - 1), ("calcTotalProb",), ("measureWithStats", nq - g), ("calcTotalProb",)]
         q = lib.createQureg(nq, env)
         assert q.numChunks == world and q.chunkId == rank and q.numAmpsPerChunk * world == q.numAmpsTotal
         full = circuits.random_state(1 << nq, seed)
