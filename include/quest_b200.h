@@ -22,6 +22,22 @@ void qb200_setStream(void* cudaStream);
 /* Number of kernels this process has launched since createQuESTEnv(). */
 unsigned long long qb200_getLaunchCount(void);
 
+/* Gate fusion.  Gate calls may return before the GPU has run them (the reference GPU backend launches
+ * asynchronously too, QuEST_gpu.cu:591); with fusion enabled (default; QUEST_B200_FUSE=0 disables) they are recorded
+ * and executed at the next call that needs the amplitudes, consecutive gates on up to four distinct target qubits
+ * sharing ONE pass over HBM.  Results are bit-identical to gate-at-a-time execution.
+ * qb200_setFusion(0) drains every queue and returns to one kernel per gate call; qb200_flush() drains the queues
+ * without waiting for the GPU; qb200_getFusionStats reports how many fused passes ran and how many gates they held. */
+void qb200_setFusion(int enabled);
+int qb200_getFusion(void);
+void qb200_flush(void);
+void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long* fusedGates);
+
+/* Measurement aid: with timing enabled every fused pass is bracketed by CUDA events on the engine stream;
+ * qb200_getFusedKernelTime synchronises, returns their summed device time and count, and clears the record. */
+void qb200_setKernelTiming(int enabled);
+void qb200_getFusedKernelTime(double* totalMs, unsigned long long* launches);
+
 /* CUDA device ordinal this process drives. */
 int qb200_getDevice(void);
 
@@ -39,6 +55,11 @@ void qb200_copyAmpsToHost(Qureg qureg, long long int start, long long int n, qre
  * (18 words) is documented at the definition. */
 void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long long ctrlMask, int vec,
                          unsigned long long* out);
+
+/* Test hook (host logic only, makes no CUDA call): how the fusion queue would group a gate list for a shard of
+ * 2^localBits amplitudes.  kinds: 0 matrix, 1 hadamard, 2 swap, 3 pauliY, 4 phase, 5 flip.  Layouts at the definition. */
+int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* targets, const unsigned long long* masks,
+                    int* groupsOut, unsigned long long* descOut);
 
 /* Sum of |amplitude|^2 over numAmps amplitudes held in device arrays dReal/dImag, written as one double to device
  * memory at dSumOut, enqueued on cudaStream (0 = default stream).  Returns 0 on success, non-zero after printing the

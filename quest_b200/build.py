@@ -40,7 +40,7 @@ def build_product(prec: int = 2, force: bool = False, verbose: bool = False) -> 
            "-I" + os.path.join(ROOT, "include"), "-I" + CSRC]
     if verbose:
         cmd += ["-Xptxas", "-v"]
-    cmd += ["-x", "cu"] + [os.path.join(CSRC, f) for f in CU_SOURCES + CXX_SOURCES]
+    cmd += [os.path.join(CSRC, f) for f in CU_SOURCES + CXX_SOURCES]  # .cu through nvcc, .cpp straight to g++
     cmd += ["-o", out, "-ldl", "-lpthread"]
     print(" ".join(cmd), flush=True)
     subprocess.run(cmd, check=True)

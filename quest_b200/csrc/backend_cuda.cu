@@ -20,10 +20,14 @@
 #include <vector>
 
 #include "qb_comm.h"
+#include "qb_fuse.h"
 #include "qb_kernels.cuh"
 #include "quest_b200.h"
 #include "quest_internal.h"
 
+// NOTE on host maths: nvcc's headers put float overloads of sqrt/cos/sin in the global namespace, while the
+// reference (C99) always calls the double versions and rounds on assignment.  Every libm call below therefore
+// casts its argument to double explicitly, so the single-precision build derives the same coefficients.
 using namespace qb;
 typedef long long int idx_t;
 typedef unsigned long long u64;
@@ -60,6 +64,11 @@ struct Engine {
     double* hResult = nullptr;      // pinned [4]
     int vecCap = 4;                 // QUEST_B200_VEC: upper bound on amplitudes per vector (1, 2 or 4)
     unsigned long long launches = 0;
+    bool fuse = true;               // QUEST_B200_FUSE / qb200_setFusion: record gates and run them in fused passes
+    unsigned long long fusedLaunches = 0, fusedGates = 0;
+    int fuseBlock = 128;            // QUEST_B200_FUSE_BLOCK: threads per CTA of the fused kernel (128 or 256)
+    bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fusedEvents;
 } g;
 
 struct QuregRec {
@@ -67,7 +76,11 @@ struct QuregRec {
     qreal* im;
     idx_t n;       // amplitudes in this shard
     int localBits; // log2 n
+    std::vector<PendingOp> queue;  // gates recorded but not yet executed (qb_fuse.h)
 };
+
+std::vector<QuregRec*> liveRegisters;  // for syncQuESTEnv / qb200_setFusion: every queue must be drainable
+constexpr size_t kQueueCap = 8192;
 
 inline QuregRec* rec(const Qureg& q) { return reinterpret_cast<QuregRec*>(q.pairStateVec.real); }
 
@@ -125,38 +138,40 @@ void dispatchV(int vec, F&& f) {
     else f(std::integral_constant<int, 1>());
 }
 
-bool localiseControls(const Qureg& q, u64& mask) { return qb::localiseControls(rec(q)->localBits, q.chunkId, mask); }
-
 u64 maskOf(const int* qubits, int n) {
     u64 m = 0;
     for (int i = 0; i < n; ++i) m |= 1ull << qubits[i];
     return m;
 }
 
-// ---- the two gate launchers ------------------------------------------------------------------------------
+// ---- gate execution ----------------------------------------------------------------------------------------
+// Every gate becomes a qb::PendingOp.  It is either executed at once (runOpNow: one single-gate kernel, the
+// shard-crossing path) or recorded in the register's queue and executed later inside a fused pass (flush).
 
-// One-target gate on a (possibly sharded) register.  qb::planShardedGate (qb_plan.h) decides what this rank does:
-//   skip  - a control on a shard-selecting qubit is 0 for this shard;
-//   local - one k_pairs launch over the shard;
-//   cross - the target qubit selects the shard: fused exchange+combine over the partner's peer mapping
-//           (k_pairsPeer); this rank processes its half of the pairs between two stream-ordered handshakes.
+// One dense gate on THIS shard only (target < localBits, controls already local).
 template <class Op>
-void launchPairs(const Qureg& q, int target, u64 ctrlMask, const Op& op) {
+void runPairsNow(const Qureg& q, int target, u64 ctrlMask, const Op& op) {
+    QuregRec* r = rec(q);
+    const int vec = pickVec(r->n);
+    const Planned p = makePlan(r->n, vec, {target}, ctrlMask);
+    if (p.nTasks == 0) return;
+    const int tvb = target - log2i(vec);
+    dispatchVT(vec, target, [&](auto V, auto T) {
+        k_pairs<Op, decltype(V)::value, decltype(T)::value>
+            <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(r->re, r->im, p.nTasks, p.plan, tvb, op);
+    });
+    launched();
+}
+
+// Dense gate whose target qubit selects the shard: fused exchange+combine over the partner's peer mapping
+// (k_pairsPeer).  qb::planShardedGate (qb_plan.h) gives this rank's role and its half of the pairs; two
+// stream-ordered handshakes bracket the kernel.
+template <class Op>
+void runPairsAcrossShards(const Qureg& q, int target, u64 ctrlMask, const Op& op) {
     QuregRec* r = rec(q);
     const int vec = pickVec(r->n);
     const ShardedGate sg = planShardedGate(r->localBits, q.chunkId, target, ctrlMask, vec);
-    if (sg.action == kShardSkip) return;
     const Planned& p = sg.planned;
-    if (sg.action == kShardLocal) {
-        if (p.nTasks == 0) return;
-        const int tvb = target - log2i(vec);
-        dispatchVT(vec, target, [&](auto V, auto T) {
-            k_pairs<Op, decltype(V)::value, decltype(T)::value>
-                <<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(r->re, r->im, p.nTasks, p.plan, tvb, op);
-        });
-        launched();
-        return;
-    }
     const comm::Partner peer = comm::partnerOf(q, target - r->localBits);
     comm::pairBarrier(peer.rank, g.stream);  // partner has finished everything enqueued before this gate
     if (sg.launches) {
@@ -174,9 +189,8 @@ void launchPairs(const Qureg& q, int target, u64 ctrlMask, const Op& op) {
 }
 
 template <class Op>
-void launchDiag(const Qureg& q, u64 mask, const Op& op) {
+void runDiagNow(const Qureg& q, u64 mask, const Op& op) {
     QuregRec* r = rec(q);
-    if (!localiseControls(q, mask)) return;
     const int vec = pickVec(r->n);
     const Planned p = makePlan(r->n, vec, {}, mask);
     if (p.nTasks == 0) return;
@@ -186,10 +200,142 @@ void launchDiag(const Qureg& q, u64 mask, const Op& op) {
     launched();
 }
 
-OpMatrix asOp(ComplexMatrix2 u) {
-    return OpMatrix{u.r0c0.real, u.r0c0.imag, u.r0c1.real, u.r0c1.imag, u.r1c0.real, u.r1c0.imag, u.r1c1.real, u.r1c1.imag};
+OpMatrix matrixOf(const PendingOp& op) {
+    return OpMatrix{op.c[0], op.c[1], op.c[2], op.c[3], op.c[4], op.c[5], op.c[6], op.c[7]};
 }
-OpCompact asOp(Complex a, Complex b) { return OpCompact{a.real, a.imag, b.real, b.imag}; }
+
+void runOpNow(const Qureg& q, const PendingOp& op) {
+    const bool cross = !isDiagonal(op.kind) && op.target >= rec(q)->localBits;
+    switch (op.kind) {
+        case kFMatrix:
+            cross ? runPairsAcrossShards(q, op.target, op.mask, matrixOf(op)) : runPairsNow(q, op.target, op.mask, matrixOf(op));
+            break;
+        case kFHadamard:
+            cross ? runPairsAcrossShards(q, op.target, op.mask, OpHadamard{op.c[0]}) : runPairsNow(q, op.target, op.mask, OpHadamard{op.c[0]});
+            break;
+        case kFSwap:
+            cross ? runPairsAcrossShards(q, op.target, op.mask, OpSwap{}) : runPairsNow(q, op.target, op.mask, OpSwap{});
+            break;
+        case kFPauliY:
+            cross ? runPairsAcrossShards(q, op.target, op.mask, OpPauliY{op.c[0]}) : runPairsNow(q, op.target, op.mask, OpPauliY{op.c[0]});
+            break;
+        case kFPhase:
+            runDiagNow(q, op.mask, DiagPhase{op.c[0], op.c[1]});
+            break;
+        default:
+            runDiagNow(q, op.mask, DiagFlip{});
+            break;
+    }
+}
+
+// Execute everything recorded for this register: single gates through their own kernel, runs of gates through
+// k_fused (one HBM pass per group, qb_fuse.h).
+void flush(const Qureg& q) {
+    QuregRec* r = rec(q);
+    if (r->queue.empty()) return;
+    std::vector<PendingOp> ops;
+    ops.swap(r->queue);
+    const std::vector<FusedGroup> groups = groupOps(ops, r->localBits);
+    static FusedLaunch fl;  // ~8.5 KB: passed by value as the kernel parameter block
+    for (const FusedGroup& grp : groups) {
+        if (grp.count == 1) {
+            runOpNow(q, ops[grp.first]);
+            continue;
+        }
+        for (int i = 0; i < grp.count; ++i) fl.gates[i] = describe(ops[grp.first + i], grp.bits);
+        for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = grp.bits[j];
+        fl.nGates = grp.count;
+        fl.nThreads = (u64)r->n >> kFuseBits;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (g.timeFused) {
+            CUDA_OK(cudaEventCreate(&e0));
+            CUDA_OK(cudaEventCreate(&e1));
+            CUDA_OK(cudaEventRecord(e0, g.stream));
+        }
+        // 128-thread CTAs, 4 per SM (128 registers per thread): measured best of 64/128/256 threads x 2-6 CTAs
+        if (g.fuseBlock == 256)
+            k_fused<kFuseBits, 256, 2><<<blocksFor(fl.nThreads), 256, 0, g.stream>>>(r->re, r->im, fl);
+        else
+            k_fused<kFuseBits, 128, 4><<<(unsigned int)((fl.nThreads + 127) / 128), 128, 0, g.stream>>>(r->re, r->im, fl);
+        launched();
+        if (g.timeFused) {
+            CUDA_OK(cudaEventRecord(e1, g.stream));
+            g.fusedEvents.emplace_back(e0, e1);
+        }
+        ++g.fusedLaunches;
+        g.fusedGates += grp.count;
+    }
+}
+
+void flushAll() {
+    for (QuregRec* r : liveRegisters) {
+        if (r->queue.empty()) continue;
+        Qureg q;
+        std::memset(&q, 0, sizeof q);
+        q.pairStateVec.real = reinterpret_cast<qreal*>(r);
+        q.numAmpsPerChunk = r->n;
+        q.chunkId = g.rank;
+        q.numChunks = g.world;
+        flush(q);
+    }
+}
+
+// the register's record with no gate pending: every entry point that reads or overwrites amplitudes uses this
+inline QuregRec* live(const Qureg& q) {
+    flush(q);
+    return rec(q);
+}
+
+// Entry for every gate of the API.  Controls on shard-selecting qubits are resolved here (QuEST_cpu.c:1841,2694):
+// this rank either drops them or has nothing to do.
+void submit(const Qureg& q, PendingOp op) {
+    QuregRec* r = rec(q);
+    if (!qb::localiseControls(r->localBits, q.chunkId, op.mask)) return;
+    const bool cross = !isDiagonal(op.kind) && op.target >= r->localBits;
+    if (cross) {
+        flush(q);
+        runOpNow(q, op);
+        return;
+    }
+    if (g.fuse && r->localBits >= kFuseBits) {
+        r->queue.push_back(op);
+        if (r->queue.size() >= kQueueCap) flush(q);
+        return;
+    }
+    runOpNow(q, op);
+}
+
+PendingOp denseOp(int kind, int target, u64 ctrlMask) {
+    PendingOp op;
+    std::memset(&op, 0, sizeof op);
+    op.kind = kind;
+    op.target = target;
+    op.mask = ctrlMask;
+    return op;
+}
+
+PendingOp matrixOp(int target, u64 ctrlMask, ComplexMatrix2 u) {
+    PendingOp op = denseOp(kFMatrix, target, ctrlMask);
+    const qreal c[8] = {u.r0c0.real, u.r0c0.imag, u.r0c1.real, u.r0c1.imag, u.r1c0.real, u.r1c0.imag, u.r1c1.real, u.r1c1.imag};
+    std::memcpy(op.c, c, sizeof c);
+    return op;
+}
+
+// [[alpha, -conj(beta)], [beta, conj(alpha)]] as a general matrix.  Evaluated by OpMatrix this gives the same IEEE
+// bits as the reference's compact expressions (QuEST_cpu.c:1614-1623): x + (-b)*y == x - b*y and x - (-a)*y == x + a*y.
+PendingOp compactOp(int target, u64 ctrlMask, Complex a, Complex b) {
+    PendingOp op = denseOp(kFMatrix, target, ctrlMask);
+    const qreal c[8] = {a.real, a.imag, -b.real, b.imag, b.real, b.imag, a.real, -a.imag};
+    std::memcpy(op.c, c, sizeof c);
+    return op;
+}
+
+PendingOp phaseOp(u64 mask, qreal c, qreal s) {
+    PendingOp op = denseOp(kFPhase, -1, mask);
+    op.c[0] = c;
+    op.c[1] = s;
+    return op;
+}
 
 // ---- reductions --------------------------------------------------------------------------------------------
 
@@ -204,7 +350,7 @@ void fetchResult(int nv, double* out) {
 void zeroResult(int nv) { CUDA_OK(cudaMemsetAsync(g.dResult, 0, nv * sizeof(double), g.stream)); }
 
 void fillShard(const Qureg& q, qreal vr, qreal vi) {
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const int vec = pickVec(r->n);
     const u64 nVec = (u64)r->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -215,7 +361,7 @@ void fillShard(const Qureg& q, qreal vr, qreal vi) {
 
 // set the amplitude with GLOBAL index gi, if this shard owns it
 void setOneGlobal(const Qureg& q, idx_t gi, qreal vr, qreal vi) {
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const idx_t off = (idx_t)q.chunkId * r->n;
     if (gi < off || gi >= off + r->n) return;
     k_setOne<<<1, 1, 0, g.stream>>>(r->re, r->im, (u64)(gi - off), vr, vi);
@@ -225,7 +371,7 @@ void setOneGlobal(const Qureg& q, idx_t gi, qreal vr, qreal vi) {
 // ---- helpers shared by several entry points ------------------------------------------------------------
 
 qreal readOne(const Qureg& q, idx_t index, bool imag) {
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const int owner = (int)(index / r->n);
     qreal v = 0;
     if (owner == q.chunkId) {
@@ -238,7 +384,7 @@ qreal readOne(const Qureg& q, idx_t index, bool imag) {
 }
 
 double sumSquares(const Qureg& q) {
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const int vec = pickVec(r->n);
     const u64 nVec = (u64)r->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -252,7 +398,7 @@ double sumSquares(const Qureg& q) {
 }
 
 double probOfZero(const Qureg& q, int t) {
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     if (t >= r->localBits) {
         // the measured qubit selects the shard: shards with the bit set contribute 0, the others everything
         // (QuEST_cpu_distributed.c:1227-1247)
@@ -277,7 +423,7 @@ double probOfZero(const Qureg& q, int t) {
 }
 
 double densDiagSum(const Qureg& q, int bit) {
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const u64 dim = 1ull << q.numQubitsRepresented;
     k_densDiagSum<<<reduceBlocks(dim), kBlock, 0, g.stream>>>(r->re, dim, bit, (u64)q.chunkId * r->n, (u64)r->n,
                                                              g.dPartials, g.dTicket, g.dResult);
@@ -290,7 +436,7 @@ double densDiagSum(const Qureg& q, int bit) {
 template <int KIND>
 void launchNoise1(const Qureg& q, int t, qreal p0, qreal p1, qreal p2) {
     if (g.world > 1) comm::unsupported("one-qubit noise on a sharded density matrix");
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const int n = q.numQubitsRepresented;
     const int vec = pickVec(r->n, 1LL << n);
     const int v = log2i(vec);
@@ -343,6 +489,8 @@ QuESTEnv createQuESTEnv(void) {
     CUDA_OK(cudaMemset(g.dTicket, 0, sizeof(unsigned int)));
     CUDA_OK(cudaMalloc(&g.dResult, 4 * sizeof(double)));
     CUDA_OK(cudaHostAlloc(&g.hResult, 4 * sizeof(double), cudaHostAllocDefault));
+    if (const char* s = std::getenv("QUEST_B200_FUSE")) g.fuse = std::atoi(s) != 0;
+    if (const char* s = std::getenv("QUEST_B200_FUSE_BLOCK")) g.fuseBlock = std::atoi(s);
     if (const char* s = std::getenv("QUEST_B200_VEC")) {
         int v = std::atoi(s);
         if (v == 1 || v == 2 || v == 4) g.vecCap = v;
@@ -363,6 +511,7 @@ void destroyQuESTEnv(QuESTEnv env) {
         std::printf("ERROR: Trying to close QuESTEnv multiple times. Ignoring\n");
         return;
     }
+    flushAll();
     CUDA_OK(cudaStreamSynchronize(g.stream));
     if (g.world > 1) comm::shutdown();
     cudaFree(g.dPartials);
@@ -376,6 +525,7 @@ void destroyQuESTEnv(QuESTEnv env) {
 void syncQuESTEnv(QuESTEnv env) {
     (void)env;
     requireEngine();
+    flushAll();
     CUDA_OK(cudaStreamSynchronize(g.stream));
     if (g.world > 1) comm::hostBarrier();
 }
@@ -445,6 +595,7 @@ void statevec_createQureg(Qureg* qureg, int numQubits, QuESTEnv env) {
     qureg->deviceStateVec.imag = r->im;
     qureg->pairStateVec.real = reinterpret_cast<qreal*>(r);
     qureg->firstLevelReduction = reinterpret_cast<qreal*>(g.dPartials);
+    liveRegisters.push_back(r);
     if (g.world > 1) comm::registerShard(*qureg, r->re, r->im, per);
 }
 
@@ -452,6 +603,8 @@ void statevec_destroyQureg(Qureg qureg, QuESTEnv env) {
     (void)env;
     QuregRec* r = rec(qureg);
     if (!r) return;
+    r->queue.clear();  // gates never observed need not run
+    liveRegisters.erase(std::remove(liveRegisters.begin(), liveRegisters.end(), r), liveRegisters.end());
     CUDA_OK(cudaStreamSynchronize(g.stream));
     if (g.world > 1) comm::unregisterShard(qureg);
     CUDA_OK(cudaFree(r->re));
@@ -461,7 +614,7 @@ void statevec_destroyQureg(Qureg qureg, QuESTEnv env) {
 
 // host -> device slice copy; complete on return, as in the reference (QuEST_gpu.cu:34-49)
 void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, idx_t numAmps) {
-    QuregRec* r = rec(qureg);
+    QuregRec* r = live(qureg);
     const idx_t off = (idx_t)qureg.chunkId * r->n;
     idx_t lo = std::max<idx_t>(startInd - off, 0), hi = std::min<idx_t>(startInd - off + numAmps, r->n);
     if (hi > lo) {
@@ -473,14 +626,14 @@ void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, i
 }
 
 void qb200_copyAmpsToHost(Qureg qureg, idx_t start, idx_t n, qreal* reals, qreal* imags) {
-    QuregRec* r = rec(qureg);
+    QuregRec* r = live(qureg);
     CUDA_OK(cudaMemcpyAsync(reals, r->re + start, n * sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
     CUDA_OK(cudaMemcpyAsync(imags, r->im + start, n * sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
     CUDA_OK(cudaStreamSynchronize(g.stream));
 }
 
 void statevec_cloneQureg(Qureg dst, Qureg src) {
-    QuregRec *d = rec(dst), *s = rec(src);
+    QuregRec *d = live(dst), *s = live(src);
     CUDA_OK(cudaMemcpyAsync(d->re, s->re, d->n * sizeof(qreal), cudaMemcpyDeviceToDevice, g.stream));
     CUDA_OK(cudaMemcpyAsync(d->im, s->im, d->n * sizeof(qreal), cudaMemcpyDeviceToDevice, g.stream));
 }
@@ -490,7 +643,7 @@ qreal statevec_getRealAmp(Qureg qureg, idx_t index) { return readOne(qureg, inde
 qreal statevec_getImagAmp(Qureg qureg, idx_t index) { return readOne(qureg, index, true); }
 
 int statevec_compareStates(Qureg a, Qureg b, qreal precision) {
-    QuregRec *ra = rec(a), *rb = rec(b);
+    QuregRec *ra = live(a), *rb = live(b);
     const int vec = pickVec(ra->n);
     const u64 nVec = (u64)ra->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -508,6 +661,7 @@ int statevec_compareStates(Qureg a, Qureg b, qreal precision) {
 // ---------------------------------------------------------------------------------------------------------
 
 void statevec_initZeroState(Qureg q) {
+    rec(q)->queue.clear();  // the whole state is overwritten: pending gates can be dropped
     QuregRec* r = rec(q);
     CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
     CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
@@ -515,11 +669,13 @@ void statevec_initZeroState(Qureg q) {
 }
 
 void statevec_initPlusState(Qureg q) {
+    rec(q)->queue.clear();
     const idx_t total = q.numAmpsPerChunk * q.numChunks;
-    fillShard(q, 1.0 / sqrt((qreal)total), 0);
+    fillShard(q, 1.0 / sqrt((double)(qreal)total), 0);
 }
 
 void statevec_initClassicalState(Qureg q, idx_t stateInd) {
+    rec(q)->queue.clear();
     QuregRec* r = rec(q);
     CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
     CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
@@ -527,13 +683,14 @@ void statevec_initClassicalState(Qureg q, idx_t stateInd) {
 }
 
 void statevec_initStateDebug(Qureg q) {
+    rec(q)->queue.clear();
     QuregRec* r = rec(q);
     k_initDebug<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n);
     launched();
 }
 
 void statevec_initStateOfSingleQubit(Qureg* q, int qubitId, int outcome) {
-    QuregRec* r = rec(*q);
+    QuregRec* r = live(*q);
     const idx_t total = q->numAmpsPerChunk * q->numChunks;
     const qreal norm = 1.0 / sqrt((qreal)total / 2.0);
     k_initSingleQubit<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q->chunkId * r->n,
@@ -542,12 +699,13 @@ void statevec_initStateOfSingleQubit(Qureg* q, int qubitId, int outcome) {
 }
 
 void densmatr_initPlusState(Qureg q) {
+    rec(q)->queue.clear();
     const idx_t dim = 1LL << q.numQubitsRepresented;
     fillShard(q, 1.0 / ((qreal)dim), 0);
 }
 
 void densmatr_initClassicalState(Qureg q, idx_t stateInd) {
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const idx_t dim = 1LL << q.numQubitsRepresented;
     CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
     CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
@@ -556,7 +714,7 @@ void densmatr_initClassicalState(Qureg q, idx_t stateInd) {
 
 void densmatr_initPureState(Qureg rho, Qureg psi) {
     if (g.world > 1) comm::unsupported("initPureState on a sharded density matrix");
-    QuregRec *d = rec(rho), *p = rec(psi);
+    QuregRec *d = live(rho), *p = live(psi);
     k_outerProduct<<<blocksFor((u64)d->n), kBlock, 0, g.stream>>>(d->re, d->im, p->re, p->im, (u64)psi.numAmpsTotal,
                                                                  (u64)d->n);
     launched();
@@ -566,32 +724,41 @@ void densmatr_initPureState(Qureg rho, Qureg psi) {
 // gates                                                                  (replaces QuEST_gpu.cu:531-1330)
 // ---------------------------------------------------------------------------------------------------------
 
-void statevec_compactUnitary(Qureg q, const int t, Complex alpha, Complex beta) { launchPairs(q, t, 0, asOp(alpha, beta)); }
+void statevec_compactUnitary(Qureg q, const int t, Complex alpha, Complex beta) { submit(q, compactOp(t, 0, alpha, beta)); }
 void statevec_controlledCompactUnitary(Qureg q, const int c, const int t, Complex alpha, Complex beta) {
-    launchPairs(q, t, 1ull << c, asOp(alpha, beta));
+    submit(q, compactOp(t, 1ull << c, alpha, beta));
 }
-void statevec_unitary(Qureg q, const int t, ComplexMatrix2 u) { launchPairs(q, t, 0, asOp(u)); }
-void statevec_controlledUnitary(Qureg q, const int c, const int t, ComplexMatrix2 u) { launchPairs(q, t, 1ull << c, asOp(u)); }
+void statevec_unitary(Qureg q, const int t, ComplexMatrix2 u) { submit(q, matrixOp(t, 0, u)); }
+void statevec_controlledUnitary(Qureg q, const int c, const int t, ComplexMatrix2 u) { submit(q, matrixOp(t, 1ull << c, u)); }
 void statevec_multiControlledUnitary(Qureg q, int* ctrls, const int n, const int t, ComplexMatrix2 u) {
-    launchPairs(q, t, maskOf(ctrls, n), asOp(u));
+    submit(q, matrixOp(t, maskOf(ctrls, n), u));
 }
-void statevec_hadamard(Qureg q, const int t) { launchPairs(q, t, 0, OpHadamard{(qreal)(1.0 / sqrt(2))}); }
-void statevec_pauliX(Qureg q, const int t) { launchPairs(q, t, 0, OpSwap{}); }
-void statevec_controlledNot(Qureg q, const int c, const int t) { launchPairs(q, t, 1ull << c, OpSwap{}); }
-void statevec_pauliY(Qureg q, const int t) { launchPairs(q, t, 0, OpPauliY{1}); }
-void statevec_pauliYConj(Qureg q, const int t) { launchPairs(q, t, 0, OpPauliY{-1}); }
-void statevec_controlledPauliY(Qureg q, const int c, const int t) { launchPairs(q, t, 1ull << c, OpPauliY{1}); }
-void statevec_controlledPauliYConj(Qureg q, const int c, const int t) { launchPairs(q, t, 1ull << c, OpPauliY{-1}); }
+void statevec_hadamard(Qureg q, const int t) {
+    PendingOp op = denseOp(kFHadamard, t, 0);
+    op.c[0] = (qreal)(1.0 / sqrt(2));
+    submit(q, op);
+}
+void statevec_pauliX(Qureg q, const int t) { submit(q, denseOp(kFSwap, t, 0)); }
+void statevec_controlledNot(Qureg q, const int c, const int t) { submit(q, denseOp(kFSwap, t, 1ull << c)); }
+static void submitY(Qureg q, int t, u64 ctrl, qreal fac) {
+    PendingOp op = denseOp(kFPauliY, t, ctrl);
+    op.c[0] = fac;
+    submit(q, op);
+}
+void statevec_pauliY(Qureg q, const int t) { submitY(q, t, 0, 1); }
+void statevec_pauliYConj(Qureg q, const int t) { submitY(q, t, 0, -1); }
+void statevec_controlledPauliY(Qureg q, const int c, const int t) { submitY(q, t, 1ull << c, 1); }
+void statevec_controlledPauliYConj(Qureg q, const int c, const int t) { submitY(q, t, 1ull << c, -1); }
 
-void statevec_phaseShiftByTerm(Qureg q, const int t, Complex term) { launchDiag(q, 1ull << t, DiagPhase{term.real, term.imag}); }
+void statevec_phaseShiftByTerm(Qureg q, const int t, Complex term) { submit(q, phaseOp(1ull << t, term.real, term.imag)); }
 void statevec_controlledPhaseShift(Qureg q, const int q1, const int q2, qreal angle) {
-    launchDiag(q, (1ull << q1) | (1ull << q2), DiagPhase{(qreal)cos(angle), (qreal)sin(angle)});
+    submit(q, phaseOp((1ull << q1) | (1ull << q2), (qreal)cos((double)angle), (qreal)sin((double)angle)));
 }
 void statevec_multiControlledPhaseShift(Qureg q, int* ctrls, int n, qreal angle) {
-    launchDiag(q, maskOf(ctrls, n), DiagPhase{(qreal)cos(angle), (qreal)sin(angle)});
+    submit(q, phaseOp(maskOf(ctrls, n), (qreal)cos((double)angle), (qreal)sin((double)angle)));
 }
-void statevec_controlledPhaseFlip(Qureg q, const int q1, const int q2) { launchDiag(q, (1ull << q1) | (1ull << q2), DiagFlip{}); }
-void statevec_multiControlledPhaseFlip(Qureg q, int* ctrls, int n) { launchDiag(q, maskOf(ctrls, n), DiagFlip{}); }
+void statevec_controlledPhaseFlip(Qureg q, const int q1, const int q2) { submit(q, denseOp(kFFlip, -1, (1ull << q1) | (1ull << q2))); }
+void statevec_multiControlledPhaseFlip(Qureg q, int* ctrls, int n) { submit(q, denseOp(kFFlip, -1, maskOf(ctrls, n))); }
 
 // ---------------------------------------------------------------------------------------------------------
 // reductions                                                             (replaces QuEST_gpu.cu:1111-1164,1335-1840)
@@ -611,7 +778,7 @@ qreal statevec_calcProbOfOutcome(Qureg q, const int t, int outcome) {
 }
 
 Complex statevec_calcInnerProduct(Qureg bra, Qureg ket) {
-    QuregRec *b = rec(bra), *k = rec(ket);
+    QuregRec *b = live(bra), *k = live(ket);
     const int vec = pickVec(b->n);
     const u64 nVec = (u64)b->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -638,7 +805,7 @@ qreal densmatr_calcProbOfOutcome(Qureg q, const int t, int outcome) {
 
 qreal densmatr_calcFidelity(Qureg rho, Qureg psi) {
     if (g.world > 1) comm::unsupported("calcFidelity on a sharded density matrix");
-    QuregRec *d = rec(rho), *p = rec(psi);
+    QuregRec *d = live(rho), *p = live(psi);
     const u64 dim = (u64)psi.numAmpsTotal;
     k_densFidelity<<<reduceBlocks(dim), kBlock, 0, g.stream>>>(d->re, d->im, p->re, p->im, dim, g.dPartials, g.dTicket,
                                                               g.dResult);
@@ -653,8 +820,8 @@ qreal densmatr_calcFidelity(Qureg rho, Qureg psi) {
 // ---------------------------------------------------------------------------------------------------------
 
 void statevec_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qreal prob) {
-    QuregRec* r = rec(q);
-    const qreal renorm = 1 / sqrt(prob);
+    QuregRec* r = live(q);
+    const qreal renorm = 1 / sqrt((double)prob);
     const int vec = pickVec(r->n);
     if (t >= r->localBits) {
         // whole shard is either kept (renormalised) or cleared (QuEST_cpu_distributed.c:1274-1292)
@@ -682,7 +849,7 @@ void statevec_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qrea
 
 void densmatr_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qreal prob) {
     if (g.world > 1) comm::unsupported("collapse of a sharded density matrix");
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const int n = q.numQubitsRepresented;
     const int vec = pickVec(r->n, 1LL << n);
     const int v = log2i(vec);
@@ -713,12 +880,12 @@ void densmatr_oneQubitDepolarise(Qureg q, const int t, qreal level) {
 void densmatr_oneQubitDamping(Qureg q, const int t, qreal damping) {
     if (damping == 0) return;
     const qreal retain = 1 - damping;
-    const qreal dephase = sqrt(retain);
+    const qreal dephase = sqrt((double)retain);
     launchNoise1<kDamping>(q, t, dephase, damping, retain);
 }
 
 void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase) {
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const int n = q.numQubitsRepresented;
     const qreal retain = 1 - dephase;
     k_dephase2<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n, 1ull << q1,
@@ -729,11 +896,11 @@ void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase
 void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
     if (level == 0) return;
     if (g.world > 1) comm::unsupported("two-qubit depolarising on a sharded density matrix");
-    QuregRec* r = rec(q);
+    QuregRec* r = live(q);
     const int n = q.numQubitsRepresented;
     // host scalars exactly as QuEST_cpu_local.c:43-48
     qreal eta = 2 / level;
-    qreal delta = eta - 1 - sqrt((eta - 1) * (eta - 1) - 1);
+    qreal delta = eta - 1 - sqrt((double)((eta - 1) * (eta - 1) - 1));
     qreal gamma = 1 + delta;
     gamma = 1 / (gamma * gamma * gamma);
     densmatr_twoQubitDephase(q, q1, q2, level);
@@ -748,7 +915,7 @@ void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
 }
 
 void densmatr_addDensityMatrix(Qureg a, qreal p, Qureg b) {
-    QuregRec *ra = rec(a), *rb = rec(b);
+    QuregRec *ra = live(a), *rb = live(b);
     const int vec = pickVec(ra->n);
     const u64 nVec = (u64)ra->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -765,6 +932,7 @@ void* qb200_getStream(void) { return (void*)g.stream; }
 
 void qb200_setStream(void* stream) {
     requireEngine();
+    flushAll();
     CUDA_OK(cudaStreamSynchronize(g.stream));
     if (g.ownsStream) cudaStreamDestroy(g.stream);
     g.stream = (cudaStream_t)stream;
@@ -773,10 +941,44 @@ void qb200_setStream(void* stream) {
 
 unsigned long long qb200_getLaunchCount(void) { return g.launches; }
 
+void qb200_setFusion(int enabled) {
+    flushAll();
+    g.fuse = enabled != 0;
+}
+
+int qb200_getFusion(void) { return g.fuse ? 1 : 0; }
+
+void qb200_flush(void) { flushAll(); }
+
+void qb200_setKernelTiming(int enabled) {
+    g.timeFused = enabled != 0;
+}
+
+// total device time (ms) and count of the fused launches recorded since timing was enabled; clears the record
+void qb200_getFusedKernelTime(double* totalMs, unsigned long long* launches) {
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+    double sum = 0;
+    for (auto& ev : g.fusedEvents) {
+        float ms = 0;
+        CUDA_OK(cudaEventElapsedTime(&ms, ev.first, ev.second));
+        sum += ms;
+        cudaEventDestroy(ev.first);
+        cudaEventDestroy(ev.second);
+    }
+    *totalMs = sum;
+    *launches = g.fusedEvents.size();
+    g.fusedEvents.clear();
+}
+
+void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long* fusedGates) {
+    *fusedLaunches = g.fusedLaunches;
+    *fusedGates = g.fusedGates;
+}
+
 int qb200_getDevice(void) { return g.device; }
 
 void qb200_getDevicePointers(Qureg qureg, void** real, void** imag) {
-    QuregRec* r = rec(qureg);
+    QuregRec* r = live(qureg);
     *real = r->re;
     *imag = r->im;
 }
@@ -793,6 +995,33 @@ void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long l
     for (int i = 0; i < kMaxInsert; ++i) out[8 + i] = sg.planned.plan.pos[i];
     out[16] = sg.planned.plan.skipMask;
     out[17] = sg.ctrlMask;
+}
+
+// Host grouping logic of the fusion queue, exposed for CPU-only tests (no CUDA call): groups the given gate list
+// exactly as flush() would for a shard of 2^localBits amplitudes.  groupsOut: 7 ints per group (first, count,
+// bits[4], nDenseBits); descOut: 4 words per gate (kind, pos, regMask, outerMask).  Returns the number of groups.
+int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* targets, const unsigned long long* masks,
+                    int* groupsOut, unsigned long long* descOut) {
+    std::vector<PendingOp> ops(nOps);
+    for (int i = 0; i < nOps; ++i) {
+        std::memset(&ops[i], 0, sizeof(PendingOp));
+        ops[i].kind = kinds[i];
+        ops[i].target = targets[i];
+        ops[i].mask = masks[i];
+    }
+    const std::vector<FusedGroup> groups = groupOps(ops, localBits);
+    for (size_t gi = 0; gi < groups.size(); ++gi) {
+        const FusedGroup& grp = groups[gi];
+        int* o = groupsOut + 7 * gi;
+        o[0] = grp.first; o[1] = grp.count; o[6] = grp.nDenseBits;
+        for (int j = 0; j < kFuseBits; ++j) o[2 + j] = grp.bits[j];
+        for (int i = 0; i < grp.count; ++i) {
+            const FusedGate fg = describe(ops[grp.first + i], grp.bits);
+            unsigned long long* d = descOut + 4 * (grp.first + i);
+            d[0] = fg.kind; d[1] = fg.pos; d[2] = fg.regMask; d[3] = fg.outerMask;
+        }
+    }
+    return (int)groups.size();
 }
 
 }  // extern "C"

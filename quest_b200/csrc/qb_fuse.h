@@ -1,0 +1,122 @@
+// quest-b200 gate fusion: host-side queue and grouping (CUDA-free, unit-tested on CPU through qb200_debugFuse).
+//
+// Every gate of the QuEST API is one pass over HBM (16 GiB read + 16 GiB written at 30 qubits) however little
+// arithmetic it does.  The API lets a gate call return before the GPU has run it (the reference GPU backend
+// launches asynchronously, QuEST_gpu.cu:591), so gate calls are recorded in a per-register queue and executed at
+// the next call that needs the amplitudes (any value-returning call, a copy, syncQuESTEnv, a shard-crossing gate).
+// At that point consecutive gates are grouped: a group is a run of gates, in program order, whose dense (non-
+// diagonal) targets fall on at most kFuseBits distinct qubits; diagonal gates and control qubits are unrestricted.
+// One launch of k_fused then loads 2^kFuseBits amplitudes per thread - the sub-block spanned by those qubits -
+// applies the whole run in registers, gate after gate in the original order with the original per-gate
+// arithmetic, and writes the block back: one HBM pass for the whole group, bit-identical results.
+#pragma once
+
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "QuEST_precision.h"
+
+namespace qb {
+
+constexpr int kFuseBits = 4;       // qubits resolved in registers per launch (16 amplitudes per thread)
+constexpr int kMaxFusedGates = 96;  // gates per launch: descriptors travel as kernel parameters (constant bank)
+
+enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, kFPhase = 4, kFFlip = 5 };
+
+inline bool isDiagonal(int kind) { return kind == kFPhase || kind == kFFlip; }
+
+// A recorded gate: target and control mask are LOCAL bit positions of this rank's shard (controls on
+// shard-selecting qubits were already resolved when the gate was recorded).
+struct PendingOp {
+    int kind;
+    int target;                    // dense kinds only
+    unsigned long long mask;       // dense: control mask; diagonal: all selecting bits
+    qreal c[8];                    // Matrix: r00,i00,r01,i01,r10,i10,r11,i11; Hadamard: c[0]=1/sqrt2;
+                                   // PauliY: c[0]=+-1; Phase: c[0]=cos, c[1]=sin
+};
+
+// What the kernel reads per gate.
+struct FusedGate {
+    int kind;
+    int pos;                       // dense: which of the kFuseBits register bits is the target
+    unsigned int regMask;          // control/selecting bits that are register bits (bit j = j-th fused qubit)
+    unsigned int pad;
+    unsigned long long outerMask;  // control/selecting bits outside the fused qubits (amplitude-index space)
+    qreal c[8];
+};
+
+struct FusedGroup {
+    int first, count;              // ops [first, first+count) of the queue
+    int bits[kFuseBits];           // fused qubits, ascending; padded with unused qubits when the group needs fewer
+    int nDenseBits;                // how many of them are targets of dense gates
+};
+
+// Greedy, order-preserving grouping.
+inline std::vector<FusedGroup> groupOps(const std::vector<PendingOp>& ops, int localBits) {
+    std::vector<FusedGroup> out;
+    const int n = (int)ops.size();
+    int i = 0;
+    while (i < n) {
+        FusedGroup g;
+        g.first = i;
+        g.count = 0;
+        g.nDenseBits = 0;
+        unsigned long long chosen = 0;
+        while (i < n && g.count < kMaxFusedGates) {
+            const PendingOp& op = ops[i];
+            if (!isDiagonal(op.kind) && !((chosen >> op.target) & 1)) {
+                if (g.nDenseBits == kFuseBits) break;
+                chosen |= 1ull << op.target;
+                ++g.nDenseBits;
+            }
+            ++g.count;
+            ++i;
+        }
+        // pad with qubits the group's gates mention (keeps their predicates in registers), then with the
+        // highest unused qubits (keeps the remaining index bits low => consecutive threads, consecutive amplitudes)
+        int have = g.nDenseBits;
+        for (int k = g.first; k < g.first + g.count && have < kFuseBits; ++k) {
+            unsigned long long m = ops[k].mask & ~chosen;
+            while (m && have < kFuseBits) {
+                const int b = __builtin_ctzll(m);
+                m &= m - 1;
+                if (b < localBits) {
+                    chosen |= 1ull << b;
+                    ++have;
+                }
+            }
+        }
+        for (int b = localBits - 1; b >= 0 && have < kFuseBits; --b)
+            if (!((chosen >> b) & 1)) {
+                chosen |= 1ull << b;
+                ++have;
+            }
+        int j = 0;
+        for (int b = 0; b < 64 && j < kFuseBits; ++b)
+            if ((chosen >> b) & 1) g.bits[j++] = b;
+        out.push_back(g);
+    }
+    return out;
+}
+
+// Translate one queued op into the kernel's descriptor for a group with fused qubits `bits`.
+inline FusedGate describe(const PendingOp& op, const int* bits) {
+    FusedGate fg;
+    std::memset(&fg, 0, sizeof fg);
+    fg.kind = op.kind;
+    fg.pos = 0;
+    unsigned long long outer = op.mask;
+    for (int j = 0; j < kFuseBits; ++j) {
+        if (!isDiagonal(op.kind) && bits[j] == op.target) fg.pos = j;
+        if ((op.mask >> bits[j]) & 1) {
+            fg.regMask |= 1u << j;
+            outer &= ~(1ull << bits[j]);
+        }
+    }
+    fg.outerMask = outer;
+    for (int k = 0; k < 8; ++k) fg.c[k] = op.c[k];
+    return fg;
+}
+
+}  // namespace qb

@@ -12,6 +12,7 @@
 #pragma once
 
 #include "qb_device.cuh"
+#include "qb_fuse.h"
 
 namespace qb {
 
@@ -166,6 +167,209 @@ __global__ void __launch_bounds__(kBlock) k_diag(qreal* __restrict__ re, qreal* 
         if ((e & plan.loMask) == plan.loMask) op(R.v[e], I.v[e]);
     store<VEC>(re + i, R);
     store<VEC>(im + i, I);
+}
+
+// ======================================================================================================
+// fused multi-gate pass (qb_fuse.h): each thread owns the 2^R amplitudes spanned by the R fused qubits, keeps them
+// in registers, and runs the recorded gates over them in program order.  Dense gates use exactly the per-pair
+// arithmetic of the single-gate kernels (OpMatrix also serves compactUnitary: with r01=-bR, i01=bI, r10=bR,
+// i10=bI, r11=aR, i11=-aI its expression tree evaluates to the same IEEE bits as OpCompact).
+// ======================================================================================================
+
+struct FusedLaunch {
+    int pos[kFuseBits];                  // fused qubits, ascending (amplitude-index bit positions)
+    int nGates;
+    unsigned long long nThreads;
+    FusedGate gates[kMaxFusedGates];     // the recorded gates, read through the constant bank (kernel parameter)
+};
+
+template <int P, int R, class PairFn>
+__device__ __forceinline__ void forEachPair(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e) {
+        if ((e >> P) & 1) continue;
+        if ((e & regMask) == regMask) fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
+    }
+}
+
+// no control among the fused qubits: straight-line arithmetic on all pairs (no per-pair select)
+template <int P, int R, class PairFn>
+__device__ __forceinline__ void forEveryPair(qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e) {
+        if ((e >> P) & 1) continue;
+        fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
+    }
+}
+
+template <int R, class PairFn>
+__device__ __forceinline__ void onTargetBitUnmasked(int pos, qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
+    switch (pos) {
+        case 0: forEveryPair<0, R>(xr, xi, fn); break;
+        case 1: forEveryPair<1, R>(xr, xi, fn); break;
+        case 2: forEveryPair<2, R>(xr, xi, fn); break;
+        default: forEveryPair<3, R>(xr, xi, fn); break;
+    }
+}
+
+template <int R, class PairFn>
+__device__ __forceinline__ void onTargetBit(int pos, qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
+    switch (pos) {
+        case 0: forEachPair<0, R>(xr, xi, regMask, fn); break;
+        case 1: forEachPair<1, R>(xr, xi, regMask, fn); break;
+        case 2: forEachPair<2, R>(xr, xi, regMask, fn); break;
+        default: forEachPair<3, R>(xr, xi, regMask, fn); break;
+    }
+}
+
+// Diagonal gates touch only the register elements whose fused-qubit bits contain MASK.  MASK is a compile-time
+// constant here (the caller switches on the 16 possible values), so exactly the selected elements are computed.
+template <int MASK, int R, class ElemFn>
+__device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 << R], ElemFn fn) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e)
+        if ((e & MASK) == MASK) fn(xr[e], xi[e]);
+}
+
+template <int R, class ElemFn>
+__device__ __forceinline__ void onSelected(unsigned int regMask, qreal (&xr)[1 << R], qreal (&xi)[1 << R], ElemFn fn) {
+    switch (regMask & 15u) {
+        case 0: forSelected<0, R>(xr, xi, fn); break;
+        case 1: forSelected<1, R>(xr, xi, fn); break;
+        case 2: forSelected<2, R>(xr, xi, fn); break;
+        case 3: forSelected<3, R>(xr, xi, fn); break;
+        case 4: forSelected<4, R>(xr, xi, fn); break;
+        case 5: forSelected<5, R>(xr, xi, fn); break;
+        case 6: forSelected<6, R>(xr, xi, fn); break;
+        case 7: forSelected<7, R>(xr, xi, fn); break;
+        case 8: forSelected<8, R>(xr, xi, fn); break;
+        case 9: forSelected<9, R>(xr, xi, fn); break;
+        case 10: forSelected<10, R>(xr, xi, fn); break;
+        case 11: forSelected<11, R>(xr, xi, fn); break;
+        case 12: forSelected<12, R>(xr, xi, fn); break;
+        case 13: forSelected<13, R>(xr, xi, fn); break;
+        case 14: forSelected<14, R>(xr, xi, fn); break;
+        default: forSelected<15, R>(xr, xi, fn); break;
+    }
+}
+
+template <int R, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, qreal* __restrict__ im,
+                                                const __grid_constant__ FusedLaunch fl) {
+    static_assert(R == kFuseBits && R == 4, "k_fused is written for 4 fused qubits");
+    constexpr int E = 1 << R;
+    unsigned long long k = (unsigned long long)blockIdx.x * BLOCK + threadIdx.x;
+    if (k >= fl.nThreads) return;
+    // outer index: this thread's amplitude index with the fused qubits at 0
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+        const int b = fl.pos[j];
+        const unsigned long long low = k & ((1ull << b) - 1ull);
+        k = ((k >> b) << (b + 1)) | low;
+    }
+    const unsigned long long base = k;
+    unsigned long long off[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+        unsigned long long o = 0;
+#pragma unroll
+        for (int j = 0; j < R; ++j)
+            if ((e >> j) & 1) o += 1ull << fl.pos[j];
+        off[e] = o;
+    }
+    // Register index bit j <-> fused qubit pos[j].  When the lowest fused qubits are qubit 0 (and 1), neighbouring
+    // register elements are neighbours in memory: move them as 16- or 32-byte vectors so that a warp request
+    // touches each 128-byte line once per 32 B instead of once per 8 B.
+    const int lowRun = (fl.pos[0] == 0) ? ((fl.pos[1] == 1) ? 4 : 2) : 1;
+    qreal xr[E], xi[E];
+    if (lowRun == 4) {
+#pragma unroll
+        for (int e = 0; e < E; e += 4) {
+            const Vec<qreal, 4> a = load<4>(re + base + off[e]), b = load<4>(im + base + off[e]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                xr[e + j] = a.v[j];
+                xi[e + j] = b.v[j];
+            }
+        }
+    } else if (lowRun == 2) {
+#pragma unroll
+        for (int e = 0; e < E; e += 2) {
+            const Vec<qreal, 2> a = load<2>(re + base + off[e]), b = load<2>(im + base + off[e]);
+            xr[e] = a.v[0]; xr[e + 1] = a.v[1];
+            xi[e] = b.v[0]; xi[e + 1] = b.v[1];
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            xr[e] = load<1>(re + base + off[e]).v[0];
+            xi[e] = load<1>(im + base + off[e]).v[0];
+        }
+    }
+    for (int g = 0; g < fl.nGates; ++g) {
+        const FusedGate& G = fl.gates[g];
+        if ((base & G.outerMask) != G.outerMask) continue;
+        switch (G.kind) {
+            case kFMatrix: {
+                const OpMatrix op{G.c[0], G.c[1], G.c[2], G.c[3], G.c[4], G.c[5], G.c[6], G.c[7]};
+                if (G.regMask == 0)
+                    onTargetBitUnmasked<R>(G.pos, xr, xi, op);
+                else
+                    onTargetBit<R>(G.pos, xr, xi, G.regMask, op);
+                break;
+            }
+            case kFHadamard: {  // the API has no controlled hadamard: never masked
+                const OpHadamard op{G.c[0]};
+                onTargetBitUnmasked<R>(G.pos, xr, xi, op);
+                break;
+            }
+            case kFSwap:
+                onTargetBit<R>(G.pos, xr, xi, G.regMask, OpSwap{});
+                break;
+            case kFPauliY: {
+                const OpPauliY op{G.c[0]};
+                onTargetBit<R>(G.pos, xr, xi, G.regMask, op);
+                break;
+            }
+            case kFPhase:
+                onSelected<R>(G.regMask, xr, xi, DiagPhase{G.c[0], G.c[1]});
+                break;
+            default:  // kFFlip
+                onSelected<R>(G.regMask, xr, xi, DiagFlip{});
+                break;
+        }
+    }
+    if (lowRun == 4) {
+#pragma unroll
+        for (int e = 0; e < E; e += 4) {
+            Vec<qreal, 4> a, b;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                a.v[j] = xr[e + j];
+                b.v[j] = xi[e + j];
+            }
+            store<4>(re + base + off[e], a);
+            store<4>(im + base + off[e], b);
+        }
+    } else if (lowRun == 2) {
+#pragma unroll
+        for (int e = 0; e < E; e += 2) {
+            Vec<qreal, 2> a, b;
+            a.v[0] = xr[e]; a.v[1] = xr[e + 1];
+            b.v[0] = xi[e]; b.v[1] = xi[e + 1];
+            store<2>(re + base + off[e], a);
+            store<2>(im + base + off[e], b);
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            Vec<qreal, 1> a, b;
+            a.v[0] = xr[e];
+            b.v[0] = xi[e];
+            store<1>(re + base + off[e], a);
+            store<1>(im + base + off[e], b);
+        }
+    }
 }
 
 // ======================================================================================================

@@ -4,7 +4,8 @@
 // (QuEST/src/QuEST_common.c): turning rotations into (alpha, beta) pairs, turning Z-family gates into one
 // phase term, and the measurement decision.  All trigonometry is done here with the host libm in double,
 // exactly where the reference does it (QuEST_common.c:62-69,195-235), so that the device only ever sees
-// finished coefficients and CPU/GPU results can be compared bit for bit.
+// finished coefficients and CPU/GPU results can be compared bit for bit.  libm is always called on doubles (explicit
+// casts): the reference is C99, where cos(float) means cos((double)x), and some C++ tool-chains add float overloads.
 #include <sys/time.h>
 #include <unistd.h>
 
@@ -73,20 +74,20 @@ void getComplexPairFromRotation(qreal angle, Vector axis, Complex* alpha, Comple
 // U(alpha, beta) = Rz(rz2) Ry(ry) Rz(rz1); used only for the QASM log (QuEST_common.c:72-81)
 void getZYZRotAnglesFromComplexPair(Complex alpha, Complex beta, qreal* rz2, qreal* ry, qreal* rz1) {
     qreal alphaMag = sqrt((double)(alpha.real * alpha.real + alpha.imag * alpha.imag));
-    *ry = 2.0 * acos(alphaMag);
-    qreal alphaPhase = atan2(alpha.imag, alpha.real);
-    qreal betaPhase = atan2(beta.imag, beta.real);
+    *ry = 2.0 * acos((double)alphaMag);
+    qreal alphaPhase = atan2((double)alpha.imag, (double)alpha.real);
+    qreal betaPhase = atan2((double)beta.imag, (double)beta.real);
     *rz2 = -alphaPhase + betaPhase;
     *rz1 = -alphaPhase - betaPhase;
 }
 
 // u = exp(i phase) U(alpha, beta); used only for the QASM log (QuEST_common.c:84-96)
 void getComplexPairAndPhaseFromUnitary(ComplexMatrix2 u, Complex* alpha, Complex* beta, qreal* globalPhase) {
-    qreal p00 = atan2(u.r0c0.imag, u.r0c0.real);
-    qreal p11 = atan2(u.r1c1.imag, u.r1c1.real);
+    qreal p00 = atan2((double)u.r0c0.imag, (double)u.r0c0.real);
+    qreal p11 = atan2((double)u.r1c1.imag, (double)u.r1c1.real);
     *globalPhase = (p00 + p11) / 2.0;
-    qreal c = cos(*globalPhase);
-    qreal s = sin(*globalPhase);
+    qreal c = cos((double)*globalPhase);
+    qreal s = sin((double)*globalPhase);
     alpha->real = u.r0c0.real * c + u.r0c0.imag * s;
     alpha->imag = u.r0c0.imag * c - u.r0c0.real * s;
     beta->real = u.r1c0.real * c + u.r1c0.imag * s;
@@ -158,7 +159,7 @@ static void phaseByTerm(Qureg q, int target, qreal re, qreal im) {
     statevec_phaseShiftByTerm(q, target, term);
 }
 
-void statevec_phaseShift(Qureg q, const int t, qreal angle) { phaseByTerm(q, t, cos(angle), sin(angle)); }
+void statevec_phaseShift(Qureg q, const int t, qreal angle) { phaseByTerm(q, t, cos((double)angle), sin((double)angle)); }
 void statevec_pauliZ(Qureg q, const int t) { phaseByTerm(q, t, -1, 0); }
 void statevec_sGate(Qureg q, const int t) { phaseByTerm(q, t, 0, 1); }
 void statevec_sGateConj(Qureg q, const int t) { phaseByTerm(q, t, 0, -1); }

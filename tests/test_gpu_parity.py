@@ -91,10 +91,16 @@ def _side_by_side(gpu, genv, cpu, cenv, nq, dens, ops, seed):
 @pytest.mark.parametrize("nq,dens,seed", [(1, False, 1), (2, False, 2), (3, False, 3), (5, False, 4), (9, False, 5),
                                           (13, False, 6), (18, False, 7), (22, False, 8), (1, True, 9), (2, True, 10),
                                           (4, True, 11), (7, True, 12), (10, True, 13), (11, True, 14)])
-def test_bit_exact_vs_oracle_measurement_free(product, product_env, oracle, oracle_env, nq, dens, seed):
-    """Every gate family, every target position (inside the vector, mid, top), 1 to 22 qubits: identical bits."""
+@pytest.mark.parametrize("fusion", [0, 1], ids=["gate_at_a_time", "fused"])
+def test_bit_exact_vs_oracle_measurement_free(product, product_env, oracle, oracle_env, nq, dens, seed, fusion):
+    """Every gate family, every target position (inside the vector, mid, top), 1 to 22 qubits: identical bits,
+    both with one kernel per gate and through the fusion queue."""
     ops = circuits.random_circuit(nq, 220, seed, density=dens, measure=False)
-    (gs, gv), (cs, cv) = _side_by_side(product, product_env, oracle, oracle_env, nq, dens, ops, seed)
+    product.lib.qb200_setFusion(fusion)
+    try:
+        (gs, gv), (cs, cv) = _side_by_side(product, product_env, oracle, oracle_env, nq, dens, ops, seed)
+    finally:
+        product.lib.qb200_setFusion(1)
     assert np.array_equal(gs.view(np.float64), cs.view(np.float64))
     np.testing.assert_allclose(gv, cv, rtol=REL, atol=1e-13)
 
@@ -130,7 +136,7 @@ def test_every_vector_width_is_bit_exact(vec, oracle, oracle_env):
         "        st.append(lib.get_state(q)); lib.destroyQureg(q, env)\n"
         "    assert np.array_equal(st[0].view(np.float64), st[1].view(np.float64)), (nq, dens)\n"
         "print('ok')\n" % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-    env = dict(os.environ, QUEST_B200_VEC=vec)
+    env = dict(os.environ, QUEST_B200_VEC=vec, QUEST_B200_FUSE="0")  # one single-gate kernel per call
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
 
@@ -142,8 +148,13 @@ def test_many_controls_overflow_the_insertion_plan(product, product_env, oracle,
            ("multiControlledPhaseShift", list(range(0, 12)), 0.37),
            ("multiControlledPhaseFlip", list(range(2, 14)))]
     ops = [("hadamard", t) for t in range(nq)] + ops
-    (gs, _), (cs, _) = _side_by_side(product, product_env, oracle, oracle_env, nq, False, ops, 5)
-    assert np.array_equal(gs.view(np.float64), cs.view(np.float64))
+    for fusion in (0, 1):
+        product.lib.qb200_setFusion(fusion)
+        try:
+            (gs, _), (cs, _) = _side_by_side(product, product_env, oracle, oracle_env, nq, False, ops, 5)
+        finally:
+            product.lib.qb200_setFusion(1)
+        assert np.array_equal(gs.view(np.float64), cs.view(np.float64))
 
 
 # ---- full-size properties (BASELINE configs are 30 qubits; the oracle cannot follow there) -------------------
@@ -182,3 +193,70 @@ def test_qft_of_basis_state_is_uniform(product, product_env):
     np.testing.assert_allclose(scal, 0.5, atol=1e-12)
     assert abs(product.calcTotalProb(q) - 1) < 1e-12
     product.destroyQureg(q, product_env)
+
+
+# ---- gate fusion (deferred queue + k_fused) ---------------------------------------------------------------------
+
+GATE_FAMILIES = circuits.DENSE_1Q + circuits.DIAG_1Q + circuits.CTRL_DENSE + circuits.CTRL_DIAG + circuits.MULTI
+
+
+def _fusion_stats(lib):
+    import ctypes
+    a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+    lib.lib.qb200_getFusionStats(ctypes.byref(a), ctypes.byref(b))
+    return a.value, b.value
+
+
+@pytest.mark.parametrize("nq,dens,seed", [(4, False, 31), (5, False, 32), (8, False, 33), (13, False, 34), (21, False, 35),
+                                          (2, True, 36), (5, True, 37), (10, True, 38)])
+def test_fused_long_gate_runs_bit_exact(product, product_env, oracle, oracle_env, nq, dens, seed):
+    """300 gates with no read-back in between: the queue forms long groups; results must equal the oracle's bits."""
+    ops = circuits.random_circuit(nq, 300, seed, density=dens, measure=False, families=GATE_FAMILIES)
+    assert product.lib.qb200_getFusion() == 1
+    before = _fusion_stats(product)
+    (gs, _), (cs, _) = _side_by_side(product, product_env, oracle, oracle_env, nq, dens, ops, seed)
+    after = _fusion_stats(product)
+    assert np.array_equal(gs.view(np.float64), cs.view(np.float64))
+    assert after[0] > before[0] and (after[1] - before[1]) > 0.8 * len([o for o in ops if o[0] in GATE_FAMILIES])
+
+
+@pytest.mark.parametrize("nq,dens,seed", [(12, False, 41), (7, True, 42)])
+def test_fusion_off_gives_the_same_bits(product, product_env, nq, dens, seed):
+    ops = circuits.random_circuit(nq, 250, seed, density=dens, measure=False)
+    states = []
+    for mode in (1, 0):
+        product.lib.qb200_setFusion(mode)
+        q = product.createDensityQureg(nq, product_env) if dens else product.createQureg(nq, product_env)
+        circuits.prepare(product, q, seed)
+        circuits.run_circuit(product, q, ops, seed=seed)
+        states.append(product.get_state(q))
+        product.destroyQureg(q, product_env)
+    product.lib.qb200_setFusion(1)
+    assert np.array_equal(states[0].view(np.float64), states[1].view(np.float64))
+
+
+def test_queue_is_drained_by_every_observer(product, product_env, oracle, oracle_env):
+    """Pending gates must be visible to clone, inner product, compare, collapse, noise, setAmps and getAmp."""
+    nq = 9
+    res = []
+    for lib, env in ((product, product_env), (oracle, oracle_env)):
+        a, b = lib.createQureg(nq, env), lib.createQureg(nq, env)
+        circuits.prepare(lib, a, 5)
+        for t in range(nq):
+            lib.hadamard(a, t); lib.rotateY(a, t, 0.1 * t); lib.controlledNot(a, t, (t + 1) % nq)
+        lib.cloneQureg(b, a)                       # must see a's pending gates
+        lib.pauliX(b, 3); lib.tGate(b, 4)
+        ip = lib.calcInnerProduct(a, b)            # must see b's pending gates
+        lib.hadamard(a, 0)
+        amp = lib.getAmp(a, 5)
+        lib.rotateX(a, 2, 0.4)
+        lib.set_state(a, np.array([0.5 + 0.25j]), start=7)   # ordered after the pending rotateX
+        lib.phaseShift(a, 1, 0.2)
+        same = lib.compareStates(a, b, 1e-3)
+        p = lib.collapseToOutcome(a, 4, 1)
+        out = [ip.real, ip.imag, amp.real, amp.imag, same, p]
+        res.append((np.array(out), lib.get_state(a), lib.get_state(b)))
+        lib.destroyQureg(a, env); lib.destroyQureg(b, env)
+    np.testing.assert_allclose(res[0][0], res[1][0], rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(res[0][1], res[1][1], rtol=0, atol=1e-13)
+    assert np.array_equal(res[0][2].view(np.float64), res[1][2].view(np.float64))
