@@ -56,6 +56,13 @@ void qb200_copyAmpsToHost(Qureg qureg, long long int start, long long int n, qre
 void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long long ctrlMask, int vec,
                          unsigned long long* out);
 
+/* Test hook (host logic only, makes no CUDA call): the qubit-slot exchanges a sharded register would perform for a
+ * sequence of dense gates, and the exchanges that restore the identity layout afterwards.  Layouts at the definition.
+ * No counterpart in the reference, which exchanges whole shards for every gate on a shard-selecting qubit
+ * (QuEST_cpu_distributed.c:451-479). */
+int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, const unsigned long long* masks,
+                     int* eventsOut, int* physOut, int* canonOut);
+
 /* Test hook (host logic only, makes no CUDA call): how the fusion queue would group a gate list for a shard of
  * 2^localBits amplitudes.  kinds: 0 matrix, 1 hadamard, 2 swap, 3 pauliY, 4 phase, 5 flip.  Layouts at the definition. */
 int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* targets, const unsigned long long* masks,

@@ -67,6 +67,8 @@ struct Engine {
     bool fuse = true;               // QUEST_B200_FUSE / qb200_setFusion: record gates and run them in fused passes
     unsigned long long fusedLaunches = 0, fusedGates = 0;
     int fuseBlock = 128;            // QUEST_B200_FUSE_BLOCK: threads per CTA of the fused kernel (128 or 256)
+    bool remap = true;              // QUEST_B200_REMAP: make shard-selecting qubits local by slot exchange
+    unsigned long long slotSwaps = 0;
     bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fusedEvents;
 } g;
@@ -77,6 +79,7 @@ struct QuregRec {
     idx_t n;       // amplitudes in this shard
     int localBits; // log2 n
     std::vector<PendingOp> queue;  // gates recorded but not yet executed (qb_fuse.h)
+    QubitMap map;                  // where each logical qubit lives (qb_plan.h); identity unless sharded
 };
 
 std::vector<QuregRec*> liveRegisters;  // for syncQuESTEnv / qb200_setFusion: every queue must be drainable
@@ -280,16 +283,82 @@ void flushAll() {
     }
 }
 
+// Exchange a shard-selecting bit position with a local one (k_swapPeer); caller has flushed the queue.
+void exchangeSlots(const Qureg& q, SlotSwap sw) {
+    QuregRec* r = rec(q);
+    const int gbit = sw.globalSlot - r->localBits, l = sw.localSlot;
+    const comm::Partner peer = comm::partnerOf(q, gbit);
+    const bool amUpper = ((q.chunkId >> gbit) & 1) == 0;
+    const int vec = pickVec(r->n, 1LL << l);  // the local slot stays above the vector
+    const int v = log2i(vec);
+    int split = -1;
+    for (int b = r->localBits - 1; b >= v; --b)
+        if (b != l) { split = b; break; }
+    comm::pairBarrier(peer.rank, g.stream);
+    if (split >= 0 || amUpper) {
+        Planned p = split >= 0 ? makePlan(r->n, vec, {l, split}, 0) : makePlan(r->n, vec, {l}, 0);
+        if (split >= 0 && !amUpper) p.plan.setMask |= 1ull << (split - v);
+        qreal* aRe = amUpper ? r->re : peer.re;
+        qreal* aIm = amUpper ? r->im : peer.im;
+        qreal* bRe = amUpper ? peer.re : r->re;
+        qreal* bIm = amUpper ? peer.im : r->im;
+        if (p.nTasks) {
+            dispatchV(vec, [&](auto V) {
+                k_swapPeer<decltype(V)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
+            });
+            launched();
+        }
+    }
+    comm::pairBarrier(peer.rank, g.stream);
+    r->map.applySwap(sw.globalSlot, sw.localSlot);
+    ++g.slotSwaps;
+}
+
 // the register's record with no gate pending: every entry point that reads or overwrites amplitudes uses this
 inline QuregRec* live(const Qureg& q) {
     flush(q);
     return rec(q);
 }
 
+// ... and with every qubit back in its own slot: entry points that address amplitudes by index range
+inline QuregRec* canon(const Qureg& q) {
+    flush(q);
+    QuregRec* r = rec(q);
+    if (!r->map.identity()) {
+        SlotSwap sw[64];
+        const int n = planCanonicalize(r->map, sw);
+        for (int i = 0; i < n; ++i) exchangeSlots(q, sw[i]);
+    }
+    return r;
+}
+
+// the state is about to be overwritten as a whole: drop pending gates and forget the layout
+inline QuregRec* fresh(const Qureg& q) {
+    QuregRec* r = rec(q);
+    r->queue.clear();
+    r->map.reset(r->map.nQubits, r->localBits);
+    return r;
+}
+
 // Entry for every gate of the API.  Controls on shard-selecting qubits are resolved here (QuEST_cpu.c:1841,2694):
 // this rank either drops them or has nothing to do.
 void submit(const Qureg& q, PendingOp op) {
     QuregRec* r = rec(q);
+    // logical qubits -> current bit positions; a dense target living in a shard-selecting slot is first made local
+    if (g.world > 1) {
+        if (!isDiagonal(op.kind)) {
+            if (g.remap && r->localBits >= 3 && r->map.phys[op.target] >= r->localBits) {
+                const SlotSwap sw = planSwapIn(r->map, op.target, op.mask);
+                if (sw.globalSlot >= 0) {
+                    flush(q);
+                    exchangeSlots(q, sw);
+                }
+            }
+            r->map.touch(op.target);
+            op.target = r->map.phys[op.target];
+        }
+        op.mask = r->map.physMask(op.mask);
+    }
     if (!qb::localiseControls(r->localBits, q.chunkId, op.mask)) return;
     const bool cross = !isDiagonal(op.kind) && op.target >= r->localBits;
     if (cross) {
@@ -350,7 +419,7 @@ void fetchResult(int nv, double* out) {
 void zeroResult(int nv) { CUDA_OK(cudaMemsetAsync(g.dResult, 0, nv * sizeof(double), g.stream)); }
 
 void fillShard(const Qureg& q, qreal vr, qreal vi) {
-    QuregRec* r = live(q);
+    QuregRec* r = rec(q);
     const int vec = pickVec(r->n);
     const u64 nVec = (u64)r->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -361,7 +430,7 @@ void fillShard(const Qureg& q, qreal vr, qreal vi) {
 
 // set the amplitude with GLOBAL index gi, if this shard owns it
 void setOneGlobal(const Qureg& q, idx_t gi, qreal vr, qreal vi) {
-    QuregRec* r = live(q);
+    QuregRec* r = rec(q);
     const idx_t off = (idx_t)q.chunkId * r->n;
     if (gi < off || gi >= off + r->n) return;
     k_setOne<<<1, 1, 0, g.stream>>>(r->re, r->im, (u64)(gi - off), vr, vi);
@@ -372,6 +441,7 @@ void setOneGlobal(const Qureg& q, idx_t gi, qreal vr, qreal vi) {
 
 qreal readOne(const Qureg& q, idx_t index, bool imag) {
     QuregRec* r = live(q);
+    index = (idx_t)r->map.physIndex((u64)index);  // where that logical amplitude currently lives
     const int owner = (int)(index / r->n);
     qreal v = 0;
     if (owner == q.chunkId) {
@@ -399,6 +469,7 @@ double sumSquares(const Qureg& q) {
 
 double probOfZero(const Qureg& q, int t) {
     QuregRec* r = live(q);
+    t = r->map.phys[t];
     if (t >= r->localBits) {
         // the measured qubit selects the shard: shards with the bit set contribute 0, the others everything
         // (QuEST_cpu_distributed.c:1227-1247)
@@ -423,7 +494,7 @@ double probOfZero(const Qureg& q, int t) {
 }
 
 double densDiagSum(const Qureg& q, int bit) {
-    QuregRec* r = live(q);
+    QuregRec* r = canon(q);
     const u64 dim = 1ull << q.numQubitsRepresented;
     k_densDiagSum<<<reduceBlocks(dim), kBlock, 0, g.stream>>>(r->re, dim, bit, (u64)q.chunkId * r->n, (u64)r->n,
                                                              g.dPartials, g.dTicket, g.dResult);
@@ -435,6 +506,7 @@ double densDiagSum(const Qureg& q, int bit) {
 
 template <int KIND>
 void launchNoise1(const Qureg& q, int t, qreal p0, qreal p1, qreal p2) {
+    canon(q);
     if (g.world > 1) comm::unsupported("one-qubit noise on a sharded density matrix");
     QuregRec* r = live(q);
     const int n = q.numQubitsRepresented;
@@ -491,6 +563,7 @@ QuESTEnv createQuESTEnv(void) {
     CUDA_OK(cudaHostAlloc(&g.hResult, 4 * sizeof(double), cudaHostAllocDefault));
     if (const char* s = std::getenv("QUEST_B200_FUSE")) g.fuse = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_FUSE_BLOCK")) g.fuseBlock = std::atoi(s);
+    if (const char* s = std::getenv("QUEST_B200_REMAP")) g.remap = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_VEC")) {
         int v = std::atoi(s);
         if (v == 1 || v == 2 || v == 4) g.vecCap = v;
@@ -575,6 +648,7 @@ void statevec_createQureg(Qureg* qureg, int numQubits, QuESTEnv env) {
     QuregRec* r = new QuregRec();
     r->n = per;
     r->localBits = log2i((u64)per);
+    r->map.reset(numQubits, r->localBits);
     // no host mirror and no pair buffer: the shard (2 * per * sizeof(qreal) bytes) is the only allocation
     cudaError_t e1 = cudaMalloc(&r->re, per * sizeof(qreal));
     cudaError_t e2 = e1 == cudaSuccess ? cudaMalloc(&r->im, per * sizeof(qreal)) : e1;
@@ -614,7 +688,7 @@ void statevec_destroyQureg(Qureg qureg, QuESTEnv env) {
 
 // host -> device slice copy; complete on return, as in the reference (QuEST_gpu.cu:34-49)
 void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, idx_t numAmps) {
-    QuregRec* r = live(qureg);
+    QuregRec* r = (startInd == 0 && numAmps == qureg.numAmpsTotal) ? fresh(qureg) : canon(qureg);
     const idx_t off = (idx_t)qureg.chunkId * r->n;
     idx_t lo = std::max<idx_t>(startInd - off, 0), hi = std::min<idx_t>(startInd - off + numAmps, r->n);
     if (hi > lo) {
@@ -626,14 +700,15 @@ void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, i
 }
 
 void qb200_copyAmpsToHost(Qureg qureg, idx_t start, idx_t n, qreal* reals, qreal* imags) {
-    QuregRec* r = live(qureg);
+    QuregRec* r = canon(qureg);
     CUDA_OK(cudaMemcpyAsync(reals, r->re + start, n * sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
     CUDA_OK(cudaMemcpyAsync(imags, r->im + start, n * sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
     CUDA_OK(cudaStreamSynchronize(g.stream));
 }
 
 void statevec_cloneQureg(Qureg dst, Qureg src) {
-    QuregRec *d = live(dst), *s = live(src);
+    QuregRec *d = fresh(dst), *s = live(src);
+    d->map = s->map;  // same layout as the source
     CUDA_OK(cudaMemcpyAsync(d->re, s->re, d->n * sizeof(qreal), cudaMemcpyDeviceToDevice, g.stream));
     CUDA_OK(cudaMemcpyAsync(d->im, s->im, d->n * sizeof(qreal), cudaMemcpyDeviceToDevice, g.stream));
 }
@@ -643,7 +718,7 @@ qreal statevec_getRealAmp(Qureg qureg, idx_t index) { return readOne(qureg, inde
 qreal statevec_getImagAmp(Qureg qureg, idx_t index) { return readOne(qureg, index, true); }
 
 int statevec_compareStates(Qureg a, Qureg b, qreal precision) {
-    QuregRec *ra = live(a), *rb = live(b);
+    QuregRec *ra = canon(a), *rb = canon(b);
     const int vec = pickVec(ra->n);
     const u64 nVec = (u64)ra->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -661,36 +736,33 @@ int statevec_compareStates(Qureg a, Qureg b, qreal precision) {
 // ---------------------------------------------------------------------------------------------------------
 
 void statevec_initZeroState(Qureg q) {
-    rec(q)->queue.clear();  // the whole state is overwritten: pending gates can be dropped
-    QuregRec* r = rec(q);
+    QuregRec* r = fresh(q);  // the whole state is overwritten: pending gates and the qubit layout are dropped
     CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
     CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
     setOneGlobal(q, 0, 1, 0);
 }
 
 void statevec_initPlusState(Qureg q) {
-    rec(q)->queue.clear();
+    fresh(q);
     const idx_t total = q.numAmpsPerChunk * q.numChunks;
     fillShard(q, 1.0 / sqrt((double)(qreal)total), 0);
 }
 
 void statevec_initClassicalState(Qureg q, idx_t stateInd) {
-    rec(q)->queue.clear();
-    QuregRec* r = rec(q);
+    QuregRec* r = fresh(q);
     CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
     CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
     setOneGlobal(q, stateInd, 1, 0);
 }
 
 void statevec_initStateDebug(Qureg q) {
-    rec(q)->queue.clear();
-    QuregRec* r = rec(q);
+    QuregRec* r = fresh(q);
     k_initDebug<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n);
     launched();
 }
 
 void statevec_initStateOfSingleQubit(Qureg* q, int qubitId, int outcome) {
-    QuregRec* r = live(*q);
+    QuregRec* r = fresh(*q);
     const idx_t total = q->numAmpsPerChunk * q->numChunks;
     const qreal norm = 1.0 / sqrt((qreal)total / 2.0);
     k_initSingleQubit<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q->chunkId * r->n,
@@ -699,13 +771,13 @@ void statevec_initStateOfSingleQubit(Qureg* q, int qubitId, int outcome) {
 }
 
 void densmatr_initPlusState(Qureg q) {
-    rec(q)->queue.clear();
+    fresh(q);
     const idx_t dim = 1LL << q.numQubitsRepresented;
     fillShard(q, 1.0 / ((qreal)dim), 0);
 }
 
 void densmatr_initClassicalState(Qureg q, idx_t stateInd) {
-    QuregRec* r = live(q);
+    QuregRec* r = fresh(q);
     const idx_t dim = 1LL << q.numQubitsRepresented;
     CUDA_OK(cudaMemsetAsync(r->re, 0, r->n * sizeof(qreal), g.stream));
     CUDA_OK(cudaMemsetAsync(r->im, 0, r->n * sizeof(qreal), g.stream));
@@ -714,7 +786,7 @@ void densmatr_initClassicalState(Qureg q, idx_t stateInd) {
 
 void densmatr_initPureState(Qureg rho, Qureg psi) {
     if (g.world > 1) comm::unsupported("initPureState on a sharded density matrix");
-    QuregRec *d = live(rho), *p = live(psi);
+    QuregRec *d = fresh(rho), *p = canon(psi);
     k_outerProduct<<<blocksFor((u64)d->n), kBlock, 0, g.stream>>>(d->re, d->im, p->re, p->im, (u64)psi.numAmpsTotal,
                                                                  (u64)d->n);
     launched();
@@ -778,7 +850,7 @@ qreal statevec_calcProbOfOutcome(Qureg q, const int t, int outcome) {
 }
 
 Complex statevec_calcInnerProduct(Qureg bra, Qureg ket) {
-    QuregRec *b = live(bra), *k = live(ket);
+    QuregRec *b = canon(bra), *k = canon(ket);
     const int vec = pickVec(b->n);
     const u64 nVec = (u64)b->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -805,7 +877,7 @@ qreal densmatr_calcProbOfOutcome(Qureg q, const int t, int outcome) {
 
 qreal densmatr_calcFidelity(Qureg rho, Qureg psi) {
     if (g.world > 1) comm::unsupported("calcFidelity on a sharded density matrix");
-    QuregRec *d = live(rho), *p = live(psi);
+    QuregRec *d = canon(rho), *p = canon(psi);
     const u64 dim = (u64)psi.numAmpsTotal;
     k_densFidelity<<<reduceBlocks(dim), kBlock, 0, g.stream>>>(d->re, d->im, p->re, p->im, dim, g.dPartials, g.dTicket,
                                                               g.dResult);
@@ -819,8 +891,9 @@ qreal densmatr_calcFidelity(Qureg rho, Qureg psi) {
 // collapse                                                               (replaces QuEST_gpu.cu:1847-1966)
 // ---------------------------------------------------------------------------------------------------------
 
-void statevec_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qreal prob) {
+void statevec_collapseToKnownProbOutcome(Qureg q, const int tLogical, int outcome, qreal prob) {
     QuregRec* r = live(q);
+    const int t = r->map.phys[tLogical];
     const qreal renorm = 1 / sqrt((double)prob);
     const int vec = pickVec(r->n);
     if (t >= r->localBits) {
@@ -849,7 +922,7 @@ void statevec_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qrea
 
 void densmatr_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qreal prob) {
     if (g.world > 1) comm::unsupported("collapse of a sharded density matrix");
-    QuregRec* r = live(q);
+    QuregRec* r = canon(q);
     const int n = q.numQubitsRepresented;
     const int vec = pickVec(r->n, 1LL << n);
     const int v = log2i(vec);
@@ -885,7 +958,7 @@ void densmatr_oneQubitDamping(Qureg q, const int t, qreal damping) {
 }
 
 void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase) {
-    QuregRec* r = live(q);
+    QuregRec* r = canon(q);
     const int n = q.numQubitsRepresented;
     const qreal retain = 1 - dephase;
     k_dephase2<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n, 1ull << q1,
@@ -896,7 +969,7 @@ void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase
 void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
     if (level == 0) return;
     if (g.world > 1) comm::unsupported("two-qubit depolarising on a sharded density matrix");
-    QuregRec* r = live(q);
+    QuregRec* r = canon(q);
     const int n = q.numQubitsRepresented;
     // host scalars exactly as QuEST_cpu_local.c:43-48
     qreal eta = 2 / level;
@@ -915,7 +988,7 @@ void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
 }
 
 void densmatr_addDensityMatrix(Qureg a, qreal p, Qureg b) {
-    QuregRec *ra = live(a), *rb = live(b);
+    QuregRec *ra = canon(a), *rb = canon(b);
     const int vec = pickVec(ra->n);
     const u64 nVec = (u64)ra->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -978,7 +1051,7 @@ void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long*
 int qb200_getDevice(void) { return g.device; }
 
 void qb200_getDevicePointers(Qureg qureg, void** real, void** imag) {
-    QuregRec* r = live(qureg);
+    QuregRec* r = canon(qureg);
     *real = r->re;
     *imag = r->im;
 }
@@ -995,6 +1068,36 @@ void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long l
     for (int i = 0; i < kMaxInsert; ++i) out[8 + i] = sg.planned.plan.pos[i];
     out[16] = sg.planned.plan.skipMask;
     out[17] = sg.ctrlMask;
+}
+
+// Host qubit-layout logic, exposed for CPU-only tests (no CUDA call): replays the slot exchanges submit() would
+// perform for a sequence of dense gates (logical target, logical control mask) on a register of nQubits sharded into
+// 2^localBits-amplitude shards.  eventsOut: 3 ints per gate (globalSlot or -1, localSlot, physical target after the
+// exchange); physOut[nQubits]: final logical->physical map; canonOut: pairs (globalSlot, localSlot) that restore the
+// identity layout.  Returns the number of canonicalising exchanges.
+int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, const unsigned long long* masks,
+                     int* eventsOut, int* physOut, int* canonOut) {
+    QubitMap m;
+    m.reset(nQubits, localBits);
+    for (int i = 0; i < nOps; ++i) {
+        SlotSwap sw{-1, -1};
+        if (localBits >= 3 && m.phys[targets[i]] >= localBits) {
+            sw = planSwapIn(m, targets[i], masks[i]);
+            if (sw.globalSlot >= 0) m.applySwap(sw.globalSlot, sw.localSlot);
+        }
+        m.touch(targets[i]);
+        eventsOut[3 * i] = sw.globalSlot;
+        eventsOut[3 * i + 1] = sw.localSlot;
+        eventsOut[3 * i + 2] = m.phys[targets[i]];
+    }
+    for (int q = 0; q < nQubits; ++q) physOut[q] = m.phys[q];
+    SlotSwap back[64];
+    const int n = planCanonicalize(m, back);
+    for (int i = 0; i < n; ++i) {
+        canonOut[2 * i] = back[i].globalSlot;
+        canonOut[2 * i + 1] = back[i].localSlot;
+    }
+    return n;
 }
 
 // Host grouping logic of the fusion queue, exposed for CPU-only tests (no CUDA call): groups the given gate list

@@ -134,6 +134,26 @@ __global__ void __launch_bounds__(kBlock) k_pairsPeer(qreal* __restrict__ upRe, 
     store<VEC>(loIm + i, lI);
 }
 
+// Qubit-slot exchange between a shard-selecting bit and local bit l (qb_plan.h: QubitMap).  `a*` is the shard whose
+// global bit is 0, `b*` the one whose bit is 1; the amplitudes with (global=0, l=1) and (global=1, l=0) trade
+// places: a[j | 2^l] <-> b[j] for every j with bit l clear.  Half a shard crosses NVLink in each direction.  As in
+// k_pairsPeer the two GPUs split the index range between them and each performs complete swaps in place.
+template <int VEC>
+__global__ void __launch_bounds__(kBlock) k_swapPeer(qreal* __restrict__ aRe, qreal* __restrict__ aIm,
+                                                    qreal* __restrict__ bRe, qreal* __restrict__ bIm,
+                                                    unsigned long long nTasks, BitPlan plan, int lvb) {
+    const unsigned long long k = (unsigned long long)blockIdx.x * kBlock + threadIdx.x;
+    if (k >= nTasks) return;
+    const unsigned long long vi = expand(k, plan);
+    const unsigned long long ib = vi * VEC, ia = ib + ((unsigned long long)VEC << lvb);
+    const Vec<qreal, VEC> ar = load<VEC>(aRe + ia), ai = load<VEC>(aIm + ia);
+    const Vec<qreal, VEC> br = load<VEC>(bRe + ib), bi = load<VEC>(bIm + ib);
+    store<VEC>(aRe + ia, br);
+    store<VEC>(aIm + ia, bi);
+    store<VEC>(bRe + ib, ar);
+    store<VEC>(bIm + ib, ai);
+}
+
 // ======================================================================================================
 // diagonal operators on single amplitudes
 // ======================================================================================================

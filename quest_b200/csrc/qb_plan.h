@@ -135,3 +135,98 @@ inline ShardedGate planShardedGate(int localBits, int chunkId, int target, unsig
 }
 
 }  // namespace qb
+
+// ---------------------------------------------------------------------------------------------------------
+// Qubit remapping for sharded registers.
+//
+// A dense gate on a qubit that selects the GPU needs the partner's amplitudes: 16 bytes per amplitude pair over
+// NVLink for EVERY such gate.  Instead, the first gate on such a qubit swaps it with a local qubit - an exchange of
+// half a shard, 8 bytes per amplitude - after which that qubit is local: its gates join the fusion queue and cost
+// no communication until a gate needs the evicted qubit.  QubitMap records where each logical qubit currently
+// lives.  Invariant: the map is a product of disjoint transpositions (global slot g <-> local slot l), so undoing
+// it is replaying the same swaps.  All ranks run this logic on identical inputs and stay consistent.
+// ---------------------------------------------------------------------------------------------------------
+namespace qb {
+
+struct QubitMap {
+    int nQubits = 0, localBits = 0;
+    int phys[64];                   // logical qubit -> bit position in the amplitude index
+    int logicalAt[64];              // bit position -> logical qubit
+    unsigned long long lastUse[64]; // logical qubit -> tick of its last use as a dense target
+    unsigned long long tick = 0;
+
+    void reset(int n, int local) {
+        nQubits = n;
+        localBits = local;
+        tick = 0;
+        for (int q = 0; q < 64; ++q) {
+            phys[q] = logicalAt[q] = q;
+            lastUse[q] = 0;
+        }
+    }
+    bool identity() const {
+        for (int q = 0; q < nQubits; ++q)
+            if (phys[q] != q) return false;
+        return true;
+    }
+    unsigned long long physMask(unsigned long long logicalMask) const {
+        unsigned long long m = 0;
+        while (logicalMask) {
+            const int q = __builtin_ctzll(logicalMask);
+            logicalMask &= logicalMask - 1;
+            m |= 1ull << phys[q];
+        }
+        return m;
+    }
+    unsigned long long physIndex(unsigned long long logicalIndex) const {
+        unsigned long long p = 0;
+        for (int q = 0; q < nQubits; ++q)
+            if ((logicalIndex >> q) & 1) p |= 1ull << phys[q];
+        return p;
+    }
+    void touch(int logicalQubit) { lastUse[logicalQubit] = ++tick; }
+    void applySwap(int g, int l) {  // exchange the occupants of bit positions g and l
+        const int a = logicalAt[g], b = logicalAt[l];
+        logicalAt[g] = b;
+        logicalAt[l] = a;
+        phys[a] = l;
+        phys[b] = g;
+    }
+};
+
+struct SlotSwap {
+    int globalSlot, localSlot;  // bit positions to exchange; globalSlot < 0: nothing to do
+};
+
+// Which exchange makes logical qubit q local?  `avoidMask` = logical qubits that should not be evicted (the
+// gate's own controls).  (a) q sits in a global slot because it was evicted earlier: undo that transposition.
+// (b) q is global-native in its own slot: evict the least recently used local-native qubit that is at home.
+inline SlotSwap planSwapIn(const QubitMap& m, int q, unsigned long long avoidMask) {
+    SlotSwap s{-1, -1};
+    const int p = m.phys[q];
+    if (p < m.localBits) return s;
+    if (q < m.localBits) {  // (a) q's home slot is local and currently holds the qubit native to slot p
+        s.globalSlot = p;
+        s.localSlot = q;
+        return s;
+    }
+    int best = -1;
+    for (int x = 2; x < m.localBits; ++x) {  // (b); slots 0 and 1 stay put so exchanges move whole 32-byte vectors
+        if (m.phys[x] != x || ((avoidMask >> x) & 1)) continue;
+        if (best < 0 || m.lastUse[x] < m.lastUse[best] || (m.lastUse[x] == m.lastUse[best] && x > best)) best = x;
+    }
+    if (best < 0) return s;  // every local qubit is pinned: caller falls back to the cross-shard gate
+    s.globalSlot = p;
+    s.localSlot = best;
+    return s;
+}
+
+// The transpositions that restore the identity layout (each is its own inverse).
+inline int planCanonicalize(const QubitMap& m, SlotSwap* out /* >= 64 */) {
+    int n = 0;
+    for (int g = m.localBits; g < m.nQubits; ++g)
+        if (m.logicalAt[g] != g) out[n++] = SlotSwap{g, m.logicalAt[g]};  // occupant's home is the local slot
+    return n;
+}
+
+}  // namespace qb

@@ -222,3 +222,59 @@ def test_sharded_protocol_over_gloo_matches_oracle(world, oracle, oracle_env, tm
     want = oracle.get_state(q)
     oracle.destroyQureg(q, oracle_env)
     np.testing.assert_allclose(got, want, atol=1e-13)
+
+
+# ---- qubit remapping (slot exchange instead of a cross-shard pass per gate) -----------------------------------------
+
+def _swap_bits(state, a, b):
+    """Permute a full state so that index bits a and b trade places (what k_swapPeer does to the shards)."""
+    idx = np.arange(state.size)
+    ba, bb = (idx >> a) & 1, (idx >> b) & 1
+    src = idx ^ ((ba ^ bb) << a) ^ ((ba ^ bb) << b)
+    return state[src]
+
+
+@pytest.mark.parametrize("world,seed", [(2, 1), (4, 2), (8, 3)])
+def test_qubit_remap_keeps_the_state_and_ends_canonical(world, seed):
+    if not os.path.isfile(capi.PRODUCT_LIB):
+        from quest_b200 import build
+        build.build_product(2)
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    lib.qb200_debugRemap.restype = ctypes.c_int
+    rng = random.Random(seed)
+    nq = 10
+    L = nq - (world.bit_length() - 1)
+    n_ops = 80
+    targets, masks, mats = [], [], []
+    for _ in range(n_ops):
+        t = rng.randrange(nq) if rng.random() < 0.5 else rng.randrange(L, nq)
+        cs = rng.sample([q for q in range(nq) if q != t], rng.choice([0, 0, 1, 2]))
+        targets.append(t); masks.append(sum(1 << c for c in cs)); mats.append(rand_u(rng))
+    ev = (ctypes.c_int * (3 * n_ops))()
+    phys = (ctypes.c_int * nq)()
+    canon = (ctypes.c_int * 128)()
+    n_back = lib.qb200_debugRemap(nq, L, n_ops, (ctypes.c_int * n_ops)(*targets), (ctypes.c_ulonglong * n_ops)(*masks), ev, phys, canon)
+    state = circuits.random_state(1 << nq, seed)
+    want = state.copy()
+    layout = list(range(nq))  # logical -> physical, tracked independently of the library
+    cur = state.copy()
+    n_swaps = 0
+    for i in range(n_ops):
+        want = dense_reference(want, nq, targets[i], masks[i], mats[i])
+        g, l, pt = ev[3 * i], ev[3 * i + 1], ev[3 * i + 2]
+        if g >= 0:
+            assert g >= L > l >= 2
+            cur = _swap_bits(cur, g, l)
+            a, b = layout.index(g), layout.index(l)
+            layout[a], layout[b] = l, g
+            n_swaps += 1
+        assert layout[targets[i]] == pt < L          # every dense gate ends up on a local slot
+        pm = sum(1 << layout[c] for c in range(nq) if (masks[i] >> c) & 1)
+        cur = dense_reference(cur, nq, pt, pm, mats[i])
+    assert list(phys) == layout
+    # far fewer exchanges than shard-crossing gates
+    n_cross = sum(1 for t in targets if t >= L)
+    assert 0 < n_swaps < n_cross
+    for k in range(n_back):
+        cur = _swap_bits(cur, canon[2 * k], canon[2 * k + 1])
+    np.testing.assert_allclose(cur, want, atol=1e-12)
