@@ -203,6 +203,22 @@ void runDiagNow(const Qureg& q, u64 mask, const Op& op) {
     launched();
 }
 
+// One noise channel in its own pass (k_noise1).  The channels are symmetric in the qubit's row and column bits, so
+// the lower of the two bit positions plays the row and the higher - always above the vector - the column.
+template <int KIND>
+void runNoiseNow(const Qureg& q, int bitA, int bitB, qreal p0, qreal p1, qreal p2) {
+    QuregRec* r = rec(q);
+    const int lo = bitA < bitB ? bitA : bitB, hi = bitA < bitB ? bitB : bitA;
+    const int vec = pickVec(r->n, 1LL << hi);
+    const int v = log2i(vec);
+    const Planned p = makePlan(r->n, vec, {lo, hi}, 0);
+    dispatchVT(vec, lo, [&](auto V, auto T) {
+        k_noise1<KIND, decltype(V)::value, decltype(T)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(
+            r->re, r->im, p.nTasks, p.plan, lo - v, hi - v, p0, p1, p2);
+    });
+    launched();
+}
+
 OpMatrix matrixOf(const PendingOp& op) {
     return OpMatrix{op.c[0], op.c[1], op.c[2], op.c[3], op.c[4], op.c[5], op.c[6], op.c[7]};
 }
@@ -225,8 +241,17 @@ void runOpNow(const Qureg& q, const PendingOp& op) {
         case kFPhase:
             runDiagNow(q, op.mask, DiagPhase{op.c[0], op.c[1]});
             break;
-        default:
+        case kFFlip:
             runDiagNow(q, op.mask, DiagFlip{});
+            break;
+        case kFDephase:
+            runNoiseNow<kDephase>(q, op.target, op.target2, op.c[0], op.c[1], op.c[2]);
+            break;
+        case kFDepolarise:
+            runNoiseNow<kDepolarise>(q, op.target, op.target2, op.c[0], op.c[1], op.c[2]);
+            break;
+        default:
+            runNoiseNow<kDamping>(q, op.target, op.target2, op.c[0], op.c[1], op.c[2]);
             break;
     }
 }
@@ -256,10 +281,15 @@ void flush(const Qureg& q) {
             CUDA_OK(cudaEventRecord(e0, g.stream));
         }
         // 128-thread CTAs, 4 per SM (128 registers per thread): measured best of 64/128/256 threads x 2-6 CTAs
-        if (g.fuseBlock == 256)
-            k_fused<kFuseBits, 256, 2><<<blocksFor(fl.nThreads), 256, 0, g.stream>>>(r->re, r->im, fl);
+        bool noisy = false;
+        for (int i = 0; i < grp.count; ++i) noisy = noisy || isNoise(ops[grp.first + i].kind);
+        const unsigned int nb128 = (unsigned int)((fl.nThreads + 127) / 128);
+        if (noisy)
+            k_fused<kFuseBits, 128, 4, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+        else if (g.fuseBlock == 256)
+            k_fused<kFuseBits, 256, 2, false><<<blocksFor(fl.nThreads), 256, 0, g.stream>>>(r->re, r->im, fl);
         else
-            k_fused<kFuseBits, 128, 4><<<(unsigned int)((fl.nThreads + 127) / 128), 128, 0, g.stream>>>(r->re, r->im, fl);
+            k_fused<kFuseBits, 128, 4, false><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
         launched();
         if (g.timeFused) {
             CUDA_OK(cudaEventRecord(e1, g.stream));
@@ -347,19 +377,29 @@ void submit(const Qureg& q, PendingOp op) {
     // logical qubits -> current bit positions; a dense target living in a shard-selecting slot is first made local
     if (g.world > 1) {
         if (!isDiagonal(op.kind)) {
-            if (g.remap && r->localBits >= 3 && r->map.phys[op.target] >= r->localBits) {
-                const SlotSwap sw = planSwapIn(r->map, op.target, op.mask);
-                if (sw.globalSlot >= 0) {
-                    flush(q);
-                    exchangeSlots(q, sw);
+            const int logical[2] = {op.target, op.target2};
+            for (int k = 0; k < 2; ++k) {
+                const int t = logical[k];
+                if (t < 0) continue;
+                if (g.remap && r->localBits >= 3 && r->map.phys[t] >= r->localBits) {
+                    u64 keep = op.mask | (1ull << logical[0]);
+                    if (logical[1] >= 0) keep |= 1ull << logical[1];
+                    const SlotSwap sw = planSwapIn(r->map, t, keep);
+                    if (sw.globalSlot >= 0) {
+                        flush(q);
+                        exchangeSlots(q, sw);
+                    }
                 }
+                r->map.touch(t);
             }
-            r->map.touch(op.target);
-            op.target = r->map.phys[op.target];
+            op.target = r->map.phys[logical[0]];
+            if (logical[1] >= 0) op.target2 = r->map.phys[logical[1]];
         }
         op.mask = r->map.physMask(op.mask);
     }
     if (!qb::localiseControls(r->localBits, q.chunkId, op.mask)) return;
+    if (isNoise(op.kind) && (op.target >= r->localBits || op.target2 >= r->localBits))
+        comm::unsupported("one-qubit noise on a qubit that selects the shard (with QUEST_B200_REMAP=0)");
     const bool cross = !isDiagonal(op.kind) && op.target >= r->localBits;
     if (cross) {
         flush(q);
@@ -379,6 +419,7 @@ PendingOp denseOp(int kind, int target, u64 ctrlMask) {
     std::memset(&op, 0, sizeof op);
     op.kind = kind;
     op.target = target;
+    op.target2 = -1;
     op.mask = ctrlMask;
     return op;
 }
@@ -504,21 +545,6 @@ double densDiagSum(const Qureg& q, int bit) {
     return s;
 }
 
-template <int KIND>
-void launchNoise1(const Qureg& q, int t, qreal p0, qreal p1, qreal p2) {
-    canon(q);
-    if (g.world > 1) comm::unsupported("one-qubit noise on a sharded density matrix");
-    QuregRec* r = live(q);
-    const int n = q.numQubitsRepresented;
-    const int vec = pickVec(r->n, 1LL << n);
-    const int v = log2i(vec);
-    const Planned p = makePlan(r->n, vec, {t, t + n}, 0);
-    dispatchVT(vec, t, [&](auto V, auto T) {
-        k_noise1<KIND, decltype(V)::value, decltype(T)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(
-            r->re, r->im, p.nTasks, p.plan, t - v, t + n - v, p0, p1, p2);
-    });
-    launched();
-}
 
 }  // namespace
 
@@ -939,22 +965,32 @@ void densmatr_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qrea
 // ---------------------------------------------------------------------------------------------------------
 
 
+static void submitNoise(Qureg q, int kind, int t, qreal c0, qreal c1, qreal c2) {
+    PendingOp op = denseOp(kind, t, 0);
+    op.target2 = t + q.numQubitsRepresented;  // the qubit's column bit in the flattened density matrix
+    op.c[0] = c0;
+    op.c[1] = c1;
+    op.c[2] = c2;
+    submit(q, op);
+}
+
+// scalars formed exactly as the reference does on the host (QuEST_cpu.c:67-70,119,168-169)
 void densmatr_oneQubitDephase(Qureg q, const int t, qreal dephase) {
     const qreal retain = 1 - dephase;
-    launchNoise1<kDephase>(q, t, retain, 0, 0);
+    submitNoise(q, kFDephase, t, retain, 0, 0);
 }
 
 void densmatr_oneQubitDepolarise(Qureg q, const int t, qreal level) {
     if (level == 0) return;
     const qreal retain = 1 - level;
-    launchNoise1<kDepolarise>(q, t, retain, level, retain);
+    submitNoise(q, kFDepolarise, t, retain, level, retain);
 }
 
 void densmatr_oneQubitDamping(Qureg q, const int t, qreal damping) {
     if (damping == 0) return;
     const qreal retain = 1 - damping;
     const qreal dephase = sqrt((double)retain);
-    launchNoise1<kDamping>(q, t, dephase, damping, retain);
+    submitNoise(q, kFDamping, t, dephase, damping, retain);
 }
 
 void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase) {
@@ -1110,6 +1146,7 @@ int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* target
         std::memset(&ops[i], 0, sizeof(PendingOp));
         ops[i].kind = kinds[i];
         ops[i].target = targets[i];
+        ops[i].target2 = -1;
         ops[i].mask = masks[i];
     }
     const std::vector<FusedGroup> groups = groupOps(ops, localBits);

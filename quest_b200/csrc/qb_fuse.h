@@ -22,26 +22,32 @@ namespace qb {
 constexpr int kFuseBits = 4;       // qubits resolved in registers per launch (16 amplitudes per thread)
 constexpr int kMaxFusedGates = 96;  // gates per launch: descriptors travel as kernel parameters (constant bank)
 
-enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, kFPhase = 4, kFFlip = 5 };
+enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, kFPhase = 4, kFFlip = 5,
+                       // one-qubit noise channels of a density matrix: act on the 2x2 block structure spanned by the
+                       // qubit's row bit and column bit (two dense targets); symmetric under exchanging the two
+                       kFDephase = 6, kFDepolarise = 7, kFDamping = 8 };
 
 inline bool isDiagonal(int kind) { return kind == kFPhase || kind == kFFlip; }
+inline bool isNoise(int kind) { return kind >= kFDephase; }
 
 // A recorded gate: target and control mask are LOCAL bit positions of this rank's shard (controls on
 // shard-selecting qubits were already resolved when the gate was recorded).
 struct PendingOp {
     int kind;
     int target;                    // dense kinds only
+    int target2;                   // noise kinds: the second bit of the (row, column) pair; otherwise -1
     unsigned long long mask;       // dense: control mask; diagonal: all selecting bits
     qreal c[8];                    // Matrix: r00,i00,r01,i01,r10,i10,r11,i11; Hadamard: c[0]=1/sqrt2;
-                                   // PauliY: c[0]=+-1; Phase: c[0]=cos, c[1]=sin
+                                   // PauliY: c[0]=+-1; Phase: c[0]=cos, c[1]=sin; noise: c[0]=factor on
+                                   // coherences, c[1]=level, c[2]=1-level (see k_noise1)
 };
 
 // What the kernel reads per gate.
 struct FusedGate {
     int kind;
-    int pos;                       // dense: which of the kFuseBits register bits is the target
+    int pos;                       // dense: which of the kFuseBits register bits is the target (noise: the lower one)
     unsigned int regMask;          // control/selecting bits that are register bits (bit j = j-th fused qubit)
-    unsigned int pad;
+    int pos2;                      // noise: register bit of the higher of the two targets
     unsigned long long outerMask;  // control/selecting bits outside the fused qubits (amplitude-index space)
     qreal c[8];
 };
@@ -65,10 +71,14 @@ inline std::vector<FusedGroup> groupOps(const std::vector<PendingOp>& ops, int l
         unsigned long long chosen = 0;
         while (i < n && g.count < kMaxFusedGates) {
             const PendingOp& op = ops[i];
-            if (!isDiagonal(op.kind) && !((chosen >> op.target) & 1)) {
-                if (g.nDenseBits == kFuseBits) break;
-                chosen |= 1ull << op.target;
-                ++g.nDenseBits;
+            if (!isDiagonal(op.kind)) {
+                unsigned long long need = 1ull << op.target;
+                if (op.target2 >= 0) need |= 1ull << op.target2;
+                need &= ~chosen;
+                const int extra = __builtin_popcountll(need);
+                if (g.nDenseBits + extra > kFuseBits) break;
+                chosen |= need;
+                g.nDenseBits += extra;
             }
             ++g.count;
             ++i;
@@ -106,9 +116,13 @@ inline FusedGate describe(const PendingOp& op, const int* bits) {
     std::memset(&fg, 0, sizeof fg);
     fg.kind = op.kind;
     fg.pos = 0;
+    fg.pos2 = 0;
     unsigned long long outer = op.mask;
+    const int lowT = op.target2 >= 0 && op.target2 < op.target ? op.target2 : op.target;
+    const int highT = op.target2 >= 0 ? (op.target2 < op.target ? op.target : op.target2) : -1;
     for (int j = 0; j < kFuseBits; ++j) {
-        if (!isDiagonal(op.kind) && bits[j] == op.target) fg.pos = j;
+        if (!isDiagonal(op.kind) && bits[j] == lowT) fg.pos = j;
+        if (bits[j] == highT) fg.pos2 = j;
         if ((op.mask >> bits[j]) & 1) {
             fg.regMask |= 1u << j;
             outer &= ~(1ull << bits[j]);

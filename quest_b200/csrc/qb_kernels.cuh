@@ -273,7 +273,43 @@ __device__ __forceinline__ void onSelected(unsigned int regMask, qreal (&xr)[1 <
     }
 }
 
-template <int R, int BLOCK, int MINB>
+// One-qubit noise channel on the (row bit P, column bit Q) block structure, P < Q register bits.  Same arithmetic as
+// k_noise1 (reference QuEST_cpu.c:36-65, 118-215): coherences (1,0),(0,1) scaled by c0; populations (0,0),(1,1)
+// mixed (depolarising) or decayed (damping).  The channels are symmetric under exchanging the two bits.
+template <int KIND, int P, int Q, int R>
+__device__ __forceinline__ void noiseQuads(qreal (&xr)[1 << R], qreal (&xi)[1 << R], qreal c0, qreal c1, qreal c2) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e) {
+        if (((e >> P) & 1) || ((e >> Q) & 1)) continue;
+        const int e10 = e | (1 << P), e01 = e | (1 << Q), e11 = e10 | e01;
+        xr[e10] = c0 * xr[e10]; xi[e10] = c0 * xi[e10];
+        xr[e01] = c0 * xr[e01]; xi[e01] = c0 * xi[e01];
+        if (KIND == kFDepolarise) {
+            const qreal avR = (xr[e] + xr[e11]) / 2, avI = (xi[e] + xi[e11]) / 2;
+            xr[e] = c2 * xr[e] + c1 * avR;     xi[e] = c2 * xi[e] + c1 * avI;
+            xr[e11] = c2 * xr[e11] + c1 * avR; xi[e11] = c2 * xi[e11] + c1 * avI;
+        } else if (KIND == kFDamping) {
+            xr[e] = xr[e] + c1 * xr[e11];      xi[e] = xi[e] + c1 * xi[e11];
+            xr[e11] = c2 * xr[e11];            xi[e11] = c2 * xi[e11];
+        }
+    }
+}
+
+template <int KIND, int R>
+__device__ __forceinline__ void onNoiseBits(int p, int q, qreal (&xr)[1 << R], qreal (&xi)[1 << R], qreal c0, qreal c1, qreal c2) {
+    switch (p * 4 + q) {
+        case 1: noiseQuads<KIND, 0, 1, R>(xr, xi, c0, c1, c2); break;
+        case 2: noiseQuads<KIND, 0, 2, R>(xr, xi, c0, c1, c2); break;
+        case 3: noiseQuads<KIND, 0, 3, R>(xr, xi, c0, c1, c2); break;
+        case 6: noiseQuads<KIND, 1, 2, R>(xr, xi, c0, c1, c2); break;
+        case 7: noiseQuads<KIND, 1, 3, R>(xr, xi, c0, c1, c2); break;
+        default: noiseQuads<KIND, 2, 3, R>(xr, xi, c0, c1, c2); break;
+    }
+}
+
+// NOISE selects the instantiation that also understands the density-matrix noise kinds; state-vector groups use the
+// leaner one.
+template <int R, int BLOCK, int MINB, bool NOISE>
 __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, qreal* __restrict__ im,
                                                 const __grid_constant__ FusedLaunch fl) {
     static_assert(R == kFuseBits && R == 4, "k_fused is written for 4 fused qubits");
@@ -354,8 +390,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
             case kFPhase:
                 onSelected<R>(G.regMask, xr, xi, DiagPhase{G.c[0], G.c[1]});
                 break;
-            default:  // kFFlip
+            case kFFlip:
                 onSelected<R>(G.regMask, xr, xi, DiagFlip{});
+                break;
+            default:
+                if constexpr (NOISE) {
+                    if (G.kind == kFDephase) onNoiseBits<kFDephase, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                    else if (G.kind == kFDepolarise) onNoiseBits<kFDepolarise, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                    else onNoiseBits<kFDamping, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                }
                 break;
         }
     }

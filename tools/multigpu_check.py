@@ -72,6 +72,31 @@ def main():
             ok = ok and good
             print(f"case {case}: {nq} qubits over {world} GPUs, {len(ops)} ops, measure={measure}: bit-exact={same_bits} "
                   f"rel.err={err:.2e} scalars_ok={scal_ok} getAmp_ok={amp_ok} -> {'PASS' if good else 'FAIL'}", flush=True)
+    # sharded density matrices: unitaries on row and column qubits, one-qubit noise channels (also on qubits whose
+    # column bit selects the shard), purity and outcome probabilities
+    for case, (nd, seed) in enumerate([(11, 311), (9, 312)]):
+        ops = circuits.random_circuit(nd, args.depth, seed, density=True, measure=False, two_qubit_noise=False)
+        ops += [(name, t, 0.05 + 0.01 * t) for t in range(nd) for name in circuits.NOISE] + [("calcPurity",), ("calcTotalProb",)]
+        q = lib.createDensityQureg(nd, env)
+        circuits.prepare(lib, q, seed)
+        scal = circuits.run_circuit(lib, q, ops, seed=seed)
+        shard = lib.get_state(q)
+        lib.destroyQureg(q, env)
+        gathered = [torch.empty(2 * shard.size, dtype=torch.float64) for _ in range(world)] if rank == 0 else None
+        dist.gather(torch.from_numpy(shard.view(np.float64).copy()), gathered, dst=0)
+        if rank == 0:
+            got = np.concatenate([t.numpy().view(np.complex128) for t in gathered])
+            cq = cpu.createDensityQureg(nd, cenv)
+            circuits.prepare(cpu, cq, seed)
+            cscal = circuits.run_circuit(cpu, cq, ops, seed=seed)
+            want = cpu.get_state(cq)
+            cpu.destroyQureg(cq, cenv)
+            same_bits = np.array_equal(got.view(np.float64), want.view(np.float64))
+            scal_ok = np.allclose(scal, cscal, rtol=1e-12, atol=1e-13)
+            good = same_bits and scal_ok
+            ok = ok and good
+            print(f"density case {case}: {nd}-qubit density matrix over {world} GPUs, {len(ops)} ops: bit-exact={same_bits} "
+                  f"scalars_ok={scal_ok} -> {'PASS' if good else 'FAIL'}", flush=True)
     flag = torch.tensor([1 if ok else 0])
     dist.broadcast(flag, 0)
     lib.destroyQuESTEnv(env)
