@@ -324,21 +324,55 @@ def main():
     if os.path.isfile(prof2):
         roofline["traffic"] = json.load(open(prof2)).get("dram_bytes_per_launch")
 
+    # NVLink: the two kernels that move amplitudes between GPUs, timed on the top qubit with CUDA events
     nvlink = None
     if world > 1:
-        # rank 0's view of a global gate includes waiting for a partner that was busy with a gate rank 0 could skip
-        # (controls on shard-selecting qubits); the dense class with the smallest mean is free of that skew
-        means = {k: sum(v) / len(v) for k, v in cross.items() if k in ("hadamard", "compactUnitary", "rotateY")}
-        dense_cross = cross[min(means, key=means.get)] if means else []
-        if dense_cross:
-            ms = sum(dense_cross) / len(dense_cross)
-            per_dir = 16.0 * n_local / (ms * 1e-3) / 1e9  # bytes each GPU sends AND receives per dense global gate
-            nvlink = {"kernel": "qb::k_pairsPeer (dense gate on a shard-selecting qubit, exchange fused over peer memory)",
-                      "ms_per_gate": ms, "gates_timed": len(dense_cross), "bytes_each_way_per_gpu": 16.0 * n_local,
-                      "achieved_GBps_per_direction": per_dir, "peak_measured_peer_copy": 770.0, "peak_nominal": 900.0,
-                      "frac_of_measured": per_dir / 770.0, "frac_of_nominal": per_dir / 900.0,
-                      "per_class_ms": {k: sum(v) / len(v) for k, v in cross.items()},
-                      "includes": "two stream-ordered pair handshakes (NCCL send/recv of 4 bytes) per gate"}
+        lib.lib.qb200_setRemap.argtypes = [ctypes.c_int]
+        lib.lib.qb200_getSlotExchangeCount.restype = ctypes.c_ulonglong
+        top = nq - 1
+
+        def timed_ms(fn, before=None, reps=3):
+            out = []
+            for _ in range(reps):
+                if before:
+                    before()
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                fn()
+                lib.lib.qb200_flush()
+                e1.record(stream)
+                barrier()
+                out.append(e0.elapsed_time(e1))
+            t = torch.tensor([sorted(out)[len(out) // 2]], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        lib.lib.qb200_setFusion(0)
+        lib.lib.qb200_setRemap(0)
+        lib.hadamard(q, top)  # warm: NCCL pair connection
+        cross_ms = timed_ms(lambda: lib.hadamard(q, top))
+        # with remapping on, a hadamard on the (canonically placed) top qubit = one slot exchange + one local gate;
+        # qb200_setRemap(1) puts every qubit back in its own slot before each repetition
+        n0 = lib.lib.qb200_getSlotExchangeCount()
+        swap_ms = timed_ms(lambda: lib.hadamard(q, top), before=lambda: lib.lib.qb200_setRemap(1))
+        exchange_ms = swap_ms - dense_ms
+        lib.lib.qb200_setFusion(1)
+        per_dir_cross = 16.0 * n_local / (cross_ms * 1e-3) / 1e9
+        nvlink = {"cross_shard_gate": {"kernel": "qb::k_pairsPeer (dense gate on a shard-selecting qubit, exchange fused "
+                                                 "into the gate over peer memory; remapping off)",
+                                       "ms": cross_ms, "bytes_each_way_per_gpu": 16.0 * n_local,
+                                       "achieved_GBps_per_direction": per_dir_cross,
+                                       "frac_of_measured_peer_copy_770": per_dir_cross / 770.0,
+                                       "frac_of_nominal_900": per_dir_cross / 900.0,
+                                       "includes": "two stream-ordered pair handshakes (NCCL send/recv of 4 bytes)"},
+                  "slot_exchange": {"kernel": "qb::k_swapPeer (makes a shard-selecting qubit local: half a shard each way)",
+                                    "bytes_each_way_per_gpu": 8.0 * n_local, "ms": exchange_ms,
+                                    "achieved_GBps_per_direction": 8.0 * n_local / (exchange_ms * 1e-3) / 1e9,
+                                    "frac_of_measured_peer_copy_770": 8.0 * n_local / (exchange_ms * 1e-3) / 1e9 / 770.0,
+                                    "how": "hadamard on the top qubit with remapping on (one exchange + one local dense "
+                                           "gate) minus the local dense gate time",
+                                    "exchanges_counted": int(lib.lib.qb200_getSlotExchangeCount() - n0)}}
 
     # e2e: every step uploads the state from pinned host memory through initStateFromAmps, runs the same gates and
     # reads a scalar back through calcTotalProb (host wall clock, max over ranks)

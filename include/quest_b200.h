@@ -33,6 +33,14 @@ int qb200_getFusion(void);
 void qb200_flush(void);
 void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long* fusedGates);
 
+/* Sharded registers (WORLD_SIZE > 1).  With remapping enabled (default; QUEST_B200_REMAP=0 disables) a dense gate on a
+ * qubit that selects the GPU first makes that qubit local by exchanging it with the least recently used local qubit
+ * - half a shard over NVLink - and later gates on it cost no communication; the reference exchanges whole shards for
+ * every such gate (QuEST_cpu_distributed.c:451-479).  Every index-addressed call (getAmp, setAmps, ...) sees the
+ * logical layout.  qb200_setRemap(0) restores the identity layout and runs such gates as cross-shard passes. */
+void qb200_setRemap(int enabled);
+unsigned long long qb200_getSlotExchangeCount(void);
+
 /* Measurement aid: with timing enabled every fused pass is bracketed by CUDA events on the engine stream;
  * qb200_getFusedKernelTime synchronises, returns their summed device time and count, and clears the record. */
 void qb200_setKernelTiming(int enabled);

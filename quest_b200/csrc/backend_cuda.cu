@@ -219,6 +219,20 @@ void runNoiseNow(const Qureg& q, int bitA, int bitB, qreal p0, qreal p1, qreal p
     launched();
 }
 
+// Density-matrix collapse in its own pass (k_densCollapse); symmetric in the two bits like the noise channels.
+void runDensCollapseNow(const Qureg& q, int bitA, int bitB, int outcome, qreal prob) {
+    QuregRec* r = rec(q);
+    const int lo = bitA < bitB ? bitA : bitB, hi = bitA < bitB ? bitB : bitA;
+    const int vec = pickVec(r->n, 1LL << hi);
+    const int v = log2i(vec);
+    const Planned p = makePlan(r->n, vec, {lo, hi}, 0);
+    dispatchVT(vec, lo, [&](auto V, auto T) {
+        k_densCollapse<decltype(V)::value, decltype(T)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(
+            r->re, r->im, p.nTasks, p.plan, lo - v, hi - v, outcome, prob);
+    });
+    launched();
+}
+
 OpMatrix matrixOf(const PendingOp& op) {
     return OpMatrix{op.c[0], op.c[1], op.c[2], op.c[3], op.c[4], op.c[5], op.c[6], op.c[7]};
 }
@@ -250,8 +264,11 @@ void runOpNow(const Qureg& q, const PendingOp& op) {
         case kFDepolarise:
             runNoiseNow<kDepolarise>(q, op.target, op.target2, op.c[0], op.c[1], op.c[2]);
             break;
-        default:
+        case kFDamping:
             runNoiseNow<kDamping>(q, op.target, op.target2, op.c[0], op.c[1], op.c[2]);
+            break;
+        default:
+            runDensCollapseNow(q, op.target, op.target2, op.c[1] != 0 ? 1 : 0, op.c[0]);
             break;
     }
 }
@@ -946,18 +963,13 @@ void statevec_collapseToKnownProbOutcome(Qureg q, const int tLogical, int outcom
     launched();
 }
 
+// recorded like a noise channel: it acts on the (row bit, column bit) block structure of the measured qubit
 void densmatr_collapseToKnownProbOutcome(Qureg q, const int t, int outcome, qreal prob) {
-    if (g.world > 1) comm::unsupported("collapse of a sharded density matrix");
-    QuregRec* r = canon(q);
-    const int n = q.numQubitsRepresented;
-    const int vec = pickVec(r->n, 1LL << n);
-    const int v = log2i(vec);
-    const Planned p = makePlan(r->n, vec, {t, t + n}, 0);
-    dispatchVT(vec, t, [&](auto V, auto T) {
-        k_densCollapse<decltype(V)::value, decltype(T)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(
-            r->re, r->im, p.nTasks, p.plan, t - v, t + n - v, outcome, prob);
-    });
-    launched();
+    PendingOp op = denseOp(kFDensCollapse, t, 0);
+    op.target2 = t + q.numQubitsRepresented;
+    op.c[0] = prob;
+    op.c[1] = (qreal)outcome;
+    submit(q, op);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -1056,6 +1068,23 @@ void qb200_setFusion(int enabled) {
 }
 
 int qb200_getFusion(void) { return g.fuse ? 1 : 0; }
+
+// Sharded registers only.  Off: every dense gate on a shard-selecting qubit runs as a cross-shard pass
+// (k_pairsPeer).  Switching drains the queues and restores every register's identity layout first.
+void qb200_setRemap(int enabled) {
+    for (QuregRec* r : liveRegisters) {
+        Qureg q;
+        std::memset(&q, 0, sizeof q);
+        q.pairStateVec.real = reinterpret_cast<qreal*>(r);
+        q.numAmpsPerChunk = r->n;
+        q.chunkId = g.rank;
+        q.numChunks = g.world;
+        canon(q);
+    }
+    g.remap = enabled != 0;
+}
+
+unsigned long long qb200_getSlotExchangeCount(void) { return g.slotSwaps; }
 
 void qb200_flush(void) { flushAll(); }
 

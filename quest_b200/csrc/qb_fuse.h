@@ -25,7 +25,9 @@ constexpr int kMaxFusedGates = 96;  // gates per launch: descriptors travel as k
 enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, kFPhase = 4, kFFlip = 5,
                        // one-qubit noise channels of a density matrix: act on the 2x2 block structure spanned by the
                        // qubit's row bit and column bit (two dense targets); symmetric under exchanging the two
-                       kFDephase = 6, kFDepolarise = 7, kFDamping = 8 };
+                       kFDephase = 6, kFDepolarise = 7, kFDamping = 8,
+                       // density-matrix collapse: block (o,o) of the (row,column) structure /= c[0], other blocks = 0; c[1] = o
+                       kFDensCollapse = 9 };
 
 inline bool isDiagonal(int kind) { return kind == kFPhase || kind == kFFlip; }
 inline bool isNoise(int kind) { return kind >= kFDephase; }

@@ -282,6 +282,14 @@ __device__ __forceinline__ void noiseQuads(qreal (&xr)[1 << R], qreal (&xi)[1 <<
     for (int e = 0; e < (1 << R); ++e) {
         if (((e >> P) & 1) || ((e >> Q) & 1)) continue;
         const int e10 = e | (1 << P), e01 = e | (1 << Q), e11 = e10 | e01;
+        if (KIND == kFDensCollapse) {  // reference QuEST_cpu.c:778-852: kept block divided by the outcome probability
+            const int keep = (c1 != 0) ? e11 : e, drop = (c1 != 0) ? e : e11;
+            xr[keep] /= c0; xi[keep] /= c0;
+            xr[drop] = 0; xi[drop] = 0;
+            xr[e10] = 0; xi[e10] = 0;
+            xr[e01] = 0; xi[e01] = 0;
+            continue;
+        }
         xr[e10] = c0 * xr[e10]; xi[e10] = c0 * xi[e10];
         xr[e01] = c0 * xr[e01]; xi[e01] = c0 * xi[e01];
         if (KIND == kFDepolarise) {
@@ -397,7 +405,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
                 if constexpr (NOISE) {
                     if (G.kind == kFDephase) onNoiseBits<kFDephase, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
                     else if (G.kind == kFDepolarise) onNoiseBits<kFDepolarise, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
-                    else onNoiseBits<kFDamping, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                    else if (G.kind == kFDamping) onNoiseBits<kFDamping, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                    else onNoiseBits<kFDensCollapse, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
                 }
                 break;
         }
