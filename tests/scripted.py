@@ -182,3 +182,73 @@ def check_mix_aliases(lib, env):
 
 ALL_CHECKS = [check_create, check_init_states, check_measure, check_measure_with_stats,
               check_inner_product_and_fidelity, check_qasm, check_density_is_conjugate_doubling, check_mix_aliases]
+
+
+def check_second_tier_surface(lib, env):
+    """The rest of the contract surface (SURVEY §8a last row, §8(f)3): clone, compare, initPureState, fidelity,
+    addDensityMatrix, initStateOfSingleQubit, reportState / initStateFromSingleFile round trip, two-qubit noise."""
+    import ctypes
+    n = 4
+    rng = np.random.default_rng(11)
+    psi = rng.standard_normal(16) + 1j * rng.standard_normal(16)
+    psi /= np.linalg.norm(psi)
+    a, b = lib.createQureg(n, env), lib.createQureg(n, env)
+    lib.set_state(a, psi)
+    lib.cloneQureg(b, a)
+    assert lib.compareStates(a, b, 1e-15) == 1
+    lib.pauliX(b, 2)
+    assert lib.compareStates(a, b, 1e-3) == 0
+    # initStateOfSingleQubit: qubit 1 fixed to |1>, the others uniform
+    lib.initStateOfSingleQubit(ctypes.byref(b), 1, 1)
+    want = np.array([(1 / np.sqrt(8)) if (k >> 1) & 1 else 0.0 for k in range(16)])
+    np.testing.assert_allclose(lib.get_state(b), want, atol=1e-15)
+    # density matrix from a pure state, fidelity and mixing
+    rho, sigma = lib.createDensityQureg(n, env), lib.createDensityQureg(n, env)
+    if lib.has("qb200_copyAmpsToHost"):
+        lib.initPureState(rho, a)
+    else:
+        # the reference's CPU initPureState has a sign slip (QuEST_cpu.c:1153-1154, SURVEY §2.3 #4): when this check
+        # runs against the reference library itself, load |psi><psi| directly instead
+        lib.set_state(rho, np.outer(psi, psi.conj()).flatten(order="F"))
+    np.testing.assert_allclose(lib.get_state(rho).reshape(16, 16, order="F"), np.outer(psi, psi.conj()), atol=1e-15)
+    np.testing.assert_allclose(lib.calcFidelity(rho, a), 1.0, atol=1e-13)
+    np.testing.assert_allclose(lib.calcPurity(rho), 1.0, atol=1e-13)
+    lib.initPlusState(sigma)
+    lib.addDensityMatrix(rho, 0.25, sigma)
+    mixed = 0.75 * np.outer(psi, psi.conj()) + 0.25 * np.full((16, 16), 1 / 16)
+    np.testing.assert_allclose(lib.get_state(rho).reshape(16, 16, order="F"), mixed, atol=1e-15)
+    np.testing.assert_allclose(lib.calcFidelity(rho, a), (psi.conj() @ mixed @ psi).real, atol=1e-13)
+    # two-qubit channels keep the trace and lower the purity
+    p0 = lib.calcPurity(rho)
+    lib.applyTwoQubitDephaseError(rho, 0, 2, 0.1)
+    lib.applyTwoQubitDepolariseError(rho, 3, 1, 0.2)
+    np.testing.assert_allclose(lib.calcTotalProb(rho), 1.0, atol=1e-13)
+    assert lib.calcPurity(rho) < p0
+    # reportState writes state_rank_0.csv in the working directory; initStateFromSingleFile reads it back
+    cwd = os.getcwd()
+    with tempfile.TemporaryDirectory() as tmp:
+        os.chdir(tmp)
+        try:
+            lib.reportState(a)
+            text = open("state_rank_0.csv").read().splitlines()
+            assert text[0] == "real, imag" and len(text) == 17
+            np.testing.assert_allclose([float(x) for x in text[1].split(",")], [psi[0].real, psi[0].imag], atol=1e-12)
+            if lib.has("initStateFromSingleFile"):
+                fn = lib.lib.initStateFromSingleFile
+                fn.argtypes = [ctypes.POINTER(lib.Qureg), ctypes.c_char_p, lib.QuESTEnv]
+                fn.restype = None
+                lib.initZeroState(b)
+                fn(ctypes.byref(b), b"state_rank_0.csv", env)
+                got = lib.get_state(b)
+                # the reference skips only '#' lines, so the "real, imag" header written by reportState takes the
+                # slot of amplitude 0 (which is left as it was) and every amplitude lands one index later
+                # (QuEST_cpu.c:1529-1546); reproduced, not "fixed"
+                np.testing.assert_allclose(got[1:], psi[:-1], atol=1e-11)
+                assert got[0] == 1.0
+        finally:
+            os.chdir(cwd)
+    for r in (a, b, rho, sigma):
+        lib.destroyQureg(r, env)
+
+
+ALL_CHECKS.append(check_second_tier_surface)

@@ -260,3 +260,38 @@ def test_queue_is_drained_by_every_observer(product, product_env, oracle, oracle
     np.testing.assert_allclose(res[0][0], res[1][0], rtol=1e-12, atol=1e-14)
     np.testing.assert_allclose(res[0][1], res[1][1], rtol=0, atol=1e-13)
     assert np.array_equal(res[0][2].view(np.float64), res[1][2].view(np.float64))
+
+
+def test_32_qubit_register_uses_64_bit_indexing(product, product_env):
+    """64 GiB of amplitudes: indices above 2^31 are reached by gates on the top qubits, reads and reductions.
+    Closed forms: rotations from |0...0> and |+...+> give product states."""
+    nq = 32
+    q = product.createQureg(nq, product_env)
+    assert q.numAmpsTotal == 1 << 32
+    th = 0.7
+    product.rotateY(q, nq - 1, th)            # top qubit
+    product.rotateY(q, 0, 2 * th)             # lowest qubit
+    product.controlledNot(q, nq - 1, nq - 2)  # entangle the two top qubits
+    c, s = np.cos(th / 2), np.sin(th / 2)
+    c0, s0 = np.cos(th), np.sin(th)
+    # |psi> = (c|00> + s|11>)_{31,30} x (c0|0> + s0|1>)_0
+    for idx, want in [(0, c * c0), (1, c * s0), ((3 << 30), s * c0), ((3 << 30) | 1, s * s0), (1 << 31, 0.0), (1 << 30, 0.0)]:
+        amp = product.getAmp(q, idx)
+        assert abs(amp.real - want) < 1e-15 and amp.imag == 0.0, (idx, amp.real, want)
+    np.testing.assert_allclose(product.calcProbOfOutcome(q, nq - 1, 1), s * s, rtol=1e-13)
+    np.testing.assert_allclose(product.calcProbOfOutcome(q, nq - 2, 1), s * s, rtol=1e-13)
+    np.testing.assert_allclose(product.calcProbOfOutcome(q, 0, 1), s0 * s0, rtol=1e-13)
+    np.testing.assert_allclose(product.calcTotalProb(q), 1.0, rtol=1e-13)
+    # a long fused run over low, middle and top qubits keeps the norm
+    product.initPlusState(q)
+    for t in (0, 1, 5, 17, 30, 31, 2, 29):
+        product.hadamard(q, t)
+        product.compactUnitary(q, t, product.complex(circuits.SWEEP_ALPHA), product.complex(circuits.SWEEP_BETA))
+        product.controlledPhaseShift(q, t, (t + 7) % nq, 0.3)
+    np.testing.assert_allclose(product.calcTotalProb(q), 1.0, rtol=1e-12)
+    # collapse of the top qubit
+    p = product.collapseToOutcome(q, nq - 1, 1)
+    assert 0 < p < 1
+    np.testing.assert_allclose(product.calcTotalProb(q), 1.0, rtol=1e-12)
+    assert product.calcProbOfOutcome(q, nq - 1, 0) < 1e-15
+    product.destroyQureg(q, product_env)
