@@ -315,6 +315,55 @@ __device__ __forceinline__ void onNoiseBits(int p, int q, qreal (&xr)[1 << R], q
     }
 }
 
+// The recorded gates, in program order, on the 2^R amplitudes a thread holds in registers.
+template <int R, bool NOISE>
+__device__ __forceinline__ void applyRecordedGates(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned long long base,
+                                                   const FusedLaunch& fl) {
+    constexpr int E = 1 << R;
+    (void)E;
+    for (int g = 0; g < fl.nGates; ++g) {
+        const FusedGate& G = fl.gates[g];
+        if ((base & G.outerMask) != G.outerMask) continue;
+        switch (G.kind) {
+            case kFMatrix: {
+                const OpMatrix op{G.c[0], G.c[1], G.c[2], G.c[3], G.c[4], G.c[5], G.c[6], G.c[7]};
+                if (G.regMask == 0)
+                    onTargetBitUnmasked<R>(G.pos, xr, xi, op);
+                else
+                    onTargetBit<R>(G.pos, xr, xi, G.regMask, op);
+                break;
+            }
+            case kFHadamard: {  // the API has no controlled hadamard: never masked
+                const OpHadamard op{G.c[0]};
+                onTargetBitUnmasked<R>(G.pos, xr, xi, op);
+                break;
+            }
+            case kFSwap:
+                onTargetBit<R>(G.pos, xr, xi, G.regMask, OpSwap{});
+                break;
+            case kFPauliY: {
+                const OpPauliY op{G.c[0]};
+                onTargetBit<R>(G.pos, xr, xi, G.regMask, op);
+                break;
+            }
+            case kFPhase:
+                onSelected<R>(G.regMask, xr, xi, DiagPhase{G.c[0], G.c[1]});
+                break;
+            case kFFlip:
+                onSelected<R>(G.regMask, xr, xi, DiagFlip{});
+                break;
+            default:
+                if constexpr (NOISE) {
+                    if (G.kind == kFDephase) onNoiseBits<kFDephase, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                    else if (G.kind == kFDepolarise) onNoiseBits<kFDepolarise, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                    else if (G.kind == kFDamping) onNoiseBits<kFDamping, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                    else onNoiseBits<kFDensCollapse, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+                }
+                break;
+        }
+    }
+}
+
 // NOISE selects the instantiation that also understands the density-matrix noise kinds; state-vector groups use the
 // leaner one.
 template <int R, int BLOCK, int MINB, bool NOISE>
@@ -370,47 +419,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
             xi[e] = load<1>(im + base + off[e]).v[0];
         }
     }
-    for (int g = 0; g < fl.nGates; ++g) {
-        const FusedGate& G = fl.gates[g];
-        if ((base & G.outerMask) != G.outerMask) continue;
-        switch (G.kind) {
-            case kFMatrix: {
-                const OpMatrix op{G.c[0], G.c[1], G.c[2], G.c[3], G.c[4], G.c[5], G.c[6], G.c[7]};
-                if (G.regMask == 0)
-                    onTargetBitUnmasked<R>(G.pos, xr, xi, op);
-                else
-                    onTargetBit<R>(G.pos, xr, xi, G.regMask, op);
-                break;
-            }
-            case kFHadamard: {  // the API has no controlled hadamard: never masked
-                const OpHadamard op{G.c[0]};
-                onTargetBitUnmasked<R>(G.pos, xr, xi, op);
-                break;
-            }
-            case kFSwap:
-                onTargetBit<R>(G.pos, xr, xi, G.regMask, OpSwap{});
-                break;
-            case kFPauliY: {
-                const OpPauliY op{G.c[0]};
-                onTargetBit<R>(G.pos, xr, xi, G.regMask, op);
-                break;
-            }
-            case kFPhase:
-                onSelected<R>(G.regMask, xr, xi, DiagPhase{G.c[0], G.c[1]});
-                break;
-            case kFFlip:
-                onSelected<R>(G.regMask, xr, xi, DiagFlip{});
-                break;
-            default:
-                if constexpr (NOISE) {
-                    if (G.kind == kFDephase) onNoiseBits<kFDephase, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
-                    else if (G.kind == kFDepolarise) onNoiseBits<kFDepolarise, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
-                    else if (G.kind == kFDamping) onNoiseBits<kFDamping, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
-                    else onNoiseBits<kFDensCollapse, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
-                }
-                break;
-        }
-    }
+    applyRecordedGates<R, NOISE>(xr, xi, base, fl);
     if (lowRun == 4) {
 #pragma unroll
         for (int e = 0; e < E; e += 4) {
