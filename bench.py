@@ -36,10 +36,6 @@ sys.path.insert(0, ROOT)
 
 from quest_b200 import capi, circuits  # noqa: E402
 
-BYTES_PER_AMP = {"hadamard": 32, "compactUnitary": 32, "rotateY": 32, "controlledNot": 16,
-                 "multiControlledPhaseShift": 4, "measure": 32}  # algorithmic, double precision
-
-
 def target_of(op):
     """Target qubit of a circuit op (controlledNot carries its control first)."""
     name = op[0]

@@ -22,19 +22,9 @@ constexpr int kBlock = 256;
 // 2x2 operators on one amplitude pair (up = target bit 0, lo = target bit 1)
 // ======================================================================================================
 
-// [[alpha, -conj(beta)], [beta, conj(alpha)]]           (reference QuEST_cpu.c:1614-1623)
-struct OpCompact {
-    qreal aR, aI, bR, bI;
-    __device__ __forceinline__ void operator()(qreal& uR, qreal& uI, qreal& lR, qreal& lI) const {
-        const qreal nuR = aR * uR - aI * uI - bR * lR - bI * lI;
-        const qreal nuI = aR * uI + aI * uR - bR * lI + bI * lR;
-        const qreal nlR = bR * uR - bI * uI + aR * lR + aI * lI;
-        const qreal nlI = bR * uI + bI * uR + aR * lI - aI * lR;
-        uR = nuR; uI = nuI; lR = nlR; lI = nlI;
-    }
-};
-
-// general 2x2                                             (reference QuEST_cpu.c:1672-1681)
+// general 2x2 (reference QuEST_cpu.c:1672-1681).  Also serves compactUnitary [[a, -conj(b)], [b, conj(a)]]
+// (QuEST_cpu.c:1614-1623): with r01=-bR, i01=bI, r10=bR, i10=bI, r11=aR, i11=-aI every expression below evaluates to
+// the same IEEE bits as the reference's compact form, because x + (-b)*y == x - b*y and x - (-a)*y == x + a*y exactly.
 struct OpMatrix {
     qreal r00, i00, r01, i01, r10, i10, r11, i11;
     __device__ __forceinline__ void operator()(qreal& uR, qreal& uI, qreal& lR, qreal& lI) const {
@@ -193,7 +183,7 @@ __global__ void __launch_bounds__(kBlock) k_diag(qreal* __restrict__ re, qreal* 
 // fused multi-gate pass (qb_fuse.h): each thread owns the 2^R amplitudes spanned by the R fused qubits, keeps them
 // in registers, and runs the recorded gates over them in program order.  Dense gates use exactly the per-pair
 // arithmetic of the single-gate kernels (OpMatrix also serves compactUnitary: with r01=-bR, i01=bI, r10=bR,
-// i10=bI, r11=aR, i11=-aI its expression tree evaluates to the same IEEE bits as OpCompact).
+// i10=bI, r11=aR, i11=-aI its expression tree evaluates to the same IEEE bits as the reference's compact form).
 // ======================================================================================================
 
 struct FusedLaunch {

@@ -25,6 +25,8 @@ def main():
     lib = capi.load_product()
     env = lib.createQuESTEnv()
     lib.lib.qb200_getStream.restype = ctypes.c_void_p
+    lib.lib.qb200_setFusion.argtypes = [ctypes.c_int]
+    lib.lib.qb200_setFusion(0)  # this tool times the single-gate kernels: one launch per call
     stream = torch.cuda.ExternalStream(lib.lib.qb200_getStream())
     nq = args.qubits
     peaks = json.load(open("MEASURED_PEAKS.json")) if os.path.exists("MEASURED_PEAKS.json") else {"hbm_gbs": 6650.0}
