@@ -21,6 +21,8 @@ def main():
     ap.add_argument("--qft-qubits", type=int, default=30)
     ap.add_argument("--dm-qubits", type=int, default=15)
     ap.add_argument("--layers", type=int, default=10)
+    ap.add_argument("--config1-qubits", type=int, default=24)
+    ap.add_argument("--skip-config1", action="store_true")
     ap.add_argument("--out", default="gpurun_out/config_bench.json")
     args = ap.parse_args()
     lib = capi.load_product()
@@ -53,6 +55,38 @@ def main():
         print(label, {k: (v if not isinstance(v, dict) else {kk: vv for kk, vv in v.items() if kk != "scalars"}) for k, v in res.items()}, flush=True)
         return res
 
+    # configs[0]: 24-qubit layered circuit (hadamard / rotateY / controlledNot on every qubit, 20 layers = 1440 gates):
+    # the reference's CPU/OpenMP build on this box's cores next to the GPU library, then every amplitude compared
+    if os.path.isfile(capi.REFERENCE_LIB) and not args.skip_config1:
+        n1 = args.config1_qubits
+        ops1 = circuits.config1_layers(n1, 20)
+        cpu = capi.load(capi.REFERENCE_LIB)
+        cenv = cpu.createQuESTEnv()
+        cq = cpu.createQureg(n1, cenv)
+        t0 = time.perf_counter()
+        circuits.run_circuit(cpu, cq, ops1)
+        cpu_s = time.perf_counter() - t0
+        want = cpu.get_state(cq)
+        cpu.destroyQureg(cq, cenv)
+        lib.lib.qb200_setFusion(1)
+        gq = lib.createQureg(n1, env)
+        circuits.run_circuit(lib, gq, ops1[:72])
+        lib.initZeroState(gq)
+        lib.syncQuESTEnv(env)
+        t0 = time.perf_counter()
+        circuits.run_circuit(lib, gq, ops1)
+        lib.syncQuESTEnv(env)
+        gpu_s = time.perf_counter() - t0
+        got = lib.get_state(gq)
+        lib.destroyQureg(gq, env)
+        out[f"config1_layers_{n1}q"] = {
+            "gates": len(ops1), "cpu_reference_seconds": cpu_s, "cpu_gates_per_s": len(ops1) / cpu_s,
+            "cpu_threads": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count())), "gpu_seconds": gpu_s,
+            "gpu_gates_per_s": len(ops1) / gpu_s, "speedup": cpu_s / gpu_s,
+            "all_amplitudes_bit_identical": bool(np.array_equal(got.view(np.float64), want.view(np.float64))),
+            "max_abs_diff": float(np.abs(got - want).max())}
+        print(f"config1_layers_{n1}q", out[f"config1_layers_{n1}q"], flush=True)
+
     nq = args.qft_qubits
     r = timed(lambda: lib.createQureg(nq, env), lambda q: lib.initClassicalState(q, 0x2AAAAAAA & ((1 << nq) - 1)),
               circuits.config3_qft(nq), f"config3_qft_{nq}q")
@@ -66,7 +100,8 @@ def main():
     out[f"config4_noisy_density_{nd}q"]["purity_per_layer"] = r["fused"]["scalars"]
     for v in out.values():
         for m in ("gate_at_a_time", "fused"):
-            v[m].pop("scalars", None)
+            if m in v:
+                v[m].pop("scalars", None)
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(out, open(args.out, "w"), indent=1)
 

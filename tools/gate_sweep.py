@@ -78,9 +78,8 @@ def main():
             gbs = bytes_per_amp * N / (med * 1e-3) / 1e9
             rows.append({"gate": name, "target": t, "ms_median": med, "ms_best": best, "GBps": gbs, "frac_measured": gbs / peak})
             print(f"{name:20s} t={t:2d}  {med:8.3f} ms (best {best:8.3f})  {gbs:8.1f} GB/s  {gbs / peak:5.2f} of measured", flush=True)
-    extra = {"calcTotalProb": (lambda: lib.calcTotalProb(q), 16)}
-    if args.density:
-        extra["calcPurity"] = (lambda: lib.calcPurity(q), 16)
+    # (the trace of a density matrix reads only 2^q diagonal elements: latency-bound, not listed)
+    extra = {"calcPurity": (lambda: lib.calcPurity(q), 16)} if args.density else {"calcTotalProb": (lambda: lib.calcTotalProb(q), 16)}
     for name, (fn, bpa) in extra.items():
         med, best = timed(fn)
         gbs = bpa * N / (med * 1e-3) / 1e9
