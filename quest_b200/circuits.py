@@ -263,3 +263,101 @@ def config5_sharded(nq: int = 34, layers: int = 3, seed: int = 34) -> List[Op]:
     ops.append(("measure", nq // 2))
     ops.append(("calcTotalProb",))
     return ops
+
+
+# ---- API fuzz: several registers, gates interleaved with every kind of observer and copy ----------------------
+
+def random_api_sequence(nq: int, depth: int, seed: int):
+    """Random calls over two state-vectors (a, b) and two density matrices (r, s) of nq qubits: gates, noise,
+    initialisers, partial setAmps, clone, inner product, fidelity, compare, mixing, probabilities, measurement.
+    Exercises every path that must drain a register's recorded gates (and restore its qubit layout) first."""
+    rng = random.Random(seed)
+    calls = []
+    gate_pool = DENSE_1Q + DIAG_1Q + CTRL_DENSE + CTRL_DIAG + MULTI
+    for _ in range(depth):
+        kind = rng.random()
+        if kind < 0.62:
+            reg = rng.choice("abrs")
+            ops = random_circuit(nq, 3, rng.randrange(1 << 30), density=False, measure=False, families=gate_pool)
+            calls += [("gate", reg, op) for op in ops[:2] if op[0] in gate_pool]
+        elif kind < 0.70:
+            reg = rng.choice("rs")
+            calls.append(("gate", reg, (rng.choice(NOISE), rng.randrange(nq), rng.uniform(0, 0.3))))
+        elif kind < 0.74:
+            calls.append(("clone", *rng.choice([("a", "b"), ("b", "a"), ("r", "s"), ("s", "r")])))
+        elif kind < 0.78:
+            calls.append(("inner", "a", "b"))
+        elif kind < 0.81:
+            calls.append(("fidelity", rng.choice("ar"), "b"))
+        elif kind < 0.84:
+            calls.append(("compare", *rng.choice([("a", "b"), ("r", "s")])))
+        elif kind < 0.87:
+            calls.append(("mix", "r", rng.uniform(0, 1), "s"))
+        elif kind < 0.90:
+            start = rng.randrange(1 << nq)
+            n = rng.randint(1, (1 << nq) - start)
+            vals = [complex(rng.uniform(-0.1, 0.1), rng.uniform(-0.1, 0.1)) for _ in range(min(n, 7))]
+            calls.append(("setamps", rng.choice("ab"), start, vals))
+        elif kind < 0.93:
+            calls.append(("init", rng.choice("abrs"), rng.choice(["zero", "plus", "debug", "classical"]), rng.randrange(1 << nq)))
+        elif kind < 0.96:
+            calls.append(("prob", rng.choice("abrs"), rng.randrange(nq), rng.randrange(2)))
+        elif kind < 0.98:
+            calls.append(("getamp", rng.choice("ab"), rng.randrange(1 << nq)))
+        else:
+            calls.append(("purity", rng.choice("rs")))
+    calls += [("totalprob", r) for r in "abrs"]
+    return calls
+
+
+def run_api_sequence(lib, env, nq: int, calls, seed: int):
+    """Replay `calls`; returns (scalars, {register: final state})."""
+    import ctypes
+    regs = {"a": lib.createQureg(nq, env), "b": lib.createQureg(nq, env),
+            "r": lib.createDensityQureg(nq, env), "s": lib.createDensityQureg(nq, env)}
+    for name, q in regs.items():
+        prepare(lib, q, seed + ord(name))
+        if q.isDensityMatrix:
+            lib.rotateY(q, 0, 0.3 + 0.1 * ord(name))
+    key = (ctypes.c_ulong * 1)(seed)
+    lib.seedQuEST(key, 1)
+    out = []
+    labels = []  # which call produced each scalar (for diagnostics)
+    for ci, c in enumerate(calls):
+        k = c[0]
+        n_before = len(out)
+        if k == "gate":
+            v = apply_op(lib, regs[c[1]], c[2])
+            if v is not None:
+                out.append(v)
+        elif k == "clone":
+            lib.cloneQureg(regs[c[1]], regs[c[2]])
+        elif k == "inner":
+            z = lib.calcInnerProduct(regs[c[1]], regs[c[2]])
+            out += [z.real, z.imag]
+        elif k == "fidelity":
+            out.append(lib.calcFidelity(regs[c[1]], regs[c[2]]))
+        elif k == "compare":
+            out.append(float(lib.compareStates(regs[c[1]], regs[c[2]], 1e-9)))
+        elif k == "mix":
+            lib.addDensityMatrix(regs[c[1]], c[2], regs[c[3]])
+        elif k == "setamps":
+            lib.set_state(regs[c[1]], np.array(c[3]), start=min(c[2], (1 << nq) - len(c[3])))
+        elif k == "init":
+            q = regs[c[1]]
+            {"zero": lib.initZeroState, "plus": lib.initPlusState, "debug": lib.initStateDebug}.get(c[2], lambda r: lib.initClassicalState(r, c[3]))(q)
+        elif k == "prob":
+            out.append(lib.calcProbOfOutcome(regs[c[1]], c[2], c[3]))
+        elif k == "getamp":
+            z = lib.getAmp(regs[c[1]], c[2])
+            out += [z.real, z.imag]
+        elif k == "purity":
+            out.append(lib.calcPurity(regs[c[1]]))
+        elif k == "totalprob":
+            out.append(lib.calcTotalProb(regs[c[1]]))
+        labels += [(ci, c[:3])] * (len(out) - n_before)
+    run_api_sequence.last_labels = labels
+    states = {name: lib.get_state(q) for name, q in regs.items()}
+    for q in regs.values():
+        lib.destroyQureg(q, env)
+    return np.array(out, dtype=np.float64), states

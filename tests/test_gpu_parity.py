@@ -295,3 +295,15 @@ def test_32_qubit_register_uses_64_bit_indexing(product, product_env):
     np.testing.assert_allclose(product.calcTotalProb(q), 1.0, rtol=1e-12)
     assert product.calcProbOfOutcome(q, nq - 1, 0) < 1e-15
     product.destroyQureg(q, product_env)
+
+
+@pytest.mark.parametrize("nq,seed", [(4, 401), (6, 402), (9, 403), (11, 404)])
+def test_api_fuzz_vs_oracle(product, product_env, oracle, oracle_env, nq, seed):
+    """Random multi-register API sequences - gates interleaved with clone, inner product, fidelity, compare, mixing,
+    partial setAmps, re-initialisation, probabilities, getAmp - through the fusion queue, against the CPU oracle."""
+    calls = circuits.random_api_sequence(nq, 400, seed)
+    a, sa = circuits.run_api_sequence(product, product_env, nq, calls, seed)
+    b, sb = circuits.run_api_sequence(oracle, oracle_env, nq, calls, seed)
+    np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-13)
+    for k in sa:
+        np.testing.assert_allclose(sa[k], sb[k], rtol=0, atol=1e-13 * max(1.0, np.abs(sb[k]).max()))

@@ -78,3 +78,15 @@ def test_oracle_vs_live_reference(oracle, oracle_env, reference, reference_env, 
         states.append(lib.get_state(q))
         lib.destroyQureg(q, env)
     assert np.array_equal(states[0].view(np.float64), states[1].view(np.float64))
+
+
+@pytest.mark.parametrize("nq,seed", [(4, 401), (6, 402)])
+def test_api_fuzz_oracle_vs_live_reference(oracle, oracle_env, reference, reference_env, nq, seed):
+    """Random multi-register API sequences (gates, noise, copies, observers): oracle and reference agree bit for bit
+    (the sequence avoids initPureState, whose reference implementation has a known sign slip)."""
+    calls = circuits.random_api_sequence(nq, 300, seed)
+    a, sa = circuits.run_api_sequence(oracle, oracle_env, nq, calls, seed)
+    b, sb = circuits.run_api_sequence(reference, reference_env, nq, calls, seed)
+    np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-13)
+    for k in sa:
+        np.testing.assert_allclose(sa[k], sb[k], rtol=0, atol=1e-13 * max(1.0, np.abs(sb[k]).max()))

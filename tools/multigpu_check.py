@@ -98,6 +98,32 @@ def main():
             ok = ok and good
             print(f"density case {case}: {nd}-qubit density matrix over {world} GPUs, {len(ops)} ops: bit-exact={same_bits} "
                   f"scalars_ok={scal_ok} -> {'PASS' if good else 'FAIL'}", flush=True)
+    # multi-register API fuzz: copies and observers interleaved with gates on sharded registers
+    for case, (nq, seed) in enumerate([(9, 321), (12, 322)]):
+        calls = [c for c in circuits.random_api_sequence(nq, 300, seed) if not (c[0] == "fidelity" and c[1] == "r")]
+        scal, states = circuits.run_api_sequence(lib, env, nq, calls, seed)
+        parts = {}
+        for name in sorted(states):
+            shard = states[name]
+            gathered = [torch.empty(2 * shard.size, dtype=torch.float64) for _ in range(world)] if rank == 0 else None
+            dist.gather(torch.from_numpy(shard.view(np.float64).copy()), gathered, dst=0)
+            if rank == 0:
+                parts[name] = np.concatenate([t.numpy().view(np.complex128) for t in gathered])
+        if rank == 0:
+            cscal, cstates = circuits.run_api_sequence(cpu, cenv, nq, calls, seed)
+            # the CPU checker sums up to 4^nq terms sequentially (one OpenMP thread under torchrun): its own rounding
+            # error bound is ~N*eps, far above the GPU's tree reduction; compare scalars at that bound
+            tol = max(1e-12, 4.0 ** nq * 4.5e-16)
+            scal_ok = np.allclose(scal, cscal, rtol=tol, atol=1e-13)
+            st_ok = all(np.allclose(parts[k], cstates[k], rtol=0, atol=1e-13 * max(1.0, np.abs(cstates[k]).max())) for k in parts)
+            good = scal_ok and st_ok
+            ok = ok and good
+            if not scal_ok:
+                bad = np.nonzero(~np.isclose(scal, cscal, rtol=tol, atol=1e-13))[0]
+                for i in bad[:6]:
+                    print("   scalar", i, circuits.run_api_sequence.last_labels[i], "gpu", scal[i], "cpu", cscal[i], flush=True)
+            print(f"api fuzz case {case}: {nq} qubits, {len(calls)} calls over 4 registers on {world} GPUs: scalars_ok={scal_ok} "
+                  f"states_ok={st_ok} -> {'PASS' if good else 'FAIL'}", flush=True)
     flag = torch.tensor([1 if ok else 0])
     dist.broadcast(flag, 0)
     lib.destroyQuESTEnv(env)
