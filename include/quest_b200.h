@@ -33,6 +33,14 @@ int qb200_getFusion(void);
 void qb200_flush(void);
 void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long* fusedGates);
 
+/* Arithmetic of the fused pass.  0 (default): every product and sum is rounded separately, exactly as the reference's
+ * CPU build does (gcc without FMA), so amplitudes are bit-identical to it.  1 (or QUEST_B200_FMA=1): products feeding
+ * a sum may be contracted into fused multiply-adds - fewer fp64 instructions per gate, results within an ulp or two
+ * per gate of the exact mode (inside the 1e-12 bar, not bit-identical).  Pending gates run under the old setting.
+ * No reference counterpart: the reference's precision is a compile-time choice (QuEST_precision.h). */
+void qb200_setArithmetic(int contracted);
+int qb200_getArithmetic(void);
+
 /* Sharded registers (WORLD_SIZE > 1).  With remapping enabled (default; QUEST_B200_REMAP=0 disables) a dense gate on a
  * qubit that selects the GPU first makes that qubit local by exchanging it with the least recently used local qubit
  * - half a shard over NVLink - and later gates on it cost no communication; the reference exchanges whole shards for

@@ -267,10 +267,12 @@ def config5_sharded(nq: int = 34, layers: int = 3, seed: int = 34) -> List[Op]:
 
 # ---- API fuzz: several registers, gates interleaved with every kind of observer and copy ----------------------
 
-def random_api_sequence(nq: int, depth: int, seed: int):
+def random_api_sequence(nq: int, depth: int, seed: int, extended: bool = False):
     """Random calls over two state-vectors (a, b) and two density matrices (r, s) of nq qubits: gates, noise,
     initialisers, partial setAmps, clone, inner product, fidelity, compare, mixing, probabilities, measurement.
-    Exercises every path that must drain a register's recorded gates (and restore its qubit layout) first."""
+    Exercises every path that must drain a register's recorded gates (and restore its qubit layout) first.
+    extended=True adds initPureState (whose reference build has a sign slip, so only product-vs-oracle runs use it)
+    and the two-qubit noise channels."""
     rng = random.Random(seed)
     calls = []
     gate_pool = DENSE_1Q + DIAG_1Q + CTRL_DENSE + CTRL_DIAG + MULTI
@@ -306,6 +308,12 @@ def random_api_sequence(nq: int, depth: int, seed: int):
             calls.append(("getamp", rng.choice("ab"), rng.randrange(1 << nq)))
         else:
             calls.append(("purity", rng.choice("rs")))
+        if extended and rng.random() < 0.06:
+            if rng.random() < 0.4:
+                calls.append(("initpure", rng.choice("rs"), rng.choice("ab")))
+            else:
+                t1, t2 = rng.sample(range(nq), 2)
+                calls.append(("gate", rng.choice("rs"), (rng.choice(NOISE2), t1, t2, rng.uniform(0, 0.3))))
     calls += [("totalprob", r) for r in "abrs"]
     return calls
 
@@ -353,6 +361,8 @@ def run_api_sequence(lib, env, nq: int, calls, seed: int):
             out += [z.real, z.imag]
         elif k == "purity":
             out.append(lib.calcPurity(regs[c[1]]))
+        elif k == "initpure":
+            lib.initPureState(regs[c[1]], regs[c[2]])
         elif k == "totalprob":
             out.append(lib.calcTotalProb(regs[c[1]]))
         labels += [(ci, c[:3])] * (len(out) - n_before)

@@ -66,7 +66,7 @@ struct Engine {
     unsigned long long launches = 0;
     bool fuse = true;               // QUEST_B200_FUSE / qb200_setFusion: record gates and run them in fused passes
     unsigned long long fusedLaunches = 0, fusedGates = 0;
-    int fuseBlock = 128;            // QUEST_B200_FUSE_BLOCK: threads per CTA of the fused kernel (128 or 256)
+    bool contract = false;          // QUEST_B200_FMA / qb200_setArithmetic: fused pass may contract a*b+c into fma
     bool remap = true;              // QUEST_B200_REMAP: make shard-selecting qubits local by slot exchange
     unsigned long long slotSwaps = 0;
     bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
@@ -281,13 +281,22 @@ void flush(const Qureg& q) {
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
     const std::vector<FusedGroup> groups = groupOps(ops, r->localBits);
+#ifndef QB_FUSED_MINB
+#define QB_FUSED_MINB 4
+#endif
     static FusedLaunch fl;  // ~8.5 KB: passed by value as the kernel parameter block
     for (const FusedGroup& grp : groups) {
         if (grp.count == 1) {
             runOpNow(q, ops[grp.first]);
             continue;
         }
-        for (int i = 0; i < grp.count; ++i) fl.gates[i] = describe(ops[grp.first + i], grp.bits);
+        for (int i = 0; i < grp.count; ++i) {
+            const FusedGate fg = describe(ops[grp.first + i], grp.bits);
+            fl.ctl[i] = GateCtl{opcodeOf(fg), fg.regMask};
+            fl.outerMask[i] = fg.outerMask;
+            std::memcpy(fl.c[i], fg.c, sizeof fg.c);
+        }
+        fl.ctl[grp.count] = GateCtl{0, 0};
         for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = grp.bits[j];
         fl.nGates = grp.count;
         fl.nThreads = (u64)r->n >> kFuseBits;
@@ -302,11 +311,11 @@ void flush(const Qureg& q) {
         for (int i = 0; i < grp.count; ++i) noisy = noisy || isNoise(ops[grp.first + i].kind);
         const unsigned int nb128 = (unsigned int)((fl.nThreads + 127) / 128);
         if (noisy)
-            k_fused<kFuseBits, 128, 4, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
-        else if (g.fuseBlock == 256)
-            k_fused<kFuseBits, 256, 2, false><<<blocksFor(fl.nThreads), 256, 0, g.stream>>>(r->re, r->im, fl);
+            k_fused<kFuseBits, 128, QB_FUSED_MINB, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+        else if (g.contract)
+            k_fused<kFuseBits, 128, QB_FUSED_MINB, false, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
         else
-            k_fused<kFuseBits, 128, 4, false><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+            k_fused<kFuseBits, 128, QB_FUSED_MINB, false><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
         launched();
         if (g.timeFused) {
             CUDA_OK(cudaEventRecord(e1, g.stream));
@@ -605,7 +614,7 @@ QuESTEnv createQuESTEnv(void) {
     CUDA_OK(cudaMalloc(&g.dResult, 4 * sizeof(double)));
     CUDA_OK(cudaHostAlloc(&g.hResult, 4 * sizeof(double), cudaHostAllocDefault));
     if (const char* s = std::getenv("QUEST_B200_FUSE")) g.fuse = std::atoi(s) != 0;
-    if (const char* s = std::getenv("QUEST_B200_FUSE_BLOCK")) g.fuseBlock = std::atoi(s);
+    if (const char* s = std::getenv("QUEST_B200_FMA")) g.contract = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_REMAP")) g.remap = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_VEC")) {
         int v = std::atoi(s);
@@ -827,12 +836,40 @@ void densmatr_initClassicalState(Qureg q, idx_t stateInd) {
     setOneGlobal(q, (dim + 1) * stateInd, 1, 0);
 }
 
+// A whole copy of a (much smaller) state-vector next to a density-matrix shard.  One GPU: the register itself.
+// Sharded: an ncclAllGather of the shards into a temporary - the exchange the reference makes with MPI_Allgather
+// into pairStateVec (copyVecIntoMatrixPairState, QuEST_cpu_distributed.c:373-403).
+struct WholeState {
+    const qreal *re, *im;
+    qreal* owned;
+};
+static WholeState wholeStateOf(const Qureg& psi) {
+    QuregRec* p = canon(psi);
+    if (g.world == 1) return WholeState{p->re, p->im, nullptr};
+    const size_t shardBytes = (size_t)p->n * sizeof(qreal), total = shardBytes * g.world;
+    qreal* buf = nullptr;
+    CUDA_OK(cudaMalloc(&buf, 2 * total));
+    qreal* bufIm = buf + (size_t)p->n * g.world;
+    comm::allGatherBytes(p->re, buf, shardBytes, g.stream);
+    comm::allGatherBytes(p->im, bufIm, shardBytes, g.stream);
+    return WholeState{buf, bufIm, buf};
+}
+static void release(WholeState& w) {
+    if (!w.owned) return;
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+    CUDA_OK(cudaFree(w.owned));
+    w.owned = nullptr;
+}
+
+// this rank's shard holds whole columns [chunkId * n / dim, ...) of the density matrix (QuEST_cpu.c:1107-1150)
 void densmatr_initPureState(Qureg rho, Qureg psi) {
-    if (g.world > 1) comm::unsupported("initPureState on a sharded density matrix");
-    QuregRec *d = fresh(rho), *p = canon(psi);
-    k_outerProduct<<<blocksFor((u64)d->n), kBlock, 0, g.stream>>>(d->re, d->im, p->re, p->im, (u64)psi.numAmpsTotal,
-                                                                 (u64)d->n);
+    if (rho.numAmpsPerChunk < psi.numAmpsTotal) comm::unsupported("a density-matrix shard smaller than one column");
+    WholeState w = wholeStateOf(psi);
+    QuregRec* d = fresh(rho);
+    k_outerProduct<<<blocksFor((u64)d->n), kBlock, 0, g.stream>>>(d->re, d->im, w.re, w.im, (u64)psi.numAmpsTotal,
+                                                                 (u64)d->n, (u64)rho.chunkId * (u64)d->n);
     launched();
+    release(w);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -918,15 +955,18 @@ qreal densmatr_calcProbOfOutcome(Qureg q, const int t, int outcome) {
     return p;
 }
 
+// each rank sums over the columns it holds, the partial sums meet in fetchResult (QuEST_cpu_distributed.c:407-420)
 qreal densmatr_calcFidelity(Qureg rho, Qureg psi) {
-    if (g.world > 1) comm::unsupported("calcFidelity on a sharded density matrix");
-    QuregRec *d = canon(rho), *p = canon(psi);
-    const u64 dim = (u64)psi.numAmpsTotal;
-    k_densFidelity<<<reduceBlocks(dim), kBlock, 0, g.stream>>>(d->re, d->im, p->re, p->im, dim, g.dPartials, g.dTicket,
-                                                              g.dResult);
+    if (rho.numAmpsPerChunk < psi.numAmpsTotal) comm::unsupported("a density-matrix shard smaller than one column");
+    WholeState w = wholeStateOf(psi);
+    QuregRec* d = canon(rho);
+    const u64 dim = (u64)psi.numAmpsTotal, nCols = (u64)d->n / dim;
+    k_densFidelity<<<reduceBlocks(dim), kBlock, 0, g.stream>>>(d->re, d->im, w.re, w.im, dim, (u64)rho.chunkId * nCols,
+                                                              nCols, g.dPartials, g.dTicket, g.dResult);
     launched();
     double s;
     fetchResult(1, &s);
+    release(w);
     return (qreal)s;
 }
 
@@ -1005,27 +1045,55 @@ void densmatr_oneQubitDamping(Qureg q, const int t, qreal damping) {
     submitNoise(q, kFDamping, t, dephase, damping, retain);
 }
 
-void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase) {
-    QuregRec* r = canon(q);
+// Diagonal in the amplitude index, so it runs in whatever layout the register is in: the four bits are looked up
+// in the qubit map and tested on the global index.
+static void dephase2Now(const Qureg& q, QuregRec* r, int q1, int q2, qreal retain) {
     const int n = q.numQubitsRepresented;
-    const qreal retain = 1 - dephase;
-    k_dephase2<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n, 1ull << q1,
-                                                             1ull << (q1 + n), 1ull << q2, 1ull << (q2 + n), retain);
+    const QubitMap& m = r->map;
+    k_dephase2<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n,
+                                                             1ull << m.phys[q1], 1ull << m.phys[q1 + n],
+                                                             1ull << m.phys[q2], 1ull << m.phys[q2 + n], retain);
     launched();
 }
 
+void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase) {
+    QuregRec* r = live(q);
+    const qreal retain = 1 - dephase;
+    dephase2Now(q, r, q1, q2, retain);
+}
+
+// Make every listed qubit of a sharded register local (half-shard slot exchanges), none evicting another.
+static void bringLocal(const Qureg& q, QuregRec* r, std::initializer_list<int> qubits, const char* what) {
+    if (g.world == 1) return;
+    u64 keep = 0;
+    for (int t : qubits) keep |= 1ull << t;
+    for (int t : qubits) {
+        if (r->map.phys[t] >= r->localBits) {
+            const SlotSwap sw = g.remap ? planSwapIn(r->map, t, keep) : SlotSwap{-1, -1};
+            if (sw.globalSlot < 0) comm::unsupported(what);
+            exchangeSlots(q, sw);
+        }
+        r->map.touch(t);
+    }
+}
+
+// The reference's distributed version exchanges whole shards up to three times (QuEST_cpu_distributed.c:724-806).
+// Here the column bits of the two qubits are first made local (at most log2(G) half-shard exchanges, none when an
+// earlier gate or channel already brought them in), after which the three sweeps are the single-GPU ones.
 void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
     if (level == 0) return;
-    if (g.world > 1) comm::unsupported("two-qubit depolarising on a sharded density matrix");
-    QuregRec* r = canon(q);
+    QuregRec* r = live(q);
     const int n = q.numQubitsRepresented;
+    bringLocal(q, r, {q1, q2, q1 + n, q2 + n},
+               "two-qubit depolarising across shards (with QUEST_B200_REMAP=0, or a shard too small to re-home its qubits)");
     // host scalars exactly as QuEST_cpu_local.c:43-48
     qreal eta = 2 / level;
     qreal delta = eta - 1 - sqrt((double)((eta - 1) * (eta - 1) - 1));
     qreal gamma = 1 + delta;
     gamma = 1 / (gamma * gamma * gamma);
-    densmatr_twoQubitDephase(q, q1, q2, level);
-    const u64 tot1 = (1ull << q1) | (1ull << (q1 + n)), tot2 = (1ull << q2) | (1ull << (q2 + n));
+    dephase2Now(q, r, q1, q2, 1 - level);
+    const QubitMap& m = r->map;
+    const u64 tot1 = (1ull << m.phys[q1]) | (1ull << m.phys[q1 + n]), tot2 = (1ull << m.phys[q2]) | (1ull << m.phys[q2 + n]);
     const unsigned int nb = blocksFor((u64)r->n);
     k_depol2Sweep<<<nb, kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, tot1, tot2, 0, delta, 1);
     launched();
@@ -1050,6 +1118,14 @@ void densmatr_addDensityMatrix(Qureg a, qreal p, Qureg b) {
 // ---------------------------------------------------------------------------------------------------------
 
 void* qb200_getStream(void) { return (void*)g.stream; }
+
+// Pending gates were recorded under the old setting: run them first.
+void qb200_setArithmetic(int contracted) {
+    requireEngine();
+    flushAll();
+    g.contract = contracted != 0;
+}
+int qb200_getArithmetic(void) { return g.contract ? 1 : 0; }
 
 void qb200_setStream(void* stream) {
     requireEngine();
@@ -1187,7 +1263,8 @@ int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* target
         for (int i = 0; i < grp.count; ++i) {
             const FusedGate fg = describe(ops[grp.first + i], grp.bits);
             unsigned long long* d = descOut + 4 * (grp.first + i);
-            d[0] = fg.kind; d[1] = fg.pos; d[2] = fg.regMask; d[3] = fg.outerMask;
+            d[0] = (unsigned long long)fg.kind | ((unsigned long long)opcodeOf(fg) << 8);  // what the kernel jumps on
+            d[1] = fg.pos; d[2] = fg.regMask; d[3] = fg.outerMask;
         }
     }
     return (int)groups.size();

@@ -145,6 +145,7 @@ struct Nccl {
     int (*CommInitRank)(NcclComm*, int, NcclId, int) = nullptr;
     int (*CommDestroy)(NcclComm) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, NcclComm, cudaStream_t) = nullptr;
     int (*Send)(const void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
     int (*Recv)(void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
@@ -152,7 +153,7 @@ struct Nccl {
     const char* (*GetErrorString)(int) = nullptr;
     NcclComm comm = nullptr;
 } nccl;
-constexpr int kNcclInt32 = 2, kNcclFloat64 = 8, kNcclSum = 0;
+constexpr int kNcclInt8 = 0, kNcclInt32 = 2, kNcclFloat64 = 8, kNcclSum = 0;
 
 #define NCCL_OK(call)                                                            \
     do {                                                                         \
@@ -175,6 +176,7 @@ void loadNccl() {
     nccl.CommInitRank = reinterpret_cast<decltype(nccl.CommInitRank)>(sym("ncclCommInitRank"));
     nccl.CommDestroy = reinterpret_cast<decltype(nccl.CommDestroy)>(sym("ncclCommDestroy"));
     nccl.AllReduce = reinterpret_cast<decltype(nccl.AllReduce)>(sym("ncclAllReduce"));
+    nccl.AllGather = reinterpret_cast<decltype(nccl.AllGather)>(sym("ncclAllGather"));
     nccl.Send = reinterpret_cast<decltype(nccl.Send)>(sym("ncclSend"));
     nccl.Recv = reinterpret_cast<decltype(nccl.Recv)>(sym("ncclRecv"));
     nccl.GroupStart = reinterpret_cast<decltype(nccl.GroupStart)>(sym("ncclGroupStart"));
@@ -265,6 +267,11 @@ void broadcastBytes(void* buf, size_t n, int root) {
 
 void allReduceSum(double* devBuf, int n, cudaStream_t stream) {
     NCCL_OK(nccl.AllReduce(devBuf, devBuf, (size_t)n, kNcclFloat64, kNcclSum, nccl.comm, stream));
+}
+
+// every rank's `bytesPerRank` bytes, concatenated in rank order, into devOut on every rank (stream-ordered)
+void allGatherBytes(const void* devIn, void* devOut, size_t bytesPerRank, cudaStream_t stream) {
+    NCCL_OK(nccl.AllGather(devIn, devOut, bytesPerRank, kNcclInt8, nccl.comm, stream));
 }
 
 // Exchange CUDA IPC handles of this register's shard and map every peer's shard into this process.

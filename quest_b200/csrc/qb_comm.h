@@ -24,6 +24,7 @@ void hostBarrier();
 int allAnd(int flag);
 void broadcastBytes(void* buf, size_t n, int root);
 void allReduceSum(double* devBuf, int n, cudaStream_t stream);
+void allGatherBytes(const void* devIn, void* devOut, size_t bytesPerRank, cudaStream_t stream);
 void registerShard(Qureg& q, void* re, void* im, long long n);
 void unregisterShard(const Qureg& q);
 [[noreturn]] void unsupported(const char* what);

@@ -19,7 +19,10 @@
 
 namespace qb {
 
-constexpr int kFuseBits = 4;       // qubits resolved in registers per launch (16 amplitudes per thread)
+#ifndef QB_FUSE_BITS
+#define QB_FUSE_BITS 4
+#endif
+constexpr int kFuseBits = QB_FUSE_BITS;  // qubits resolved in registers per launch (2^kFuseBits amplitudes per thread)
 constexpr int kMaxFusedGates = 96;  // gates per launch: descriptors travel as kernel parameters (constant bank)
 
 enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, kFPhase = 4, kFFlip = 5,
@@ -134,5 +137,43 @@ inline FusedGate describe(const PendingOp& op, const int* bits) {
     for (int k = 0; k < 8; ++k) fg.c[k] = op.c[k];
     return fg;
 }
+
+// ---- device dispatch ---------------------------------------------------------------------------------------
+// The kernel resolves a gate with ONE table jump: kind, target position (dense gates), register mask (diagonal
+// gates) or position pair (noise) are folded into a dense opcode on the host.
+enum FusedOpcode : int {
+    kOpMatrix = 0,      // +pos           uncontrolled among the fused qubits: straight-line arithmetic on all pairs
+    kOpMatrixCtl = 4,   // +pos           some control is a fused qubit: per-pair predicate on regMask
+    kOpHadamard = 8,    // +pos
+    kOpSwap = 12,       // +pos
+    kOpPauliY = 16,     // +pos           (20..31 unused: every family starts on a multiple of 4, diagonal ones of 16)
+    kOpPhase = 32,      // +regMask (16)
+    kOpFlip = 48,       // +regMask (16)
+    kOpNoise = 64,      // +(kind - kFDephase) * 6 + pairSlot(pos, pos2)
+    kOpCount = 88
+};
+
+// (p, q), p < q < 4  ->  0..5
+inline int pairSlot(int p, int q) { return p == 0 ? q - 1 : (p == 1 ? q + 1 : 5); }
+
+inline int opcodeOf(const FusedGate& g) {
+    switch (g.kind) {
+        case kFMatrix: return (g.regMask ? kOpMatrixCtl : kOpMatrix) + g.pos;
+        case kFHadamard: return kOpHadamard + g.pos;
+        case kFSwap: return kOpSwap + g.pos;
+        case kFPauliY: return kOpPauliY + g.pos;
+        case kFPhase: return kOpPhase + (int)(g.regMask & 15u);
+        case kFFlip: return kOpFlip + (int)(g.regMask & 15u);
+        default: return kOpNoise + (g.kind - kFDephase) * 6 + pairSlot(g.pos, g.pos2);
+    }
+}
+
+// What the kernel reads per gate: 8 bytes of control, the outer-bit condition and 8 coefficients, in separate arrays:
+// the conditions of 32 gates are folded into one bit mask before the gate loop, and the control word of the NEXT
+// gate is fetched while the current one computes.
+struct GateCtl {
+    int opcode;
+    unsigned int regMask;
+};
 
 }  // namespace qb

@@ -11,6 +11,8 @@
 // Reductions accumulate in double per thread, fold with warp shuffles, and finish in the last block to arrive.
 #pragma once
 
+#include <type_traits>
+
 #include "qb_device.cuh"
 #include "qb_fuse.h"
 
@@ -32,6 +34,20 @@ struct OpMatrix {
         const qreal nuI = r00 * uI + i00 * uR + r01 * lI + i01 * lR;
         const qreal nlR = r10 * uR - i10 * uI + r11 * lR - i11 * lI;
         const qreal nlI = r10 * uI + i10 * uR + r11 * lI + i11 * lR;
+        uR = nuR; uI = nuI; lR = nlR; lI = nlI;
+    }
+};
+
+// Same operator with the products contracted into fused multiply-adds: 4 fp64 instructions per output instead of 7,
+// one rounding per term instead of two.  NOT bit-identical to the reference's CPU arithmetic (differences of an
+// ulp or two per gate); used only by the fused pass and only when the host opted in (qb200_setArithmetic).
+struct OpMatrixFma {
+    qreal r00, i00, r01, i01, r10, i10, r11, i11;
+    __device__ __forceinline__ void operator()(qreal& uR, qreal& uI, qreal& lR, qreal& lI) const {
+        const qreal nuR = fma(-i01, lI, fma(r01, lR, fma(-i00, uI, r00 * uR)));
+        const qreal nuI = fma(i01, lR, fma(r01, lI, fma(i00, uR, r00 * uI)));
+        const qreal nlR = fma(-i11, lI, fma(r11, lR, fma(-i10, uI, r10 * uR)));
+        const qreal nlI = fma(i11, lR, fma(r11, lI, fma(i10, uR, r10 * uI)));
         uR = nuR; uI = nuI; lR = nlR; lI = nlI;
     }
 };
@@ -155,6 +171,13 @@ struct DiagPhase {  // x *= (c + i s)                        (reference QuEST_cp
         r = nr; m = nm;
     }
 };
+struct DiagPhaseFma {  // contracted form, see OpMatrixFma
+    qreal c, s;
+    __device__ __forceinline__ void operator()(qreal& r, qreal& m) const {
+        const qreal nr = fma(-s, m, c * r), nm = fma(c, m, s * r);
+        r = nr; m = nm;
+    }
+};
 struct DiagFlip {  // x = -x                                 (reference QuEST_cpu.c:3014-3015)
     __device__ __forceinline__ void operator()(qreal& r, qreal& m) const { r = -r; m = -m; }
 };
@@ -190,7 +213,9 @@ struct FusedLaunch {
     int pos[kFuseBits];                  // fused qubits, ascending (amplitude-index bit positions)
     int nGates;
     unsigned long long nThreads;
-    FusedGate gates[kMaxFusedGates];     // the recorded gates, read through the constant bank (kernel parameter)
+    GateCtl ctl[kMaxFusedGates + 2];     // padded: the loop fetches ctl[g+1] while gate g computes
+    unsigned long long outerMask[kMaxFusedGates];  // control/selecting bits outside the fused qubits
+    qreal c[kMaxFusedGates][8];          // coefficients (meaning per kind: qb_fuse.h PendingOp::c)
 };
 
 template <int P, int R, class PairFn>
@@ -212,26 +237,6 @@ __device__ __forceinline__ void forEveryPair(qreal (&xr)[1 << R], qreal (&xi)[1 
     }
 }
 
-template <int R, class PairFn>
-__device__ __forceinline__ void onTargetBitUnmasked(int pos, qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
-    switch (pos) {
-        case 0: forEveryPair<0, R>(xr, xi, fn); break;
-        case 1: forEveryPair<1, R>(xr, xi, fn); break;
-        case 2: forEveryPair<2, R>(xr, xi, fn); break;
-        default: forEveryPair<3, R>(xr, xi, fn); break;
-    }
-}
-
-template <int R, class PairFn>
-__device__ __forceinline__ void onTargetBit(int pos, qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
-    switch (pos) {
-        case 0: forEachPair<0, R>(xr, xi, regMask, fn); break;
-        case 1: forEachPair<1, R>(xr, xi, regMask, fn); break;
-        case 2: forEachPair<2, R>(xr, xi, regMask, fn); break;
-        default: forEachPair<3, R>(xr, xi, regMask, fn); break;
-    }
-}
-
 // Diagonal gates touch only the register elements whose fused-qubit bits contain MASK.  MASK is a compile-time
 // constant here (the caller switches on the 16 possible values), so exactly the selected elements are computed.
 template <int MASK, int R, class ElemFn>
@@ -239,28 +244,6 @@ __device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 <
 #pragma unroll
     for (int e = 0; e < (1 << R); ++e)
         if ((e & MASK) == MASK) fn(xr[e], xi[e]);
-}
-
-template <int R, class ElemFn>
-__device__ __forceinline__ void onSelected(unsigned int regMask, qreal (&xr)[1 << R], qreal (&xi)[1 << R], ElemFn fn) {
-    switch (regMask & 15u) {
-        case 0: forSelected<0, R>(xr, xi, fn); break;
-        case 1: forSelected<1, R>(xr, xi, fn); break;
-        case 2: forSelected<2, R>(xr, xi, fn); break;
-        case 3: forSelected<3, R>(xr, xi, fn); break;
-        case 4: forSelected<4, R>(xr, xi, fn); break;
-        case 5: forSelected<5, R>(xr, xi, fn); break;
-        case 6: forSelected<6, R>(xr, xi, fn); break;
-        case 7: forSelected<7, R>(xr, xi, fn); break;
-        case 8: forSelected<8, R>(xr, xi, fn); break;
-        case 9: forSelected<9, R>(xr, xi, fn); break;
-        case 10: forSelected<10, R>(xr, xi, fn); break;
-        case 11: forSelected<11, R>(xr, xi, fn); break;
-        case 12: forSelected<12, R>(xr, xi, fn); break;
-        case 13: forSelected<13, R>(xr, xi, fn); break;
-        case 14: forSelected<14, R>(xr, xi, fn); break;
-        default: forSelected<15, R>(xr, xi, fn); break;
-    }
 }
 
 // One-qubit noise channel on the (row bit P, column bit Q) block structure, P < Q register bits.  Same arithmetic as
@@ -293,73 +276,67 @@ __device__ __forceinline__ void noiseQuads(qreal (&xr)[1 << R], qreal (&xi)[1 <<
     }
 }
 
-template <int KIND, int R>
-__device__ __forceinline__ void onNoiseBits(int p, int q, qreal (&xr)[1 << R], qreal (&xi)[1 << R], qreal c0, qreal c1, qreal c2) {
-    switch (p * 4 + q) {
-        case 1: noiseQuads<KIND, 0, 1, R>(xr, xi, c0, c1, c2); break;
-        case 2: noiseQuads<KIND, 0, 2, R>(xr, xi, c0, c1, c2); break;
-        case 3: noiseQuads<KIND, 0, 3, R>(xr, xi, c0, c1, c2); break;
-        case 6: noiseQuads<KIND, 1, 2, R>(xr, xi, c0, c1, c2); break;
-        case 7: noiseQuads<KIND, 1, 3, R>(xr, xi, c0, c1, c2); break;
-        default: noiseQuads<KIND, 2, 3, R>(xr, xi, c0, c1, c2); break;
-    }
-}
+#define QB_CASE4(BASE, ...)                                                                 \
+    case (BASE) + 0: { constexpr int P = 0; __VA_ARGS__; } break;                           \
+    case (BASE) + 1: { constexpr int P = 1; __VA_ARGS__; } break;                           \
+    case (BASE) + 2: { constexpr int P = 2; __VA_ARGS__; } break;                           \
+    case (BASE) + 3: { constexpr int P = 3; __VA_ARGS__; } break;
+#define QB_ON_POS(...) if constexpr (P < R) { __VA_ARGS__; }
+#define QB_ON_MASK(...) if constexpr (M < (1 << R)) { __VA_ARGS__; }
+#define QB_NOISE_AT(KIND, SLOT, PP, QQ)                                                                  \
+    case kOpNoise + ((KIND) - kFDephase) * 6 + (SLOT):                                                   \
+        if constexpr ((QQ) < R) noiseQuads<KIND, PP, (QQ) < R ? (QQ) : (PP) + 1, R>(xr, xi, c[0], c[1], c[2]); \
+        break;
+#define QB_CASE16(BASE, ...)                                                                \
+    QB_CASE4((BASE) + 0, { constexpr int M = P; __VA_ARGS__; })                             \
+    QB_CASE4((BASE) + 4, { constexpr int M = 4 + P; __VA_ARGS__; })                         \
+    QB_CASE4((BASE) + 8, { constexpr int M = 8 + P; __VA_ARGS__; })                         \
+    QB_CASE4((BASE) + 12, { constexpr int M = 12 + P; __VA_ARGS__; })
+#define QB_CASE_NOISE(KIND)                                                                              \
+    QB_NOISE_AT(KIND, 0, 0, 1) QB_NOISE_AT(KIND, 1, 0, 2) QB_NOISE_AT(KIND, 2, 0, 3)                         \
+    QB_NOISE_AT(KIND, 3, 1, 2) QB_NOISE_AT(KIND, 4, 1, 3) QB_NOISE_AT(KIND, 5, 2, 3)
 
-// The recorded gates, in program order, on the 2^R amplitudes a thread holds in registers.
-template <int R, bool NOISE>
-__device__ __forceinline__ void applyRecordedGates(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned long long base,
-                                                   const FusedLaunch& fl) {
-    constexpr int E = 1 << R;
-    (void)E;
-    for (int g = 0; g < fl.nGates; ++g) {
-        const FusedGate& G = fl.gates[g];
-        if ((base & G.outerMask) != G.outerMask) continue;
-        switch (G.kind) {
-            case kFMatrix: {
-                const OpMatrix op{G.c[0], G.c[1], G.c[2], G.c[3], G.c[4], G.c[5], G.c[6], G.c[7]};
-                if (G.regMask == 0)
-                    onTargetBitUnmasked<R>(G.pos, xr, xi, op);
-                else
-                    onTargetBit<R>(G.pos, xr, xi, G.regMask, op);
-                break;
-            }
-            case kFHadamard: {  // the API has no controlled hadamard: never masked
-                const OpHadamard op{G.c[0]};
-                onTargetBitUnmasked<R>(G.pos, xr, xi, op);
-                break;
-            }
-            case kFSwap:
-                onTargetBit<R>(G.pos, xr, xi, G.regMask, OpSwap{});
-                break;
-            case kFPauliY: {
-                const OpPauliY op{G.c[0]};
-                onTargetBit<R>(G.pos, xr, xi, G.regMask, op);
-                break;
-            }
-            case kFPhase:
-                onSelected<R>(G.regMask, xr, xi, DiagPhase{G.c[0], G.c[1]});
-                break;
-            case kFFlip:
-                onSelected<R>(G.regMask, xr, xi, DiagFlip{});
-                break;
-            default:
-                if constexpr (NOISE) {
-                    if (G.kind == kFDephase) onNoiseBits<kFDephase, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
-                    else if (G.kind == kFDepolarise) onNoiseBits<kFDepolarise, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
-                    else if (G.kind == kFDamping) onNoiseBits<kFDamping, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
-                    else onNoiseBits<kFDensCollapse, R>(G.pos, G.pos2, xr, xi, G.c[0], G.c[1], G.c[2]);
+// One recorded gate on the 2^R amplitudes a thread holds in registers: a single jump on the host-made opcode
+// (qb_fuse.h) into straight-line code for that (kind, register position) combination.
+template <int R, bool NOISE, bool FMA>
+__device__ __forceinline__ void applyGate(int opcode, unsigned int regMask, const qreal (&c)[8], qreal (&xr)[1 << R],
+                                          qreal (&xi)[1 << R]) {
+    using Matrix = typename std::conditional<FMA, OpMatrixFma, OpMatrix>::type;
+    using DiagPhase = typename std::conditional<FMA, DiagPhaseFma, qb::DiagPhase>::type;
+    switch (opcode) {
+        QB_CASE4(kOpMatrix, QB_ON_POS(forEveryPair<P, R>(xr, xi, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
+        QB_CASE4(kOpMatrixCtl, QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
+        QB_CASE4(kOpHadamard, QB_ON_POS(forEveryPair<P, R>(xr, xi, OpHadamard{c[0]})))  // the API has no controlled hadamard
+        QB_CASE4(kOpSwap, QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpSwap{})))
+        QB_CASE4(kOpPauliY, QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpPauliY{c[0]})))
+        QB_CASE16(kOpPhase, QB_ON_MASK(forSelected<M, R>(xr, xi, DiagPhase{c[0], c[1]})))
+        QB_CASE16(kOpFlip, QB_ON_MASK(forSelected<M, R>(xr, xi, DiagFlip{})))
+        default:
+            if constexpr (NOISE) {
+                switch (opcode) {
+                    QB_CASE_NOISE(kFDephase)
+                    QB_CASE_NOISE(kFDepolarise)
+                    QB_CASE_NOISE(kFDamping)
+                    QB_CASE_NOISE(kFDensCollapse)
+                    default: break;
                 }
-                break;
-        }
+            }
+            break;
     }
 }
+#undef QB_CASE4
+#undef QB_ON_POS
+#undef QB_ON_MASK
+#undef QB_NOISE_AT
+#undef QB_CASE16
+#undef QB_CASE_NOISE
 
 // NOISE selects the instantiation that also understands the density-matrix noise kinds; state-vector groups use the
 // leaner one.
-template <int R, int BLOCK, int MINB, bool NOISE>
+template <int R, int BLOCK, int MINB, bool NOISE, bool FMA = false>
 __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, qreal* __restrict__ im,
                                                 const __grid_constant__ FusedLaunch fl) {
-    static_assert(R == kFuseBits && R == 4, "k_fused is written for 4 fused qubits");
+    static_assert(R == kFuseBits && (R == 3 || R == 4), "k_fused is written for 3 or 4 fused qubits");
     constexpr int E = 1 << R;
     unsigned long long k = (unsigned long long)blockIdx.x * BLOCK + threadIdx.x;
     if (k >= fl.nThreads) return;
@@ -409,7 +386,25 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
             xi[e] = load<1>(im + base + off[e]).v[0];
         }
     }
-    applyRecordedGates<R, NOISE>(xr, xi, base, fl);
+    {
+        const int nGates = fl.nGates;
+        for (int g0 = 0; g0 < nGates; g0 += 32) {
+            const int cnt = min(32, nGates - g0);
+            unsigned int act = 0;
+            for (int j = 0; j < cnt; ++j) {
+                const unsigned long long m = fl.outerMask[g0 + j];
+                act |= ((base & m) == m ? 1u : 0u) << j;
+            }
+            for (int j = 0; j < cnt; ++j, act >>= 1) {
+                if (!(act & 1u)) continue;
+                const int g = g0 + j;
+                qreal c[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) c[i] = fl.c[g][i];
+                applyGate<R, NOISE, FMA>(fl.ctl[g].opcode, fl.ctl[g].regMask, c, xr, xi);
+            }
+        }
+    }
     if (lowRun == 4) {
 #pragma unroll
         for (int e = 0; e < E; e += 4) {
@@ -572,19 +567,20 @@ __global__ void __launch_bounds__(kBlock) k_countDiffs(const qreal* __restrict__
     finishReduce<1>(acc, partials, ticket, result);
 }
 
-// <psi| rho |psi>: thread per row r accumulates sum_c rho(r,c) psi_c, then multiplies conj(psi_r)
-// (reference QuEST_cpu.c:963-988)
+// <psi| rho |psi>: thread per row r accumulates sum_c rho(r,c) psi_c over the columns [col0, col0+nCols) this
+// shard holds, then multiplies conj(psi_r); psi is a whole state  (reference QuEST_cpu.c:916-988)
 __global__ void __launch_bounds__(kBlock) k_densFidelity(const qreal* __restrict__ dR, const qreal* __restrict__ dI,
                                                         const qreal* __restrict__ pR, const qreal* __restrict__ pI,
-                                                        unsigned long long dim, double* partials, unsigned int* ticket,
-                                                        double* result) {
+                                                        unsigned long long dim, unsigned long long col0,
+                                                        unsigned long long nCols, double* partials,
+                                                        unsigned int* ticket, double* result) {
     double acc[1] = {0.0};
     const unsigned long long stride = (unsigned long long)gridDim.x * kBlock;
     for (unsigned long long r = (unsigned long long)blockIdx.x * kBlock + threadIdx.x; r < dim; r += stride) {
         double rowR = 0, rowI = 0;
-        for (unsigned long long c = 0; c < dim; ++c) {
+        for (unsigned long long c = 0; c < nCols; ++c) {
             const double eR = dR[r + dim * c], eI = dI[r + dim * c];
-            const double vR = pR[c], vI = pI[c];
+            const double vR = pR[col0 + c], vI = pI[col0 + c];
             rowR += eR * vR - eI * vI;
             rowI += eR * vI + eI * vR;
         }
@@ -845,10 +841,11 @@ __global__ void __launch_bounds__(kBlock) k_mixDensity(qreal* __restrict__ aR, q
 // rho(r,c) = psi_r conj(psi_c), column-major                  (mathematically correct form)
 __global__ void __launch_bounds__(kBlock) k_outerProduct(qreal* __restrict__ dR, qreal* __restrict__ dI,
                                                         const qreal* __restrict__ pR, const qreal* __restrict__ pI,
-                                                        unsigned long long dim, unsigned long long n) {
+                                                        unsigned long long dim, unsigned long long n,
+                                                        unsigned long long off) {
     const unsigned long long i = (unsigned long long)blockIdx.x * kBlock + threadIdx.x;
     if (i >= n) return;
-    const unsigned long long r = i % dim, c = i / dim;
+    const unsigned long long r = (i + off) % dim, c = (i + off) / dim;
     const qreal kr = pR[r], ki = pI[r], br = pR[c], bi = -pI[c];
     dR[i] = kr * br - ki * bi;
     dI[i] = kr * bi + ki * br;

@@ -212,12 +212,14 @@ inline SlotSwap planSwapIn(const QubitMap& m, int q, unsigned long long avoidMas
     }
     // (b) Low slots are never evicted: exchanging slot l moves runs of 2^l contiguous amplitudes, and NVLink needs
     // runs of a few KB to reach its rate (measured: slot 2 -> 404 GB/s per direction, slot >= 10 -> ~700 GB/s).
+    // Only when every preferred slot is pinned or already hosts a guest does the search drop to the low slots.
     int best = -1;
-    const int lowest = m.localBits > 12 ? 10 : 2;
-    for (int x = lowest; x < m.localBits; ++x) {
-        if (m.phys[x] != x || ((avoidMask >> x) & 1)) continue;
-        if (best < 0 || m.lastUse[x] < m.lastUse[best] || (m.lastUse[x] == m.lastUse[best] && x > best)) best = x;
-    }
+    const int preferred = m.localBits > 12 ? 10 : 2;
+    for (int lowest = preferred; best < 0 && lowest >= 0; lowest = lowest ? 0 : -1)
+        for (int x = lowest; x < m.localBits; ++x) {
+            if (m.phys[x] != x || ((avoidMask >> x) & 1)) continue;
+            if (best < 0 || m.lastUse[x] < m.lastUse[best] || (m.lastUse[x] == m.lastUse[best] && x > best)) best = x;
+        }
     if (best < 0) return s;  // every local qubit is pinned: caller falls back to the cross-shard gate
     s.globalSlot = p;
     s.localSlot = best;

@@ -33,8 +33,28 @@ def fuse(lib, local_bits, ops):
     ng = lib.qb200_debugFuse(local_bits, n, kinds, targets, masks, groups, desc)
     gl = [dict(first=groups[7 * i], count=groups[7 * i + 1], bits=list(groups[7 * i + 2:7 * i + 6]), ndense=groups[7 * i + 6])
           for i in range(ng)]
-    dl = [dict(kind=desc[4 * i], pos=desc[4 * i + 1], reg=desc[4 * i + 2], outer=desc[4 * i + 3]) for i in range(n)]
+    dl = [dict(kind=desc[4 * i] & 0xFF, opcode=desc[4 * i] >> 8, pos=desc[4 * i + 1], reg=desc[4 * i + 2],
+               outer=desc[4 * i + 3]) for i in range(n)]
     return gl, dl
+
+
+def decode_opcode(opcode):
+    """What k_fused's single table jump selects (qb_fuse.h FusedOpcode): (kind, target position, register mask)."""
+    if opcode < 4:
+        return K_MATRIX, opcode, 0            # uncontrolled among the fused qubits
+    if opcode < 8:
+        return K_MATRIX, opcode - 4, None     # mask taken from the descriptor at run time
+    if opcode < 12:
+        return K_HAD, opcode - 8, 0
+    if opcode < 16:
+        return K_SWAP, opcode - 12, None
+    if opcode < 20:
+        return K_Y, opcode - 16, None
+    assert opcode >= 32
+    if opcode < 48:
+        return K_PHASE, None, opcode - 32
+    assert opcode < 64
+    return K_FLIP, None, opcode - 48
 
 
 def unitary(rng):
@@ -68,13 +88,17 @@ def apply_fused_group(state, local_bits, grp, descs, mats):
     reg = state[outer[:, None] + off[None, :]]  # [threads, 16]
     for d, u in zip(descs, mats):
         active = (outer & d["outer"]) == d["outer"]
+        kind, p, mask = decode_opcode(d["opcode"])  # the kernel sees only the opcode and the run-time register mask
+        assert kind == d["kind"]
+        if mask is None:
+            mask = d["reg"]
+        assert mask == d["reg"] and (p is None or p == d["pos"])
         for e in range(16):
-            if (e & d["reg"]) != d["reg"]:
+            if (e & mask) != mask:
                 continue
-            if d["kind"] in (K_PHASE, K_FLIP):
-                reg[active, e] *= (np.exp(0.3j) if d["kind"] == K_PHASE else -1)
+            if kind in (K_PHASE, K_FLIP):
+                reg[active, e] *= (np.exp(0.3j) if kind == K_PHASE else -1)
             else:
-                p = d["pos"]
                 if (e >> p) & 1:
                     continue
                 f = e | (1 << p)
@@ -98,7 +122,7 @@ def test_fused_groups_reproduce_gate_by_gate(local_bits, seed):
             qs = rng.sample(range(local_bits), rng.randint(1, min(4, local_bits)))
             ops.append((kind, -1, sum(1 << q for q in qs)))
         else:
-            cs = rng.sample(others, rng.choice([0, 0, 1, 2])) if others else []
+            cs = rng.sample(others, rng.choice([0, 0, 1, 2])) if others and kind != K_HAD else []  # no controlled hadamard in the API
             ops.append((kind, t, sum(1 << c for c in cs)))
         mats.append(unitary(nrng))
     groups, descs = fuse(lib, local_bits, ops)

@@ -5,6 +5,7 @@ Bars (BASELINE.json north_star): amplitudes within 1e-12 relative in double, mea
 under the same seed.  Gate kernels are compiled without FMA contraction and written with the reference's
 operand order, so measurement-free circuits are additionally required to match BIT FOR BIT.
 """
+import ctypes
 import os
 
 import numpy as np
@@ -235,6 +236,34 @@ def test_fusion_off_gives_the_same_bits(product, product_env, nq, dens, seed):
     assert np.array_equal(states[0].view(np.float64), states[1].view(np.float64))
 
 
+@pytest.mark.parametrize("nq,seed", [(13, 51), (16, 52)])
+def test_contracted_arithmetic_is_opt_in_and_within_tolerance(product, product_env, oracle, oracle_env, nq, seed):
+    """qb200_setArithmetic(1): the fused pass may use fma.  Off by default; when on, amplitudes stay within the 1e-12
+    bar of the oracle but are allowed to differ in the last bits; switching it off restores bit-identical results."""
+    product.lib.qb200_setArithmetic.argtypes = [ctypes.c_int]
+    assert product.lib.qb200_getArithmetic() == 0
+    ops = circuits.random_circuit(nq, 300, seed, density=False, measure=False)
+    cq = oracle.createQureg(nq, oracle_env)
+    circuits.prepare(oracle, cq, seed)
+    circuits.run_circuit(oracle, cq, ops, seed=seed)
+    want = oracle.get_state(cq)
+    oracle.destroyQureg(cq, oracle_env)
+    got = {}
+    try:
+        for mode in (1, 0):
+            product.lib.qb200_setArithmetic(mode)
+            q = product.createQureg(nq, product_env)
+            circuits.prepare(product, q, seed)
+            circuits.run_circuit(product, q, ops, seed=seed)
+            got[mode] = product.get_state(q)
+            product.destroyQureg(q, product_env)
+    finally:
+        product.lib.qb200_setArithmetic(0)
+    assert np.array_equal(got[0].view(np.float64), want.view(np.float64))
+    assert np.abs(got[1] - want).max() <= 1e-12 * np.abs(want).max()
+    assert not np.array_equal(got[1].view(np.float64), want.view(np.float64))  # the mode really changes the arithmetic
+
+
 def test_queue_is_drained_by_every_observer(product, product_env, oracle, oracle_env):
     """Pending gates must be visible to clone, inner product, compare, collapse, noise, setAmps and getAmp."""
     nq = 9
@@ -301,7 +330,7 @@ def test_32_qubit_register_uses_64_bit_indexing(product, product_env):
 def test_api_fuzz_vs_oracle(product, product_env, oracle, oracle_env, nq, seed):
     """Random multi-register API sequences - gates interleaved with clone, inner product, fidelity, compare, mixing,
     partial setAmps, re-initialisation, probabilities, getAmp - through the fusion queue, against the CPU oracle."""
-    calls = circuits.random_api_sequence(nq, 400, seed)
+    calls = circuits.random_api_sequence(nq, 400, seed, extended=True)
     a, sa = circuits.run_api_sequence(product, product_env, nq, calls, seed)
     b, sb = circuits.run_api_sequence(oracle, oracle_env, nq, calls, seed)
     np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-13)

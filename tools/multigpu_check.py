@@ -75,7 +75,7 @@ def main():
     # sharded density matrices: unitaries on row and column qubits, one-qubit noise channels (also on qubits whose
     # column bit selects the shard), purity and outcome probabilities
     for case, (nd, seed, meas) in enumerate([(11, 311, False), (9, 312, True)]):
-        ops = circuits.random_circuit(nd, args.depth, seed, density=True, measure=meas, two_qubit_noise=False)
+        ops = circuits.random_circuit(nd, args.depth, seed, density=True, measure=meas, two_qubit_noise=True)
         ops += [(name, t, 0.05 + 0.01 * t) for t in range(nd) for name in circuits.NOISE] + [("calcPurity",), ("calcTotalProb",)]
         q = lib.createDensityQureg(nd, env)
         circuits.prepare(lib, q, seed)
@@ -100,7 +100,7 @@ def main():
                   f"scalars_ok={scal_ok} -> {'PASS' if good else 'FAIL'}", flush=True)
     # multi-register API fuzz: copies and observers interleaved with gates on sharded registers
     for case, (nq, seed) in enumerate([(9, 321), (12, 322)]):
-        calls = [c for c in circuits.random_api_sequence(nq, 300, seed) if not (c[0] == "fidelity" and c[1] == "r")]
+        calls = circuits.random_api_sequence(nq, 300, seed, extended=True)
         scal, states = circuits.run_api_sequence(lib, env, nq, calls, seed)
         parts = {}
         for name in sorted(states):
