@@ -33,6 +33,13 @@ int qb200_getFusion(void);
 void qb200_flush(void);
 void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long* fusedGates);
 
+/* Bulk state I/O.  setAmps / initStateFromAmps / setDensityAmps and qb200_copyAmpsToHost accept any host pointer.  From
+ * pinned memory the copy runs at the PCIe rate as it is; from pageable memory (malloc, numpy) transfers of 8 MiB and more
+ * are staged through pinned buffers by several worker threads (QUEST_B200_IO_THREADS, default min(8, cores/2)).  The
+ * counter reports how many transfers took that path.  Reference counterpart: statevec_setAmps, QuEST_gpu.cu:34-44
+ * (two plain cudaMemcpy). */
+unsigned long long qb200_getPipelinedTransferCount(void);
+
 /* Arithmetic of the fused pass.  0 (default): every product and sum is rounded separately, exactly as the reference's
  * CPU build does (gcc without FMA), so amplitudes are bit-identical to it.  1 (or QUEST_B200_FMA=1): products feeding
  * a sum may be contracted into fused multiply-adds - fewer fp64 instructions per gate, results within an ulp or two

@@ -17,7 +17,7 @@ LIBDIR = os.path.join(HERE, "lib")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-CU_SOURCES = ["backend_cuda.cu", "qb_comm.cu", "qb_noalloc.cu"]
+CU_SOURCES = ["backend_cuda.cu", "qb_comm.cu", "qb_noalloc.cu", "qb_io.cu"]
 CXX_SOURCES = ["quest_api.cpp", "quest_common.cpp", "quest_qasm.cpp", "quest_validation.cpp", "mt19937.cpp"]
 
 

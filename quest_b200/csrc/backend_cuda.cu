@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "qb_comm.h"
+#include "qb_io.h"
 #include "qb_fuse.h"
 #include "qb_kernels.cuh"
 #include "quest_b200.h"
@@ -639,6 +640,7 @@ void destroyQuESTEnv(QuESTEnv env) {
     flushAll();
     CUDA_OK(cudaStreamSynchronize(g.stream));
     if (g.world > 1) comm::shutdown();
+    io::release();
     cudaFree(g.dPartials);
     cudaFree(g.dTicket);
     cudaFree(g.dResult);
@@ -745,18 +747,20 @@ void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, i
     idx_t lo = std::max<idx_t>(startInd - off, 0), hi = std::min<idx_t>(startInd - off + numAmps, r->n);
     if (hi > lo) {
         const idx_t src = lo + off - startInd;
-        CUDA_OK(cudaMemcpyAsync(r->re + lo, reals + src, (hi - lo) * sizeof(qreal), cudaMemcpyHostToDevice, g.stream));
-        CUDA_OK(cudaMemcpyAsync(r->im + lo, imags + src, (hi - lo) * sizeof(qreal), cudaMemcpyHostToDevice, g.stream));
+        io::upload(r->re + lo, reals + src, (hi - lo) * sizeof(qreal), g.stream);
+        io::upload(r->im + lo, imags + src, (hi - lo) * sizeof(qreal), g.stream);
     }
     CUDA_OK(cudaStreamSynchronize(g.stream));
 }
 
 void qb200_copyAmpsToHost(Qureg qureg, idx_t start, idx_t n, qreal* reals, qreal* imags) {
     QuregRec* r = canon(qureg);
-    CUDA_OK(cudaMemcpyAsync(reals, r->re + start, n * sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
-    CUDA_OK(cudaMemcpyAsync(imags, r->im + start, n * sizeof(qreal), cudaMemcpyDeviceToHost, g.stream));
+    io::download(reals, r->re + start, n * sizeof(qreal), g.stream);
+    io::download(imags, r->im + start, n * sizeof(qreal), g.stream);
     CUDA_OK(cudaStreamSynchronize(g.stream));
 }
+
+unsigned long long qb200_getPipelinedTransferCount(void) { return io::pipelinedTransfers(); }
 
 void statevec_cloneQureg(Qureg dst, Qureg src) {
     QuregRec *d = fresh(dst), *s = live(src);
