@@ -33,6 +33,14 @@ int qb200_getFusion(void);
 void qb200_flush(void);
 void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long* fusedGates);
 
+/* Sharded registers: when a slot exchange (see qb200_setRemap) follows recorded gates, the last fused pass and the
+ * exchange are cut into slabs and pipelined on two streams - the exchange of a slab runs over NVLink while the pass
+ * computes the next one (default; QUEST_B200_OVERLAP=0 / qb200_setOverlap(0) run them back to back).  Results are
+ * identical either way.  The counter reports how many exchanges were pipelined.  No reference counterpart: the
+ * reference exchanges whole shards with a blocking MPI_Sendrecv (QuEST_cpu_distributed.c:451-479). */
+void qb200_setOverlap(int enabled);
+unsigned long long qb200_getOverlappedExchangeCount(void);
+
 /* Bulk state I/O.  setAmps / initStateFromAmps / setDensityAmps and qb200_copyAmpsToHost accept any host pointer.  From
  * pinned memory the copy runs at the PCIe rate as it is; from pageable memory (malloc, numpy) transfers of 8 MiB and more
  * are staged through pinned buffers by several worker threads (QUEST_B200_IO_THREADS, default min(8, cores/2)).  The
@@ -85,6 +93,11 @@ void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long l
  * (QuEST_cpu_distributed.c:451-479). */
 int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, const unsigned long long* masks,
                      int* eventsOut, int* physOut, int* canonOut);
+
+/* Test hook (host logic only, makes no CUDA call): the slab bits chosen for pipelining a fused pass with a slot
+ * exchange, and every k_swapPeer launch plan of that exchange.  Layouts at the definition. */
+int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int lowestAllowed, int vec, int localSlot,
+                     int* bitsOut, unsigned long long* swapOut);
 
 /* Test hook (host logic only, makes no CUDA call): how the fusion queue would group a gate list for a shard of
  * 2^localBits amplitudes.  kinds: 0 matrix, 1 hadamard, 2 swap, 3 pauliY, 4 phase, 5 flip.  Layouts at the definition. */

@@ -70,6 +70,13 @@ struct Engine {
     bool contract = false;          // QUEST_B200_FMA / qb200_setArithmetic: fused pass may contract a*b+c into fma
     bool remap = true;              // QUEST_B200_REMAP: make shard-selecting qubits local by slot exchange
     unsigned long long slotSwaps = 0;
+    bool overlap = true;            // QUEST_B200_OVERLAP: pipeline a slot exchange with the fused pass before it
+    int swapCtasPerSm = 1;          // QUEST_B200_SWAP_CTAS: footprint of a pipelined exchange
+    int overlapMinBits = 24;        // ... for shards of at least 2^24 amplitudes (QUEST_B200_OVERLAP_MIN_BITS: tests)
+    cudaStream_t comm = nullptr;    // high-priority stream of the pipelined exchanges (sharded runs only)
+    cudaEvent_t slabEv[8] = {};     // pass on slab s has been enqueued up to here
+    cudaEvent_t commDone = nullptr;
+    unsigned long long overlapped = 0;
     bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fusedEvents;
 } g;
@@ -80,6 +87,10 @@ struct QuregRec {
     idx_t n;       // amplitudes in this shard
     int localBits; // log2 n
     std::vector<PendingOp> queue;  // gates recorded but not yet executed (qb_fuse.h)
+    // The same on every rank (ranks drop different gates, so their queues differ): how many gate calls arrived since
+    // the last flush and which bit positions they used as dense targets.  Decisions two GPUs must agree on use these.
+    size_t callsSinceFlush = 0;
+    u64 denseSinceFlush = 0;
     QubitMap map;                  // where each logical qubit lives (qb_plan.h); identity unless sharded
 };
 
@@ -274,57 +285,87 @@ void runOpNow(const Qureg& q, const PendingOp& op) {
     }
 }
 
+#ifndef QB_FUSED_MINB
+#define QB_FUSED_MINB 4
+#endif
+FusedLaunch fl;  // ~8.5 KB: passed by value as the kernel parameter block
+
+// Fill the parameter block for one group of recorded gates; returns whether it holds noise channels.
+bool prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
+    bool noisy = false;
+    for (int i = 0; i < grp.count; ++i) {
+        const FusedGate fg = describe(ops[grp.first + i], grp.bits);
+        fl.ctl[i] = GateCtl{opcodeOf(fg), fg.regMask};
+        fl.outerMask[i] = fg.outerMask;
+        std::memcpy(fl.c[i], fg.c, sizeof fg.c);
+        noisy = noisy || isNoise(ops[grp.first + i].kind);
+    }
+    fl.ctl[grp.count] = GateCtl{0, 0};
+    for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = grp.bits[j];
+    fl.nGates = grp.count;
+    return noisy;
+}
+
+// One launch of k_fused over the whole shard (sp == nullptr) or over slab `slab` of it.
+void launchPrepared(QuregRec* r, bool noisy, const SlabPlan* sp, int slab) {
+    int n = 0;
+    for (int j = 0; j < kFuseBits; ++j) fl.ins[n++] = fl.pos[j];
+    if (sp)
+        for (int j = 0; j < sp->nBits; ++j) fl.ins[n++] = sp->bits[j];
+    std::sort(fl.ins, fl.ins + n);
+    fl.nIns = n;
+    fl.slabMask = sp ? sp->valueMask(slab) : 0;
+    fl.nThreads = (u64)r->n >> n;
+    // 128-thread CTAs, 4 per SM (128 registers per thread): measured best of 64/128/256 threads x 2-6 CTAs
+    const unsigned int nb128 = (unsigned int)((fl.nThreads + 127) / 128);
+    if (noisy)
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+    else if (g.contract)
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, false, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+    else
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, false><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+    launched();
+}
+
+struct FusedTimer {  // qb200_setKernelTiming: one event pair per fused pass (a pass cut into slabs counts once)
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    void start() {
+        if (!g.timeFused) return;
+        CUDA_OK(cudaEventCreate(&e0));
+        CUDA_OK(cudaEventCreate(&e1));
+        CUDA_OK(cudaEventRecord(e0, g.stream));
+    }
+    void stop() {
+        if (!g.timeFused) return;
+        CUDA_OK(cudaEventRecord(e1, g.stream));
+        g.fusedEvents.emplace_back(e0, e1);
+    }
+};
+
+void runGroup(const Qureg& q, const std::vector<PendingOp>& ops, const FusedGroup& grp) {
+    if (grp.count == 1) {
+        runOpNow(q, ops[grp.first]);
+        return;
+    }
+    const bool noisy = prepareGroup(ops, grp);
+    FusedTimer t;
+    t.start();
+    launchPrepared(rec(q), noisy, nullptr, 0);
+    t.stop();
+    ++g.fusedLaunches;
+    g.fusedGates += grp.count;
+}
+
 // Execute everything recorded for this register: single gates through their own kernel, runs of gates through
 // k_fused (one HBM pass per group, qb_fuse.h).
 void flush(const Qureg& q) {
     QuregRec* r = rec(q);
+    r->callsSinceFlush = 0;
+    r->denseSinceFlush = 0;
     if (r->queue.empty()) return;
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
-    const std::vector<FusedGroup> groups = groupOps(ops, r->localBits);
-#ifndef QB_FUSED_MINB
-#define QB_FUSED_MINB 4
-#endif
-    static FusedLaunch fl;  // ~8.5 KB: passed by value as the kernel parameter block
-    for (const FusedGroup& grp : groups) {
-        if (grp.count == 1) {
-            runOpNow(q, ops[grp.first]);
-            continue;
-        }
-        for (int i = 0; i < grp.count; ++i) {
-            const FusedGate fg = describe(ops[grp.first + i], grp.bits);
-            fl.ctl[i] = GateCtl{opcodeOf(fg), fg.regMask};
-            fl.outerMask[i] = fg.outerMask;
-            std::memcpy(fl.c[i], fg.c, sizeof fg.c);
-        }
-        fl.ctl[grp.count] = GateCtl{0, 0};
-        for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = grp.bits[j];
-        fl.nGates = grp.count;
-        fl.nThreads = (u64)r->n >> kFuseBits;
-        cudaEvent_t e0 = nullptr, e1 = nullptr;
-        if (g.timeFused) {
-            CUDA_OK(cudaEventCreate(&e0));
-            CUDA_OK(cudaEventCreate(&e1));
-            CUDA_OK(cudaEventRecord(e0, g.stream));
-        }
-        // 128-thread CTAs, 4 per SM (128 registers per thread): measured best of 64/128/256 threads x 2-6 CTAs
-        bool noisy = false;
-        for (int i = 0; i < grp.count; ++i) noisy = noisy || isNoise(ops[grp.first + i].kind);
-        const unsigned int nb128 = (unsigned int)((fl.nThreads + 127) / 128);
-        if (noisy)
-            k_fused<kFuseBits, 128, QB_FUSED_MINB, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
-        else if (g.contract)
-            k_fused<kFuseBits, 128, QB_FUSED_MINB, false, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
-        else
-            k_fused<kFuseBits, 128, QB_FUSED_MINB, false><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
-        launched();
-        if (g.timeFused) {
-            CUDA_OK(cudaEventRecord(e1, g.stream));
-            g.fusedEvents.emplace_back(e0, e1);
-        }
-        ++g.fusedLaunches;
-        g.fusedGates += grp.count;
-    }
+    for (const FusedGroup& grp : groupOps(ops, r->localBits)) runGroup(q, ops, grp);
 }
 
 void flushAll() {
@@ -340,35 +381,126 @@ void flushAll() {
     }
 }
 
-// Exchange a shard-selecting bit position with a local one (k_swapPeer); caller has flushed the queue.
-void exchangeSlots(const Qureg& q, SlotSwap sw) {
+// The k_swapPeer launch of a slot exchange, whole shard (sp == nullptr) or one slab, bracketed by nothing: the
+// callers place the handshakes.  Each GPU of the pair moves half of the (local slot = 1 here, = 0 there) pairs.
+void launchSwap(const Qureg& q, SlotSwap sw, const SlabPlan* sp, int slab, cudaStream_t stream) {
     QuregRec* r = rec(q);
     const int gbit = sw.globalSlot - r->localBits, l = sw.localSlot;
     const comm::Partner peer = comm::partnerOf(q, gbit);
     const bool amUpper = ((q.chunkId >> gbit) & 1) == 0;
     const int vec = pickVec(r->n, 1LL << l);  // the local slot stays above the vector
     const int v = log2i(vec);
-    int split = -1;
-    for (int b = r->localBits - 1; b >= v; --b)
-        if (b != l) { split = b; break; }
-    comm::pairBarrier(peer.rank, g.stream);
-    if (split >= 0 || amUpper) {
-        Planned p = split >= 0 ? makePlan(r->n, vec, {l, split}, 0) : makePlan(r->n, vec, {l}, 0);
-        if (split >= 0 && !amUpper) p.plan.setMask |= 1ull << (split - v);
-        qreal* aRe = amUpper ? r->re : peer.re;
-        qreal* aIm = amUpper ? r->im : peer.im;
-        qreal* bRe = amUpper ? peer.re : r->re;
-        qreal* bIm = amUpper ? peer.im : r->im;
-        if (p.nTasks) {
-            dispatchV(vec, [&](auto V) {
-                k_swapPeer<decltype(V)::value><<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
-            });
-            launched();
-        }
-    }
-    comm::pairBarrier(peer.rank, g.stream);
+    const SwapLaunch plan = planSlotSwap(r->localBits, vec, l, amUpper, sp, slab);
+    if (!plan.active) return;
+    const Planned& p = plan.planned;
+    qreal* aRe = amUpper ? r->re : peer.re;
+    qreal* aIm = amUpper ? r->im : peer.im;
+    qreal* bRe = amUpper ? peer.re : r->re;
+    qreal* bIm = amUpper ? peer.im : r->im;
+    // alone: up to 8 CTAs on every SM; next to a fused pass: g.swapCtasPerSm, the rest of each SM stays with the pass
+    const unsigned int cap = (unsigned int)g.numSMs * (sp ? (unsigned int)g.swapCtasPerSm : 8u);
+    const unsigned int grid = std::min(blocksFor(p.nTasks), cap);
+    dispatchV(vec, [&](auto V) {
+        k_swapPeer<decltype(V)::value><<<grid, kBlock, 0, stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
+    });
+    launched();
+}
+
+// Exchange a shard-selecting bit position with a local one; caller has flushed the queue.
+void exchangeSlots(const Qureg& q, SlotSwap sw) {
+    QuregRec* r = rec(q);
+    const comm::Partner peer = comm::partnerOf(q, sw.globalSlot - r->localBits);
+    comm::pairBarrier(peer.rank, g.stream);  // partner has finished everything enqueued before the exchange
+    launchSwap(q, sw, nullptr, 0, g.stream);
+    comm::pairBarrier(peer.rank, g.stream);  // partner's remote writes into this shard have landed
     r->map.applySwap(sw.globalSlot, sw.localSlot);
     ++g.slotSwaps;
+}
+
+// flush(q) followed by exchangeSlots(q, sw), with the last fused pass and the exchange cut into slabs
+// (qb::planSlabs) and pipelined: the pass runs slab after slab on the engine stream; as soon as slab s is done on
+// both GPUs of the pair (event + handshake on the communication stream) its half goes over NVLink while the pass
+// computes slab s+1.  The pass is bound by fp64 issue, the exchange by NVLink, so they overlap almost completely.
+void flushThenExchange(const Qureg& q, SlotSwap sw) {
+    QuregRec* r = rec(q);
+    // Both GPUs of the pair must cut along the same bits and issue the same handshakes, whatever their own queues hold:
+    // everything below that shapes the protocol derives from rank-independent state.
+    const u64 busy = r->denseSinceFlush | (1ull << sw.localSlot);
+    const int spare = r->localBits - __builtin_popcountll(busy & ((1ull << r->localBits) - 1)) - kFuseBits;
+    const int lowest = std::min(16, g.overlapMinBits / 2 + 2);
+    SlabPlan sp{0, {0, 0, 0}};
+    if (g.overlap && g.comm && r->callsSinceFlush > 0 && r->localBits >= g.overlapMinBits && spare > 0)
+        sp = planSlabs(r->localBits, busy, std::min(kMaxSlabBits, spare), lowest);
+    if (sp.nBits == 0) {
+        flush(q);
+        exchangeSlots(q, sw);
+        return;
+    }
+    u64 slabBits = 0;
+    for (int j = 0; j < sp.nBits; ++j) slabBits |= 1ull << sp.bits[j];
+    std::vector<PendingOp> ops;
+    ops.swap(r->queue);
+    r->callsSinceFlush = 0;
+    r->denseSinceFlush = 0;
+    const std::vector<FusedGroup> groups = groupOps(ops, r->localBits, slabBits);
+    for (size_t i = 0; i + 1 < groups.size(); ++i) runGroup(q, ops, groups[i]);
+    // this rank's last group, if it is a fused pass, is the one that is cut into slabs
+    const bool cut = !groups.empty() && groups.back().count > 1;
+    if (!groups.empty() && !cut) runGroup(q, ops, groups.back());
+    const comm::Partner peer = comm::partnerOf(q, sw.globalSlot - r->localBits);
+    const bool noisy = cut ? prepareGroup(ops, groups.back()) : false;
+    FusedTimer t;
+    if (cut) t.start();
+    static const bool trace = std::getenv("QUEST_B200_OVERLAP_TRACE") != nullptr;
+    cudaEvent_t tr0 = nullptr, trPass[8] = {}, trSwapIn[8] = {}, trSwapOut[8] = {};
+    if (trace) {
+        CUDA_OK(cudaEventCreate(&tr0));
+        CUDA_OK(cudaEventRecord(tr0, g.stream));
+    }
+    for (int s = 0; s < (1 << sp.nBits); ++s) {
+        if (cut) launchPrepared(r, noisy, &sp, s);
+        CUDA_OK(cudaEventRecord(g.slabEv[s], g.stream));
+        if (trace) {
+            CUDA_OK(cudaEventCreate(&trPass[s]));
+            CUDA_OK(cudaEventRecord(trPass[s], g.stream));
+        }
+        CUDA_OK(cudaStreamWaitEvent(g.comm, g.slabEv[s], 0));
+        comm::pairBarrier(peer.rank, g.comm, 1);  // the partner has finished slab s too
+        if (trace) {
+            CUDA_OK(cudaEventCreate(&trSwapIn[s]));
+            CUDA_OK(cudaEventRecord(trSwapIn[s], g.comm));
+        }
+        launchSwap(q, sw, &sp, s, g.comm);
+        if (trace) {
+            CUDA_OK(cudaEventCreate(&trSwapOut[s]));
+            CUDA_OK(cudaEventRecord(trSwapOut[s], g.comm));
+        }
+    }
+    if (trace) {
+        CUDA_OK(cudaStreamSynchronize(g.comm));
+        CUDA_OK(cudaStreamSynchronize(g.stream));
+        std::fprintf(stderr, "[rank %d] pipelined exchange, %d slabs (ms since the first slab was enqueued):\n", g.rank, 1 << sp.nBits);
+        for (int s = 0; s < (1 << sp.nBits); ++s) {
+            float a = 0, b = 0, c = 0;
+            cudaEventElapsedTime(&a, tr0, trPass[s]);
+            cudaEventElapsedTime(&b, tr0, trSwapIn[s]);
+            cudaEventElapsedTime(&c, tr0, trSwapOut[s]);
+            std::fprintf(stderr, "  slab %d: pass done %.3f   swap start %.3f   swap done %.3f\n", s, a, b, c);
+            cudaEventDestroy(trPass[s]); cudaEventDestroy(trSwapIn[s]); cudaEventDestroy(trSwapOut[s]);
+        }
+        cudaEventDestroy(tr0);
+    }
+    if (cut) {
+        t.stop();
+        ++g.fusedLaunches;
+        g.fusedGates += groups.back().count;
+    }
+    comm::pairBarrier(peer.rank, g.comm, 1);  // the partner's remote writes into this shard have landed
+    CUDA_OK(cudaEventRecord(g.commDone, g.comm));
+    CUDA_OK(cudaStreamWaitEvent(g.stream, g.commDone, 0));
+    r->map.applySwap(sw.globalSlot, sw.localSlot);
+    ++g.slotSwaps;
+    ++g.overlapped;
 }
 
 // the register's record with no gate pending: every entry point that reads or overwrites amplitudes uses this
@@ -393,6 +525,8 @@ inline QuregRec* canon(const Qureg& q) {
 inline QuregRec* fresh(const Qureg& q) {
     QuregRec* r = rec(q);
     r->queue.clear();
+    r->callsSinceFlush = 0;
+    r->denseSinceFlush = 0;
     r->map.reset(r->map.nQubits, r->localBits);
     return r;
 }
@@ -412,10 +546,7 @@ void submit(const Qureg& q, PendingOp op) {
                     u64 keep = op.mask | (1ull << logical[0]);
                     if (logical[1] >= 0) keep |= 1ull << logical[1];
                     const SlotSwap sw = planSwapIn(r->map, t, keep);
-                    if (sw.globalSlot >= 0) {
-                        flush(q);
-                        exchangeSlots(q, sw);
-                    }
+                    if (sw.globalSlot >= 0) flushThenExchange(q, sw);
                 }
                 r->map.touch(t);
             }
@@ -423,6 +554,15 @@ void submit(const Qureg& q, PendingOp op) {
             if (logical[1] >= 0) op.target2 = r->map.phys[logical[1]];
         }
         op.mask = r->map.physMask(op.mask);
+    }
+    const bool recording = g.fuse && r->localBits >= kFuseBits;
+    if (recording) {  // before any rank-dependent decision: every rank counts every gate call
+        if (r->callsSinceFlush >= kQueueCap) flush(q);
+        ++r->callsSinceFlush;
+        if (!isDiagonal(op.kind)) {
+            if (op.target < r->localBits) r->denseSinceFlush |= 1ull << op.target;
+            if (op.target2 >= 0 && op.target2 < r->localBits) r->denseSinceFlush |= 1ull << op.target2;
+        }
     }
     if (!qb::localiseControls(r->localBits, q.chunkId, op.mask)) return;
     if (isNoise(op.kind) && (op.target >= r->localBits || op.target2 >= r->localBits))
@@ -433,9 +573,8 @@ void submit(const Qureg& q, PendingOp op) {
         runOpNow(q, op);
         return;
     }
-    if (g.fuse && r->localBits >= kFuseBits) {
+    if (recording) {
         r->queue.push_back(op);
-        if (r->queue.size() >= kQueueCap) flush(q);
         return;
     }
     runOpNow(q, op);
@@ -624,7 +763,17 @@ QuESTEnv createQuESTEnv(void) {
     g.rank = ln.rank;
     g.world = ln.world;
     g.up = true;
-    if (g.world > 1) comm::init(ln, g.device, g.stream);
+    if (g.world > 1) {
+        comm::init(ln, g.device, g.stream);
+        if (const char* s = std::getenv("QUEST_B200_OVERLAP")) g.overlap = std::atoi(s) != 0;
+        if (const char* s = std::getenv("QUEST_B200_SWAP_CTAS")) g.swapCtasPerSm = std::max(1, std::min(8, std::atoi(s)));
+        if (const char* s = std::getenv("QUEST_B200_OVERLAP_MIN_BITS")) g.overlapMinBits = std::max(8, std::atoi(s));
+        int lowPrio = 0, highPrio = 0;
+        CUDA_OK(cudaDeviceGetStreamPriorityRange(&lowPrio, &highPrio));
+        CUDA_OK(cudaStreamCreateWithPriority(&g.comm, cudaStreamNonBlocking, highPrio));
+        for (cudaEvent_t& e : g.slabEv) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        CUDA_OK(cudaEventCreateWithFlags(&g.commDone, cudaEventDisableTiming));
+    }
     env.rank = g.rank;
     env.numRanks = g.world;
     seedQuESTDefault();
@@ -639,6 +788,12 @@ void destroyQuESTEnv(QuESTEnv env) {
     }
     flushAll();
     CUDA_OK(cudaStreamSynchronize(g.stream));
+    if (g.comm) {
+        CUDA_OK(cudaStreamSynchronize(g.comm));
+        cudaStreamDestroy(g.comm);
+        for (cudaEvent_t e : g.slabEv) cudaEventDestroy(e);
+        cudaEventDestroy(g.commDone);
+    }
     if (g.world > 1) comm::shutdown();
     io::release();
     cudaFree(g.dPartials);
@@ -759,6 +914,14 @@ void qb200_copyAmpsToHost(Qureg qureg, idx_t start, idx_t n, qreal* reals, qreal
     io::download(imags, r->im + start, n * sizeof(qreal), g.stream);
     CUDA_OK(cudaStreamSynchronize(g.stream));
 }
+
+// Pending gates are executed under the old setting first.
+void qb200_setOverlap(int enabled) {
+    requireEngine();
+    flushAll();
+    g.overlap = enabled != 0;
+}
+unsigned long long qb200_getOverlappedExchangeCount(void) { return g.overlapped; }
 
 unsigned long long qb200_getPipelinedTransferCount(void) { return io::pipelinedTransfers(); }
 
@@ -1243,6 +1406,26 @@ int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, c
         canonOut[2 * i + 1] = back[i].localSlot;
     }
     return n;
+}
+
+// Host slab logic (qb::planSlabs, qb::planSlotSwap), exposed for CPU-only tests (no CUDA call).  Returns the number of
+// slab bits chosen (bitsOut[3]); swapOut, per slab and per rank of the pair (upper first): nTasks, nIns, setMask,
+// pos[8] = 11 words each.
+int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int lowestAllowed, int vec, int localSlot,
+                     int* bitsOut, unsigned long long* swapOut) {
+    const SlabPlan sp = planSlabs(localBits, busyMask, want, lowestAllowed);
+    for (int j = 0; j < sp.nBits; ++j) bitsOut[j] = sp.bits[j];
+    unsigned long long* o = swapOut;
+    for (int s = 0; s < (1 << sp.nBits); ++s)
+        for (int upper = 1; upper >= 0; --upper) {
+            const SwapLaunch sl = planSlotSwap(localBits, vec, localSlot, upper != 0, sp.nBits ? &sp : nullptr, s);
+            o[0] = sl.active ? sl.planned.nTasks : 0;
+            o[1] = sl.planned.plan.nIns;
+            o[2] = sl.planned.plan.setMask;
+            for (int i = 0; i < kMaxInsert; ++i) o[3 + i] = sl.planned.plan.pos[i];
+            o += 11;
+        }
+    return sp.nBits;
 }
 
 // Host grouping logic of the fusion queue, exposed for CPU-only tests (no CUDA call): groups the given gate list

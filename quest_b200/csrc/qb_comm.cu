@@ -6,8 +6,11 @@
 //   MPI_Sendrecv of whole shards    -> nothing is sent: partner shards are mapped into this process with CUDA IPC
 //                                      and read/written directly over NVLink by the gate kernel (k_pairsPeer)
 //   MPI_Allreduce of one scalar     -> ncclAllReduce on the engine stream
+//   (pair handshakes)               -> a sequence counter in the partner's memory + cuStreamWaitValue32, no kernel spins
 // NCCL is loaded with dlopen (the copy already in the process if a framework brought one, else libnccl.so.2), so a
 // single-GPU user never needs it.
+#include <cuda.h>  // driver types only: entry points are fetched with cudaGetDriverEntryPoint, libcuda is not linked
+
 #include <arpa/inet.h>
 #include <dlfcn.h>
 #include <netdb.h>
@@ -146,14 +149,10 @@ struct Nccl {
     int (*CommDestroy)(NcclComm) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
     int (*AllGather)(const void*, void*, size_t, int, NcclComm, cudaStream_t) = nullptr;
-    int (*Send)(const void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
-    int (*Recv)(void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
-    int (*GroupStart)() = nullptr;
-    int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
     NcclComm comm = nullptr;
 } nccl;
-constexpr int kNcclInt8 = 0, kNcclInt32 = 2, kNcclFloat64 = 8, kNcclSum = 0;
+constexpr int kNcclInt8 = 0, kNcclFloat64 = 8, kNcclSum = 0;
 
 #define NCCL_OK(call)                                                            \
     do {                                                                         \
@@ -177,10 +176,6 @@ void loadNccl() {
     nccl.CommDestroy = reinterpret_cast<decltype(nccl.CommDestroy)>(sym("ncclCommDestroy"));
     nccl.AllReduce = reinterpret_cast<decltype(nccl.AllReduce)>(sym("ncclAllReduce"));
     nccl.AllGather = reinterpret_cast<decltype(nccl.AllGather)>(sym("ncclAllGather"));
-    nccl.Send = reinterpret_cast<decltype(nccl.Send)>(sym("ncclSend"));
-    nccl.Recv = reinterpret_cast<decltype(nccl.Recv)>(sym("ncclRecv"));
-    nccl.GroupStart = reinterpret_cast<decltype(nccl.GroupStart)>(sym("ncclGroupStart"));
-    nccl.GroupEnd = reinterpret_cast<decltype(nccl.GroupEnd)>(sym("ncclGroupEnd"));
     nccl.GetErrorString = reinterpret_cast<decltype(nccl.GetErrorString)>(sym("ncclGetErrorString"));
 }
 
@@ -190,8 +185,69 @@ struct PeerMap {
 };
 std::map<const void*, PeerMap> peers;  // key: the register's opaque record pointer (Qureg.pairStateVec.real)
 
-int* dTokens = nullptr;  // two ints: [0] sent, [1] received by the pair handshake
 cudaStream_t engineStream = nullptr;
+
+// ---- pair handshake ----------------------------------------------------------------------------------------
+// Each rank owns an array of sequence counters, one 64-byte slot per (peer, channel), mapped into every peer with
+// CUDA IPC.  signal = a one-thread kernel that stores the next sequence number into MY slot of the PARTNER's array
+// over NVLink; wait = a stream memory operation (cuStreamWaitValue32, >=) on the partner's slot of MY array.  Nothing
+// spins on an SM and nothing needs an SM to be free, so a handshake can run while a compute kernel fills the GPU.
+// Channels keep handshakes issued on different streams from being mistaken for one another.
+constexpr int kChannels = 2, kSlotWords = 16;
+struct Flags {
+    unsigned int* mine = nullptr;
+    std::vector<unsigned int*> peer;   // [rank]
+    std::vector<unsigned int> seq;     // [rank * kChannels + channel]: handshakes issued so far
+    CUresult (*waitValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int) = nullptr;
+    unsigned int waitFlags = 0;
+} flags;
+
+__global__ void k_signal(unsigned int* slot, unsigned int value) {
+    __threadfence_system();  // everything this stream did before (stream order) is visible before the counter moves
+    *reinterpret_cast<volatile unsigned int*>(slot) = value;
+}
+
+void setupFlags() {
+    const size_t bytes = (size_t)star.world * kChannels * kSlotWords * sizeof(unsigned int);
+    COMM_CUDA_OK(cudaMalloc(&flags.mine, bytes));
+    COMM_CUDA_OK(cudaMemset(flags.mine, 0, bytes));
+    COMM_CUDA_OK(cudaDeviceSynchronize());
+    cudaIpcMemHandle_t h;
+    COMM_CUDA_OK(cudaIpcGetMemHandle(&h, flags.mine));
+    std::vector<cudaIpcMemHandle_t> all(star.world);
+    allGather(&h, sizeof h, all.data());
+    flags.peer.assign(star.world, nullptr);
+    for (int r = 0; r < star.world; ++r) {
+        if (r == star.rank) {
+            flags.peer[r] = flags.mine;
+            continue;
+        }
+        void* p = nullptr;
+        COMM_CUDA_OK(cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess));
+        flags.peer[r] = static_cast<unsigned int*>(p);
+    }
+    flags.seq.assign((size_t)star.world * kChannels, 0u);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult found;
+    COMM_CUDA_OK(cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &found));
+    if (!fn || found != cudaDriverEntryPointSuccess) die("the CUDA driver lacks cuStreamWaitValue32");
+    flags.waitValue32 = reinterpret_cast<decltype(flags.waitValue32)>(fn);
+    int dev = 0, canFlush = 0;
+    COMM_CUDA_OK(cudaGetDevice(&dev));
+    if (cudaDeviceGetAttribute(&canFlush, cudaDevAttrCanFlushRemoteWrites, dev) != cudaSuccess) {
+        cudaGetLastError();
+        canFlush = 0;
+    }
+    flags.waitFlags = CU_STREAM_WAIT_VALUE_GEQ | (canFlush ? CU_STREAM_WAIT_VALUE_FLUSH : 0u);
+}
+
+void teardownFlags() {
+    for (int r = 0; r < (int)flags.peer.size(); ++r)
+        if (r != star.rank && flags.peer[r]) cudaIpcCloseMemHandle(flags.peer[r]);
+    hostBarrier();  // peers have dropped their mappings
+    if (flags.mine) cudaFree(flags.mine);
+    flags = Flags();
+}
 
 }  // namespace
 
@@ -226,8 +282,7 @@ void init(const Launch& ln, int device, cudaStream_t stream) {
     if (ln.rank == 0) NCCL_OK(nccl.GetUniqueId(&id));
     broadcastBytes(&id, sizeof id, 0);
     NCCL_OK(nccl.CommInitRank(&nccl.comm, ln.world, id, ln.rank));
-    COMM_CUDA_OK(cudaMalloc(&dTokens, 2 * sizeof(int)));
-    COMM_CUDA_OK(cudaMemset(dTokens, 0, 2 * sizeof(int)));
+    setupFlags();
     hostBarrier();
 }
 
@@ -235,8 +290,7 @@ void shutdown() {
     hostBarrier();
     if (nccl.comm) nccl.CommDestroy(nccl.comm);
     nccl.comm = nullptr;
-    if (dTokens) cudaFree(dTokens);
-    dTokens = nullptr;
+    teardownFlags();
     if (star.up >= 0) ::close(star.up);
     for (int fd : star.down)
         if (fd >= 0) ::close(fd);
@@ -334,13 +388,18 @@ Partner partnerOf(const Qureg& q, int gbit) {
     return p;
 }
 
-// Stream-ordered handshake with one partner: returns (on the stream) only after the partner's stream has reached
-// its matching call, i.e. after everything the partner enqueued before it has completed.
-void pairBarrier(int partnerRank, cudaStream_t stream) {
-    NCCL_OK(nccl.GroupStart());
-    NCCL_OK(nccl.Send(dTokens, 1, kNcclInt32, partnerRank, nccl.comm, stream));
-    NCCL_OK(nccl.Recv(dTokens + 1, 1, kNcclInt32, partnerRank, nccl.comm, stream));
-    NCCL_OK(nccl.GroupEnd());
+// Stream-ordered handshake with one partner: work enqueued on `stream` after this call starts only after the partner's
+// stream has reached its matching call (same partner pair, same channel), i.e. after everything the partner enqueued
+// before it has completed and is visible here.
+void pairBarrier(int partnerRank, cudaStream_t stream, int channel) {
+    const unsigned int seq = ++flags.seq[(size_t)partnerRank * kChannels + channel];
+    unsigned int* theirs = flags.peer[partnerRank] + ((size_t)star.rank * kChannels + channel) * kSlotWords;
+    unsigned int* ours = flags.mine + ((size_t)partnerRank * kChannels + channel) * kSlotWords;
+    k_signal<<<1, 1, 0, stream>>>(theirs, seq);
+    COMM_CUDA_OK(cudaGetLastError());
+    const CUresult r = flags.waitValue32(reinterpret_cast<CUstream>(stream), reinterpret_cast<CUdeviceptr>(ours), seq,
+                                         flags.waitFlags);
+    if (r != CUDA_SUCCESS) die("cuStreamWaitValue32 failed in the pair handshake");
 }
 
 }  // namespace comm

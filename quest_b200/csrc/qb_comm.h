@@ -37,7 +37,7 @@ struct Partner {
     int rank;
 };
 Partner partnerOf(const Qureg& q, int gbit);
-void pairBarrier(int partnerRank, cudaStream_t stream);
+void pairBarrier(int partnerRank, cudaStream_t stream, int channel = 0);  // channel: 0 engine stream, 1 communication stream
 
 }  // namespace comm
 }  // namespace qb

@@ -64,7 +64,9 @@ struct FusedGroup {
 };
 
 // Greedy, order-preserving grouping.
-inline std::vector<FusedGroup> groupOps(const std::vector<PendingOp>& ops, int localBits) {
+// `avoidMask`: bits that must not be used to pad a group (they are held out for slab pipelining, qb_plan.h); they
+// never hold a dense target of these ops.
+inline std::vector<FusedGroup> groupOps(const std::vector<PendingOp>& ops, int localBits, unsigned long long avoidMask = 0) {
     std::vector<FusedGroup> out;
     const int n = (int)ops.size();
     int i = 0;
@@ -96,14 +98,14 @@ inline std::vector<FusedGroup> groupOps(const std::vector<PendingOp>& ops, int l
             while (m && have < kFuseBits) {
                 const int b = __builtin_ctzll(m);
                 m &= m - 1;
-                if (b < localBits) {
+                if (b < localBits && !((avoidMask >> b) & 1)) {
                     chosen |= 1ull << b;
                     ++have;
                 }
             }
         }
         for (int b = localBits - 1; b >= 0 && have < kFuseBits; --b)
-            if (!((chosen >> b) & 1)) {
+            if (!((chosen >> b) & 1) && !((avoidMask >> b) & 1)) {
                 chosen |= 1ull << b;
                 ++have;
             }

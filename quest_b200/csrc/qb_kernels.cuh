@@ -144,20 +144,24 @@ __global__ void __launch_bounds__(kBlock) k_pairsPeer(qreal* __restrict__ upRe, 
 // global bit is 0, `b*` the one whose bit is 1; the amplitudes with (global=0, l=1) and (global=1, l=0) trade
 // places: a[j | 2^l] <-> b[j] for every j with bit l clear.  Half a shard crosses NVLink in each direction.  As in
 // k_pairsPeer the two GPUs split the index range between them and each performs complete swaps in place.
+// Grid-stride: the launch decides how much of the GPU the exchange occupies.  Alone it takes every SM; pipelined with
+// a fused pass (backend_cuda.cu: flushThenExchange) it runs as one CTA per SM - enough loads in flight to keep NVLink
+// busy - and leaves the other resident-CTA slots to the pass.
 template <int VEC>
 __global__ void __launch_bounds__(kBlock) k_swapPeer(qreal* __restrict__ aRe, qreal* __restrict__ aIm,
                                                     qreal* __restrict__ bRe, qreal* __restrict__ bIm,
                                                     unsigned long long nTasks, BitPlan plan, int lvb) {
-    const unsigned long long k = (unsigned long long)blockIdx.x * kBlock + threadIdx.x;
-    if (k >= nTasks) return;
-    const unsigned long long vi = expand(k, plan);
-    const unsigned long long ib = vi * VEC, ia = ib + ((unsigned long long)VEC << lvb);
-    const Vec<qreal, VEC> ar = load<VEC>(aRe + ia), ai = load<VEC>(aIm + ia);
-    const Vec<qreal, VEC> br = load<VEC>(bRe + ib), bi = load<VEC>(bIm + ib);
-    store<VEC>(aRe + ia, br);
-    store<VEC>(aIm + ia, bi);
-    store<VEC>(bRe + ib, ar);
-    store<VEC>(bIm + ib, ai);
+    const unsigned long long stride = (unsigned long long)gridDim.x * kBlock;
+    for (unsigned long long k = (unsigned long long)blockIdx.x * kBlock + threadIdx.x; k < nTasks; k += stride) {
+        const unsigned long long vi = expand(k, plan);
+        const unsigned long long ib = vi * VEC, ia = ib + ((unsigned long long)VEC << lvb);
+        const Vec<qreal, VEC> ar = load<VEC>(aRe + ia), ai = load<VEC>(aIm + ia);
+        const Vec<qreal, VEC> br = load<VEC>(bRe + ib), bi = load<VEC>(bIm + ib);
+        store<VEC>(aRe + ia, br);
+        store<VEC>(aIm + ia, bi);
+        store<VEC>(bRe + ib, ar);
+        store<VEC>(bIm + ib, ai);
+    }
 }
 
 // ======================================================================================================
@@ -209,11 +213,16 @@ __global__ void __launch_bounds__(kBlock) k_diag(qreal* __restrict__ re, qreal* 
 // i10=bI, r11=aR, i11=-aI its expression tree evaluates to the same IEEE bits as the reference's compact form).
 // ======================================================================================================
 
+constexpr int kMaxSlabBits = 3;        // a launch may be confined to the amplitudes with given values on up to 3 bits
+
 struct FusedLaunch {
     int pos[kFuseBits];                  // fused qubits, ascending (amplitude-index bit positions)
     int nGates;
+    int nIns;                            // fused qubits + slab bits: positions held out of the thread index ...
+    int ins[kFuseBits + kMaxSlabBits];   // ... ascending
+    unsigned long long slabMask;         // value of the slab bits for this launch (0 for a whole-shard pass)
     unsigned long long nThreads;
-    GateCtl ctl[kMaxFusedGates + 2];     // padded: the loop fetches ctl[g+1] while gate g computes
+    GateCtl ctl[kMaxFusedGates + 2];     // padded
     unsigned long long outerMask[kMaxFusedGates];  // control/selecting bits outside the fused qubits
     qreal c[kMaxFusedGates][8];          // coefficients (meaning per kind: qb_fuse.h PendingOp::c)
 };
@@ -340,14 +349,16 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
     constexpr int E = 1 << R;
     unsigned long long k = (unsigned long long)blockIdx.x * BLOCK + threadIdx.x;
     if (k >= fl.nThreads) return;
-    // outer index: this thread's amplitude index with the fused qubits at 0
+    // outer index: this thread's amplitude index with the fused qubits at 0 (and the slab bits at their fixed value)
 #pragma unroll
-    for (int j = 0; j < R; ++j) {
-        const int b = fl.pos[j];
-        const unsigned long long low = k & ((1ull << b) - 1ull);
-        k = ((k >> b) << (b + 1)) | low;
+    for (int j = 0; j < R + kMaxSlabBits; ++j) {
+        if (j < fl.nIns) {
+            const int b = fl.ins[j];
+            const unsigned long long low = k & ((1ull << b) - 1ull);
+            k = ((k >> b) << (b + 1)) | low;
+        }
     }
-    const unsigned long long base = k;
+    const unsigned long long base = k | fl.slabMask;
     unsigned long long off[E];
 #pragma unroll
     for (int e = 0; e < E; ++e) {

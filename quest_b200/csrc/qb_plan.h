@@ -39,7 +39,7 @@ inline int log2u(unsigned long long x) {
 // zeroBits: amplitude-index bits the enumeration holds at 0 (the kernel addresses their 1-partners itself);
 // oneMask : amplitude-index bits that must be 1 (controls).  Bits below log2(vec) never enter the plan: a low
 // zero-bit is handled inside the vector by the kernel (TLO), low one-bits become the lane predicate loMask.
-inline Planned makePlan(long long n, int vec, std::initializer_list<int> zeroBits, unsigned long long oneMask) {
+inline Planned makePlan(long long n, int vec, const std::vector<int>& zeroBits, unsigned long long oneMask) {
     const int v = log2u((unsigned long long)vec);
     Planned out;
     std::memset(&out.plan, 0, sizeof out.plan);
@@ -61,6 +61,10 @@ inline Planned makePlan(long long n, int vec, std::initializer_list<int> zeroBit
     for (int i = 0; i < out.plan.nIns; ++i) out.plan.pos[i] = pos[i];
     out.nTasks = ((unsigned long long)n / vec) >> out.plan.nIns;
     return out;
+}
+
+inline Planned makePlan(long long n, int vec, std::initializer_list<int> zeroBits, unsigned long long oneMask) {
+    return makePlan(n, vec, std::vector<int>(zeroBits), oneMask);
 }
 
 // host twin of the device-side qb::expand (qb_device.cuh)
@@ -224,6 +228,65 @@ inline SlotSwap planSwapIn(const QubitMap& m, int q, unsigned long long avoidMas
     s.globalSlot = p;
     s.localSlot = best;
     return s;
+}
+
+// Slabs: a pass and the slot exchange that follows it can be pipelined if both are cut along the same index bits -
+// slab s = the amplitudes whose slab bits hold the value s.  The exchange of slab s needs only the pass on slab s
+// (on both GPUs of the pair), so it runs over NVLink while the pass computes slab s+1.  Slab bits are the highest
+// local bits that the pass does not hold in registers (`busyMask`) and that are not the exchange's local slot.
+struct SlabPlan {
+    int nBits;
+    int bits[3];  // ascending
+    unsigned long long valueMask(int slab) const {
+        unsigned long long m = 0;
+        for (int j = 0; j < nBits; ++j)
+            if ((slab >> j) & 1) m |= 1ull << bits[j];
+        return m;
+    }
+};
+
+inline SlabPlan planSlabs(int localBits, unsigned long long busyMask, int want, int lowestAllowed) {
+    SlabPlan p{0, {0, 0, 0}};
+    int found[3];
+    for (int b = localBits - 1; b >= lowestAllowed && p.nBits < want && p.nBits < 3; --b)
+        if (!((busyMask >> b) & 1)) found[p.nBits++] = b;
+    for (int j = 0; j < p.nBits; ++j) p.bits[j] = found[p.nBits - 1 - j];
+    return p;
+}
+
+// This rank's k_swapPeer launch for exchanging local slot l with a shard-selecting slot: the pairs
+// a[j | 2^l] <-> b[j] (j with bit l clear) are divided between the two GPUs on `split`, the highest local bit that
+// is neither l nor a slab bit; the upper rank (shard-selecting bit 0) takes split = 0.  With a slab plan only the
+// pairs inside slab `slab` are enumerated.
+struct SwapLaunch {
+    bool active;
+    Planned planned;
+};
+
+inline SwapLaunch planSlotSwap(int localBits, int vec, int l, bool amUpper, const SlabPlan* sp, int slab) {
+    SwapLaunch out;
+    out.active = false;
+    std::memset(&out.planned, 0, sizeof out.planned);
+    const int v = log2u((unsigned long long)vec);
+    unsigned long long slabBits = 0;
+    if (sp)
+        for (int j = 0; j < sp->nBits; ++j) slabBits |= 1ull << sp->bits[j];
+    int split = -1;
+    for (int b = localBits - 1; b >= v; --b)
+        if (b != l && !((slabBits >> b) & 1)) {
+            split = b;
+            break;
+        }
+    if (split < 0 && !amUpper) return out;
+    std::vector<int> zero{l};
+    if (split >= 0) zero.push_back(split);
+    if (sp)
+        for (int j = 0; j < sp->nBits; ++j) zero.push_back(sp->bits[j]);
+    out.planned = makePlan(1LL << localBits, vec, zero, 0);
+    if (split >= 0 && !amUpper) out.planned.plan.setMask |= 1ull << (split - v);
+    if (sp) out.planned.plan.setMask |= sp->valueMask(slab) >> v;
+    out.active = out.planned.nTasks != 0;
+    return out;
 }
 
 // The transpositions that restore the identity layout (each is its own inverse).

@@ -278,3 +278,51 @@ def test_qubit_remap_keeps_the_state_and_ends_canonical(world, seed):
     for k in range(n_back):
         cur = _swap_bits(cur, canon[2 * k], canon[2 * k + 1])
     np.testing.assert_allclose(cur, want, atol=1e-12)
+
+
+# ---- slab pipeline: fused pass || slot exchange (qb::planSlabs, qb::planSlotSwap) ------------------------------
+
+def _expand(k, pos, set_mask):
+    for b in pos:
+        low = k & ((1 << b) - 1)
+        k = ((k >> b) << (b + 1)) | low
+    return k | set_mask
+
+
+@pytest.mark.parametrize("local_bits,vec,local_slot,busy_extra", [(10, 1, 4, 0b1100000011), (10, 2, 6, 0b0000001111),
+                                                                   (12, 4, 10, 0b110000000011), (9, 4, 2, 0b111100000),
+                                                                   (11, 2, 10, 0b01111000000)])
+def test_slab_exchanges_cover_the_exchange_exactly_once(local_bits, vec, local_slot, busy_extra):
+    """Every pair a[j | 2^l] <-> b[j] of a slot exchange is moved by exactly one (slab, rank) launch, stays inside its
+    slab, and the slab bits avoid the busy bits; the union over slabs equals the unsliced exchange."""
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    lib.qb200_debugSlabs.restype = ctypes.c_int
+    busy = busy_extra | (1 << local_slot)
+    v = vec.bit_length() - 1
+    for want in (0, 1, 2, 3):
+        bits = (ctypes.c_int * 3)()
+        out = (ctypes.c_ulonglong * (11 * 2 * 8))()
+        nb = lib.qb200_debugSlabs(local_bits, ctypes.c_ulonglong(busy), want, v + 1, vec, local_slot, bits, out)
+        slab_bits = list(bits[:nb])
+        assert nb <= want and slab_bits == sorted(slab_bits)
+        assert all(not (busy >> b) & 1 and v < b < local_bits for b in slab_bits)
+        # the highest free bits are taken
+        free = [b for b in range(local_bits - 1, v, -1) if not (busy >> b) & 1]
+        assert sorted(free[:min(want, len(free))]) == slab_bits
+        seen = np.zeros(1 << local_bits, dtype=np.int32)  # per b-side index j: how many launches moved it
+        for s in range(1 << nb):
+            slab_val = sum(((s >> j) & 1) << slab_bits[j] for j in range(nb))
+            for r in range(2):
+                o = out[11 * (2 * s + r):11 * (2 * s + r + 1)]
+                n_tasks, n_ins, set_mask = int(o[0]), int(o[1]), int(o[2])
+                pos = [int(x) for x in o[3:3 + n_ins]]
+                for k in range(n_tasks):
+                    vi = _expand(k, pos, set_mask)
+                    for e in range(vec):
+                        j = vi * vec + e
+                        assert not (j >> local_slot) & 1
+                        assert all(((j >> slab_bits[b]) & 1) == ((s >> b) & 1) for b in range(nb)), (j, s)
+                        assert (j & sum(1 << b for b in slab_bits)) == slab_val
+                        seen[j] += 1
+        want_seen = np.array([0 if (j >> local_slot) & 1 else 1 for j in range(1 << local_bits)], dtype=np.int32)
+        assert np.array_equal(seen, want_seen)

@@ -8,6 +8,7 @@ Every rank drives its shard through the CUDA library; rank 0 gathers the shards 
 running the same circuit on one unsharded register: measurement-free circuits must match bit for bit, circuits with
 measurements must give the same outcomes and amplitudes to 1e-12 relative (north_star)."""
 import argparse
+import ctypes
 import os
 import sys
 
@@ -124,6 +125,11 @@ def main():
                     print("   scalar", i, circuits.run_api_sequence.last_labels[i], "gpu", scal[i], "cpu", cscal[i], flush=True)
             print(f"api fuzz case {case}: {nq} qubits, {len(calls)} calls over 4 registers on {world} GPUs: scalars_ok={scal_ok} "
                   f"states_ok={st_ok} -> {'PASS' if good else 'FAIL'}", flush=True)
+    lib.lib.qb200_getOverlappedExchangeCount.restype = ctypes.c_ulonglong
+    lib.lib.qb200_getSlotExchangeCount.restype = ctypes.c_ulonglong
+    if rank == 0:
+        print(f"slot exchanges: {lib.lib.qb200_getSlotExchangeCount()}, of which pipelined with the preceding fused pass: "
+              f"{lib.lib.qb200_getOverlappedExchangeCount()}", flush=True)
     flag = torch.tensor([1 if ok else 0])
     dist.broadcast(flag, 0)
     lib.destroyQuESTEnv(env)
