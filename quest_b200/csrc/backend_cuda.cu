@@ -74,8 +74,11 @@ struct Engine {
     int swapCtasPerSm = 1;          // QUEST_B200_SWAP_CTAS: footprint of a pipelined exchange
     int overlapMinBits = 24;        // ... for shards of at least 2^24 amplitudes (QUEST_B200_OVERLAP_MIN_BITS: tests)
     cudaStream_t comm = nullptr;    // high-priority stream of the pipelined exchanges (sharded runs only)
-    cudaEvent_t slabEv[8] = {};     // pass on slab s has been enqueued up to here
-    cudaEvent_t commDone = nullptr;
+    cudaEvent_t slabEv[8] = {};     // engine stream: the pass before an exchange has finished slab s
+    cudaEvent_t xDone[8] = {};      // communication stream: slab s of the exchange is complete on both GPUs
+    cudaEvent_t commDone = nullptr; // communication stream: the whole exchange is
+    void* pendingReg = nullptr;     // register whose last exchange the engine stream has not waited for yet ...
+    SlabPlan pendingPlan{0, {0, 0, 0}};  // ... and how it was cut
     unsigned long long overlapped = 0;
     bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fusedEvents;
@@ -356,16 +359,72 @@ void runGroup(const Qureg& q, const std::vector<PendingOp>& ops, const FusedGrou
     g.fusedGates += grp.count;
 }
 
+// A pipelined exchange (flushThenExchange) returns while its last slabs are still moving; the engine stream catches
+// up here before anything else touches that register.
+void settle() {
+    if (!g.pendingReg) return;
+    CUDA_OK(cudaStreamWaitEvent(g.stream, g.commDone, 0));
+    g.pendingReg = nullptr;
+}
+
+inline u64 bitsOf(const SlabPlan& sp) {
+    u64 m = 0;
+    for (int j = 0; j < sp.nBits; ++j) m |= 1ull << sp.bits[j];
+    return m;
+}
+inline u64 bitsOf(const FusedGroup& grp) {
+    u64 m = 0;
+    for (int j = 0; j < kFuseBits; ++j) m |= 1ull << grp.bits[j];
+    return m;
+}
+
+// One fused group cut along `sp`: slab s starts once `waitFor[s]` has happened (the exchange before it delivered that
+// slab) and `record[s]` marks its end (the exchange after it may take that slab).
+void runGroupInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const FusedGroup& grp, const SlabPlan& sp,
+                     const cudaEvent_t* waitFor, const cudaEvent_t* record) {
+    const bool noisy = prepareGroup(ops, grp);
+    FusedTimer t;
+    bool started = false;
+    for (int s = 0; s < (1 << sp.nBits); ++s) {
+        if (waitFor) CUDA_OK(cudaStreamWaitEvent(g.stream, waitFor[s], 0));
+        if (!started) {  // after the first wait, so that the measured time is the pass and not the exchange before it
+            t.start();
+            started = true;
+        }
+        launchPrepared(rec(q), noisy, &sp, s);
+        if (record) CUDA_OK(cudaEventRecord(record[s], g.stream));
+    }
+    t.stop();
+    ++g.fusedLaunches;
+    g.fusedGates += grp.count;
+}
+
 // Execute everything recorded for this register: single gates through their own kernel, runs of gates through
 // k_fused (one HBM pass per group, qb_fuse.h).
 void flush(const Qureg& q) {
     QuregRec* r = rec(q);
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
-    if (r->queue.empty()) return;
+    const bool pending = g.pendingReg == r;
+    if (r->queue.empty()) {
+        if (pending) settle();
+        return;
+    }
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
-    for (const FusedGroup& grp : groupOps(ops, r->localBits)) runGroup(q, ops, grp);
+    const std::vector<FusedGroup> groups = groupOps(ops, r->localBits, pending ? bitsOf(g.pendingPlan) : 0);
+    size_t first = 0;
+    if (pending) {
+        // the first pass follows the exchange slab by slab if it can be cut the same way
+        if (groups[0].count > 1 && !(bitsOf(groups[0]) & bitsOf(g.pendingPlan))) {
+            runGroupInSlabs(q, ops, groups[0], g.pendingPlan, g.xDone, nullptr);
+            g.pendingReg = nullptr;  // the last slab waited for the last piece of the exchange
+            first = 1;
+        } else {
+            settle();
+        }
+    }
+    for (size_t i = first; i < groups.size(); ++i) runGroup(q, ops, groups[i]);
 }
 
 void flushAll() {
@@ -379,6 +438,7 @@ void flushAll() {
         q.numChunks = g.world;
         flush(q);
     }
+    settle();
 }
 
 // The k_swapPeer launch of a slot exchange, whole shard (sp == nullptr) or one slab, bracketed by nothing: the
@@ -409,6 +469,7 @@ void launchSwap(const Qureg& q, SlotSwap sw, const SlabPlan* sp, int slab, cudaS
 // Exchange a shard-selecting bit position with a local one; caller has flushed the queue.
 void exchangeSlots(const Qureg& q, SlotSwap sw) {
     QuregRec* r = rec(q);
+    settle();
     const comm::Partner peer = comm::partnerOf(q, sw.globalSlot - r->localBits);
     comm::pairBarrier(peer.rank, g.stream);  // partner has finished everything enqueued before the exchange
     launchSwap(q, sw, nullptr, 0, g.stream);
@@ -417,87 +478,65 @@ void exchangeSlots(const Qureg& q, SlotSwap sw) {
     ++g.slotSwaps;
 }
 
-// flush(q) followed by exchangeSlots(q, sw), with the last fused pass and the exchange cut into slabs
-// (qb::planSlabs) and pipelined: the pass runs slab after slab on the engine stream; as soon as slab s is done on
-// both GPUs of the pair (event + handshake on the communication stream) its half goes over NVLink while the pass
-// computes slab s+1.  The pass is bound by fp64 issue, the exchange by NVLink, so they overlap almost completely.
+// flush(q) followed by exchangeSlots(q, sw), pipelined.  The exchange and the fused passes on either side of it are
+// cut into slabs (qb::planSlabs): on the communication stream slab s of the exchange starts as soon as the pass before
+// it has finished slab s on both GPUs of the pair (event + handshake) and moves over NVLink while that pass computes
+// slab s+1; the call returns without waiting, and the first pass recorded afterwards follows the exchange slab by
+// slab in the same way (flush).  Passes are bound by fp64 issue, the exchange by NVLink, so they overlap.
 void flushThenExchange(const Qureg& q, SlotSwap sw) {
     QuregRec* r = rec(q);
     // Both GPUs of the pair must cut along the same bits and issue the same handshakes, whatever their own queues hold:
     // everything below that shapes the protocol derives from rank-independent state.
     const u64 busy = r->denseSinceFlush | (1ull << sw.localSlot);
     const int spare = r->localBits - __builtin_popcountll(busy & ((1ull << r->localBits) - 1)) - kFuseBits;
-    const int lowest = std::min(16, g.overlapMinBits / 2 + 2);
     SlabPlan sp{0, {0, 0, 0}};
-    if (g.overlap && g.comm && r->callsSinceFlush > 0 && r->localBits >= g.overlapMinBits && spare > 0)
-        sp = planSlabs(r->localBits, busy, std::min(kMaxSlabBits, spare), lowest);
+    const bool eligible = g.overlap && g.comm && r->callsSinceFlush > 0 && r->localBits >= g.overlapMinBits;
+    bool chained = false;  // the previous exchange of this register is still in flight and is cut the same way
+    if (eligible && g.pendingReg == r && !(bitsOf(g.pendingPlan) & busy) && spare >= g.pendingPlan.nBits) {
+        sp = g.pendingPlan;
+        chained = true;
+    } else if (eligible && spare > 0) {
+        sp = planSlabs(r->localBits, busy, std::min(kMaxSlabBits, spare), std::min(16, g.overlapMinBits / 2 + 2));
+    }
     if (sp.nBits == 0) {
         flush(q);
         exchangeSlots(q, sw);
         return;
     }
-    u64 slabBits = 0;
-    for (int j = 0; j < sp.nBits; ++j) slabBits |= 1ull << sp.bits[j];
+    if (!chained) settle();
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
-    const std::vector<FusedGroup> groups = groupOps(ops, r->localBits, slabBits);
-    for (size_t i = 0; i + 1 < groups.size(); ++i) runGroup(q, ops, groups[i]);
-    // this rank's last group, if it is a fused pass, is the one that is cut into slabs
-    const bool cut = !groups.empty() && groups.back().count > 1;
-    if (!groups.empty() && !cut) runGroup(q, ops, groups.back());
-    const comm::Partner peer = comm::partnerOf(q, sw.globalSlot - r->localBits);
-    const bool noisy = cut ? prepareGroup(ops, groups.back()) : false;
-    FusedTimer t;
-    if (cut) t.start();
-    static const bool trace = std::getenv("QUEST_B200_OVERLAP_TRACE") != nullptr;
-    cudaEvent_t tr0 = nullptr, trPass[8] = {}, trSwapIn[8] = {}, trSwapOut[8] = {};
-    if (trace) {
-        CUDA_OK(cudaEventCreate(&tr0));
-        CUDA_OK(cudaEventRecord(tr0, g.stream));
-    }
-    for (int s = 0; s < (1 << sp.nBits); ++s) {
-        if (cut) launchPrepared(r, noisy, &sp, s);
-        CUDA_OK(cudaEventRecord(g.slabEv[s], g.stream));
-        if (trace) {
-            CUDA_OK(cudaEventCreate(&trPass[s]));
-            CUDA_OK(cudaEventRecord(trPass[s], g.stream));
+    const std::vector<FusedGroup> groups = groupOps(ops, r->localBits, bitsOf(sp));
+    const int nSlabs = 1 << sp.nBits;
+    bool signalled = false;  // the last pass recorded slabEv[] itself
+    for (size_t i = 0; i < groups.size(); ++i) {
+        const bool isFirst = i == 0, isLast = i + 1 == groups.size();
+        const bool fusedPass = groups[i].count > 1;
+        const bool follow = chained && isFirst && fusedPass;  // dense targets never sit on slab bits: see `busy`
+        if (chained && isFirst && !follow) settle();
+        if (fusedPass && (follow || isLast)) {
+            runGroupInSlabs(q, ops, groups[i], sp, follow ? g.xDone : nullptr, isLast ? g.slabEv : nullptr);
+            signalled = signalled || isLast;
+        } else {
+            runGroup(q, ops, groups[i]);
         }
+    }
+    // (with an empty queue a chained exchange simply queues up behind the previous one on the communication stream)
+    if (!signalled)
+        for (int s = 0; s < nSlabs; ++s) CUDA_OK(cudaEventRecord(g.slabEv[s], g.stream));
+    const comm::Partner peer = comm::partnerOf(q, sw.globalSlot - r->localBits);
+    for (int s = 0; s < nSlabs; ++s) {
         CUDA_OK(cudaStreamWaitEvent(g.comm, g.slabEv[s], 0));
         comm::pairBarrier(peer.rank, g.comm, 1);  // the partner has finished slab s too
-        if (trace) {
-            CUDA_OK(cudaEventCreate(&trSwapIn[s]));
-            CUDA_OK(cudaEventRecord(trSwapIn[s], g.comm));
-        }
         launchSwap(q, sw, &sp, s, g.comm);
-        if (trace) {
-            CUDA_OK(cudaEventCreate(&trSwapOut[s]));
-            CUDA_OK(cudaEventRecord(trSwapOut[s], g.comm));
-        }
+        comm::pairBarrier(peer.rank, g.comm, 1);  // the partner's remote writes into this slab have landed
+        CUDA_OK(cudaEventRecord(g.xDone[s], g.comm));
     }
-    if (trace) {
-        CUDA_OK(cudaStreamSynchronize(g.comm));
-        CUDA_OK(cudaStreamSynchronize(g.stream));
-        std::fprintf(stderr, "[rank %d] pipelined exchange, %d slabs (ms since the first slab was enqueued):\n", g.rank, 1 << sp.nBits);
-        for (int s = 0; s < (1 << sp.nBits); ++s) {
-            float a = 0, b = 0, c = 0;
-            cudaEventElapsedTime(&a, tr0, trPass[s]);
-            cudaEventElapsedTime(&b, tr0, trSwapIn[s]);
-            cudaEventElapsedTime(&c, tr0, trSwapOut[s]);
-            std::fprintf(stderr, "  slab %d: pass done %.3f   swap start %.3f   swap done %.3f\n", s, a, b, c);
-            cudaEventDestroy(trPass[s]); cudaEventDestroy(trSwapIn[s]); cudaEventDestroy(trSwapOut[s]);
-        }
-        cudaEventDestroy(tr0);
-    }
-    if (cut) {
-        t.stop();
-        ++g.fusedLaunches;
-        g.fusedGates += groups.back().count;
-    }
-    comm::pairBarrier(peer.rank, g.comm, 1);  // the partner's remote writes into this shard have landed
     CUDA_OK(cudaEventRecord(g.commDone, g.comm));
-    CUDA_OK(cudaStreamWaitEvent(g.stream, g.commDone, 0));
+    g.pendingReg = r;
+    g.pendingPlan = sp;
     r->map.applySwap(sw.globalSlot, sw.localSlot);
     ++g.slotSwaps;
     ++g.overlapped;
@@ -524,6 +563,7 @@ inline QuregRec* canon(const Qureg& q) {
 // the state is about to be overwritten as a whole: drop pending gates and forget the layout
 inline QuregRec* fresh(const Qureg& q) {
     QuregRec* r = rec(q);
+    if (g.pendingReg == r) settle();
     r->queue.clear();
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
@@ -772,6 +812,7 @@ QuESTEnv createQuESTEnv(void) {
         CUDA_OK(cudaDeviceGetStreamPriorityRange(&lowPrio, &highPrio));
         CUDA_OK(cudaStreamCreateWithPriority(&g.comm, cudaStreamNonBlocking, highPrio));
         for (cudaEvent_t& e : g.slabEv) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (cudaEvent_t& e : g.xDone) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         CUDA_OK(cudaEventCreateWithFlags(&g.commDone, cudaEventDisableTiming));
     }
     env.rank = g.rank;
@@ -792,6 +833,7 @@ void destroyQuESTEnv(QuESTEnv env) {
         CUDA_OK(cudaStreamSynchronize(g.comm));
         cudaStreamDestroy(g.comm);
         for (cudaEvent_t e : g.slabEv) cudaEventDestroy(e);
+        for (cudaEvent_t e : g.xDone) cudaEventDestroy(e);
         cudaEventDestroy(g.commDone);
     }
     if (g.world > 1) comm::shutdown();
@@ -887,6 +929,7 @@ void statevec_destroyQureg(Qureg qureg, QuESTEnv env) {
     QuregRec* r = rec(qureg);
     if (!r) return;
     r->queue.clear();  // gates never observed need not run
+    if (g.pendingReg == r) settle();
     liveRegisters.erase(std::remove(liveRegisters.begin(), liveRegisters.end(), r), liveRegisters.end());
     CUDA_OK(cudaStreamSynchronize(g.stream));
     if (g.world > 1) comm::unregisterShard(qureg);
