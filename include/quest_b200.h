@@ -41,6 +41,12 @@ void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long*
 void qb200_setOverlap(int enabled);
 unsigned long long qb200_getOverlappedExchangeCount(void);
 
+/* calcProbOfOutcome on state-vectors: the second query on an unchanged state computes P(qubit = 0) for EVERY qubit in
+ * one pass over HBM; further queries are answered from that result until any call changes the state (e.g. the per-qubit
+ * read-out after a QFT costs two passes instead of one per qubit).  QUEST_B200_PROB_CACHE=0 disables it.  Registers whose
+ * device pointers were handed out (qb200_getDevicePointers) are never cached.  The reference recomputes every query
+ * (QuEST_cpu_local.c:267, QuEST_cpu.c:2844). */
+
 /* Bulk state I/O.  setAmps / initStateFromAmps / setDensityAmps and qb200_copyAmpsToHost accept any host pointer.  From
  * pinned memory the copy runs at the PCIe rate as it is; from pageable memory (malloc, numpy) transfers of 8 MiB and more
  * are staged through pinned buffers by several worker threads (QUEST_B200_IO_THREADS, default min(8, cores/2)).  The

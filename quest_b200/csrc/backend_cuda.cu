@@ -63,6 +63,11 @@ struct Engine {
     unsigned int* dTicket = nullptr;
     double* dResult = nullptr;      // [4]
     double* hResult = nullptr;      // pinned [4]
+    double* dWidePartials = nullptr; // [kProbAll * wideBlocks]: scratch of the all-qubit probability pass
+    unsigned int wideBlocks = 0;
+    double* dWide = nullptr;        // [kProbAll]
+    double* hWide = nullptr;        // pinned [kProbAll]
+    bool probCache = true;          // QUEST_B200_PROB_CACHE
     int vecCap = 4;                 // QUEST_B200_VEC: upper bound on amplitudes per vector (1, 2 or 4)
     unsigned long long launches = 0;
     bool fuse = true;               // QUEST_B200_FUSE / qb200_setFusion: record gates and run them in fused passes
@@ -94,6 +99,12 @@ struct QuregRec {
     // the last flush and which bit positions they used as dense targets.  Decisions two GPUs must agree on use these.
     size_t callsSinceFlush = 0;
     u64 denseSinceFlush = 0;
+    // calcProbOfOutcome: the second query on an unchanged state computes P(qubit = 0) for every qubit in one pass;
+    // later queries are answered from here until the state changes (dirty()).
+    bool probValid = false;
+    bool exposed = false;  // device pointers were handed out (qb200_getDevicePointers): the state can change unseen
+    int probQueries = 0;
+    double probZero[64];
     QubitMap map;                  // where each logical qubit lives (qb_plan.h); identity unless sharded
 };
 
@@ -103,6 +114,12 @@ constexpr size_t kQueueCap = 8192;
 inline QuregRec* rec(const Qureg& q) { return reinterpret_cast<QuregRec*>(q.pairStateVec.real); }
 
 inline int log2i(u64 x) { return qb::log2u(x); }
+
+// the amplitudes of this register are about to change (or may be changed behind our back)
+inline void dirty(QuregRec* r) {
+    r->probValid = false;
+    r->probQueries = 0;
+}
 
 void requireEngine() {
     if (!g.up) {
@@ -564,6 +581,7 @@ inline QuregRec* canon(const Qureg& q) {
 inline QuregRec* fresh(const Qureg& q) {
     QuregRec* r = rec(q);
     if (g.pendingReg == r) settle();
+    dirty(r);
     r->queue.clear();
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
@@ -575,6 +593,7 @@ inline QuregRec* fresh(const Qureg& q) {
 // this rank either drops them or has nothing to do.
 void submit(const Qureg& q, PendingOp op) {
     QuregRec* r = rec(q);
+    dirty(r);
     // logical qubits -> current bit positions; a dense target living in a shard-selecting slot is first made local
     if (g.world > 1) {
         if (!isDiagonal(op.kind)) {
@@ -714,9 +733,34 @@ double sumSquares(const Qureg& q) {
     return s;
 }
 
-double probOfZero(const Qureg& q, int t) {
+// All index bits of the shard in one pass (k_probAllZero), reduced over the shards, stored per LOGICAL qubit.
+void fillProbCache(const Qureg& q, QuregRec* r) {
+    const int vec = pickVec(r->n);
+    const u64 nVec = (u64)r->n / vec;
+    const unsigned int blocks = (unsigned int)std::min<u64>(g.wideBlocks, (nVec + kBlock - 1) / kBlock);
+    dispatchV(vec, [&](auto V) {
+        k_probAllZero<decltype(V)::value><<<blocks, kBlock, 0, g.stream>>>(r->re, r->im, nVec, r->localBits,
+                                                                           g.dWidePartials, g.dTicket, g.dWide);
+    });
+    launched();
+    if (g.world > 1) {
+        k_probAllShardBits<<<1, 1, 0, g.stream>>>(g.dWide, r->localBits, log2i((u64)g.world), q.chunkId);
+        launched();
+        comm::allReduceSum(g.dWide, kProbAll, g.stream);
+    }
+    CUDA_OK(cudaMemcpyAsync(g.hWide, g.dWide, kProbAll * sizeof(double), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_OK(cudaStreamSynchronize(g.stream));
+    for (int lq = 0; lq < r->map.nQubits; ++lq) r->probZero[lq] = g.hWide[r->map.phys[lq]];
+    r->probValid = true;
+}
+
+double probOfZero(const Qureg& q, int tLogical) {
     QuregRec* r = live(q);
-    t = r->map.phys[t];
+    if (g.probCache && !r->exposed && r->map.nQubits < kProbAll - 1) {
+        if (!r->probValid && ++r->probQueries >= 2) fillProbCache(q, r);
+        if (r->probValid) return r->probZero[tLogical];
+    }
+    const int t = r->map.phys[tLogical];
     if (t >= r->localBits) {
         // the measured qubit selects the shard: shards with the bit set contribute 0, the others everything
         // (QuEST_cpu_distributed.c:1227-1247)
@@ -793,6 +837,11 @@ QuESTEnv createQuESTEnv(void) {
     CUDA_OK(cudaMemset(g.dTicket, 0, sizeof(unsigned int)));
     CUDA_OK(cudaMalloc(&g.dResult, 4 * sizeof(double)));
     CUDA_OK(cudaHostAlloc(&g.hResult, 4 * sizeof(double), cudaHostAllocDefault));
+    g.wideBlocks = (unsigned int)g.numSMs * 4;
+    CUDA_OK(cudaMalloc(&g.dWidePartials, (size_t)kProbAll * g.wideBlocks * sizeof(double)));
+    CUDA_OK(cudaMalloc(&g.dWide, kProbAll * sizeof(double)));
+    CUDA_OK(cudaHostAlloc(&g.hWide, kProbAll * sizeof(double), cudaHostAllocDefault));
+    if (const char* s = std::getenv("QUEST_B200_PROB_CACHE")) g.probCache = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_FUSE")) g.fuse = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_FMA")) g.contract = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_REMAP")) g.remap = std::atoi(s) != 0;
@@ -842,6 +891,9 @@ void destroyQuESTEnv(QuESTEnv env) {
     cudaFree(g.dTicket);
     cudaFree(g.dResult);
     cudaFreeHost(g.hResult);
+    cudaFree(g.dWidePartials);
+    cudaFree(g.dWide);
+    cudaFreeHost(g.hWide);
     if (g.ownsStream) cudaStreamDestroy(g.stream);
     g = Engine();
 }
@@ -941,6 +993,7 @@ void statevec_destroyQureg(Qureg qureg, QuESTEnv env) {
 // host -> device slice copy; complete on return, as in the reference (QuEST_gpu.cu:34-49)
 void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, idx_t numAmps) {
     QuregRec* r = (startInd == 0 && numAmps == qureg.numAmpsTotal) ? fresh(qureg) : canon(qureg);
+    dirty(r);
     const idx_t off = (idx_t)qureg.chunkId * r->n;
     idx_t lo = std::max<idx_t>(startInd - off, 0), hi = std::min<idx_t>(startInd - off + numAmps, r->n);
     if (hi > lo) {
@@ -1186,6 +1239,7 @@ qreal densmatr_calcFidelity(Qureg rho, Qureg psi) {
 
 void statevec_collapseToKnownProbOutcome(Qureg q, const int tLogical, int outcome, qreal prob) {
     QuregRec* r = live(q);
+    dirty(r);
     const int t = r->map.phys[tLogical];
     const qreal renorm = 1 / sqrt((double)prob);
     const int vec = pickVec(r->n);
@@ -1268,6 +1322,7 @@ static void dephase2Now(const Qureg& q, QuregRec* r, int q1, int q2, qreal retai
 
 void densmatr_twoQubitDephase(Qureg q, const int q1, const int q2, qreal dephase) {
     QuregRec* r = live(q);
+    dirty(r);
     const qreal retain = 1 - dephase;
     dephase2Now(q, r, q1, q2, retain);
 }
@@ -1293,6 +1348,7 @@ static void bringLocal(const Qureg& q, QuregRec* r, std::initializer_list<int> q
 void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
     if (level == 0) return;
     QuregRec* r = live(q);
+    dirty(r);
     const int n = q.numQubitsRepresented;
     bringLocal(q, r, {q1, q2, q1 + n, q2 + n},
                "two-qubit depolarising across shards (with QUEST_B200_REMAP=0, or a shard too small to re-home its qubits)");
@@ -1315,6 +1371,7 @@ void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
 
 void densmatr_addDensityMatrix(Qureg a, qreal p, Qureg b) {
     QuregRec *ra = canon(a), *rb = canon(b);
+    dirty(ra);
     const int vec = pickVec(ra->n);
     const u64 nVec = (u64)ra->n / vec;
     dispatchV(vec, [&](auto V) {
@@ -1403,6 +1460,8 @@ int qb200_getDevice(void) { return g.device; }
 
 void qb200_getDevicePointers(Qureg qureg, void** real, void** imag) {
     QuregRec* r = canon(qureg);
+    dirty(r);
+    r->exposed = true;  // the caller may write through these pointers at any time: no result is cached from now on
     *real = r->re;
     *imag = r->im;
 }

@@ -505,6 +505,49 @@ __global__ void __launch_bounds__(kBlock) k_probZero(const qreal* __restrict__ r
     finishReduce<1>(acc, partials, ticket, result);
 }
 
+// P(bit b = 0) for EVERY index bit b of the shard in one pass, plus the total: acc[b] for b < nBits, acc[kProbAll-1].
+// Serves the second and later calcProbOfOutcome calls on an unchanged state (backend_cuda.cu: probOfZero), e.g. the
+// per-qubit read-out after a QFT: one pass instead of one per qubit.
+constexpr int kProbAll = 40;
+
+template <int VEC>
+__global__ void __launch_bounds__(kBlock) k_probAllZero(const qreal* __restrict__ re, const qreal* __restrict__ im,
+                                                       unsigned long long nVec, int nBits, double* partials,
+                                                       unsigned int* ticket, double* result) {
+    constexpr int LOW = VEC == 4 ? 2 : (VEC == 2 ? 1 : 0);  // index bits that live inside one vector
+    double acc[kProbAll];
+#pragma unroll
+    for (int b = 0; b < kProbAll; ++b) acc[b] = 0.0;
+    const unsigned long long stride = (unsigned long long)gridDim.x * kBlock;
+#pragma unroll 2
+    for (unsigned long long k = (unsigned long long)blockIdx.x * kBlock + threadIdx.x; k < nVec; k += stride) {
+        const unsigned long long i = k * VEC;
+        const Vec<qreal, VEC> R = load<VEC>(re + i), I = load<VEC>(im + i);
+        double p[VEC], sum = 0.0;
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) {
+            p[e] = (double)(R.v[e] * R.v[e] + I.v[e] * I.v[e]);
+            sum += p[e];
+        }
+#pragma unroll
+        for (int b = 0; b < LOW; ++b)
+#pragma unroll
+            for (int e = 0; e < VEC; ++e)
+                if (!((e >> b) & 1)) acc[b] += p[e];
+#pragma unroll
+        for (int b = LOW; b < kProbAll - 1; ++b)
+            if (b < nBits) acc[b] += ((i >> b) & 1ull) ? 0.0 : sum;
+        acc[kProbAll - 1] += sum;
+    }
+    finishReduce<kProbAll>(acc, partials, ticket, result);
+}
+
+// Bits that select the shard: a shard contributes everything or nothing (QuEST_cpu_distributed.c:1227-1247).
+__global__ void k_probAllShardBits(double* result, int localBits, int nShardBits, int chunkId) {
+    for (int gb = 0; gb < nShardBits && localBits + gb < kProbAll - 1; ++gb)
+        result[localBits + gb] = ((chunkId >> gb) & 1) ? 0.0 : result[kProbAll - 1];
+}
+
 // sum |amp|^2 over every amplitude: calcTotalProb (state-vector) and calcPurity (density)
 template <int VEC>
 __global__ void __launch_bounds__(kBlock) k_sumSquares(const qreal* __restrict__ re, const qreal* __restrict__ im,

@@ -264,6 +264,45 @@ def test_contracted_arithmetic_is_opt_in_and_within_tolerance(product, product_e
     assert not np.array_equal(got[1].view(np.float64), want.view(np.float64))  # the mode really changes the arithmetic
 
 
+@pytest.mark.parametrize("nq,seed", [(5, 61), (13, 62), (20, 63)])
+def test_all_qubit_probabilities_come_from_one_pass_and_follow_the_state(product, product_env, oracle, oracle_env, nq, seed):
+    """The second calcProbOfOutcome on an unchanged state computes every qubit's probability in one pass; later queries
+    launch nothing; anything that changes the state (gate, collapse, partial setAmps, re-initialisation) is seen."""
+    product.lib.qb200_getLaunchCount.restype = ctypes.c_ulonglong
+    ops = circuits.random_circuit(nq, 120, seed, density=False, measure=False)
+    gq, cq = product.createQureg(nq, product_env), oracle.createQureg(nq, oracle_env)
+    for lib, q in ((product, gq), (oracle, cq)):
+        circuits.prepare(lib, q, seed)
+        circuits.run_circuit(lib, q, ops, seed=seed)
+
+    def sweep():
+        for t in range(nq):
+            for outcome in (0, 1):
+                got, want = product.calcProbOfOutcome(gq, t, outcome), oracle.calcProbOfOutcome(cq, t, outcome)
+                assert abs(got - want) <= 1e-12, (t, outcome, got, want)
+
+    sweep()
+    before = product.lib.qb200_getLaunchCount()
+    sweep()
+    assert product.lib.qb200_getLaunchCount() == before  # answered from the cached pass
+    angle = float(np.random.default_rng(seed).uniform(0.1, 1.0))
+    mutations = [
+        lambda lib, q: lib.hadamard(q, nq // 2),
+        lambda lib, q: lib.collapseToOutcome(q, 1, 0) if lib.calcProbOfOutcome(q, 1, 0) > 1e-6 else lib.pauliX(q, 1),
+        lambda lib, q: lib.set_state(q, np.array([0.25 - 0.5j, 0.125j, -0.375]), start=3),
+        lambda lib, q: lib.controlledPhaseShift(q, 0, nq - 1, 0.4),
+        lambda lib, q: lib.initPlusState(q),
+        lambda lib, q: lib.rotateY(q, nq - 1, angle),
+    ]
+    for m in mutations:
+        m(product, gq)
+        m(oracle, cq)
+        sweep()
+        sweep()
+    product.destroyQureg(gq, product_env)
+    oracle.destroyQureg(cq, oracle_env)
+
+
 def test_queue_is_drained_by_every_observer(product, product_env, oracle, oracle_env):
     """Pending gates must be visible to clone, inner product, compare, collapse, noise, setAmps and getAmp."""
     nq = 9

@@ -44,7 +44,10 @@ def main():
             extra += [("hadamard", t), ("compactUnitary", t, circuits.SWEEP_ALPHA, circuits.SWEEP_BETA), ("controlledNot", 0, t),
                       ("controlledNot", t, 1), ("pauliY", t), ("multiControlledUnitary", [2, (t - 1)], t, circuits._unitary(__import__("random").Random(t))),
                       ("calcProbOfOutcome", t, 1), ("phaseShift", t, 0.3), ("controlledPhaseShift", t, 3, 0.2)]
-        ops = extra + ops + extra
+        # every qubit's probability, asked twice: the second query on an unchanged state fills the all-qubit cache
+        # (one pass + shard-selecting bits + allreduce), the rest are answered from it - in the remapped layout
+        probes = [("calcProbOfOutcome", t, o) for o in (0, 1) for t in range(nq)]
+        ops = extra + ops[:len(ops) // 2] + probes + ops[len(ops) // 2:] + extra + probes
         if measure:  # a measurement whose qubit selects the shard: whole shards are kept or cleared
             ops += [("measure", nq - 1), ("calcTotalProb",), ("measureWithStats", nq - g), ("calcTotalProb",)]
         q = lib.createQureg(nq, env)
