@@ -380,7 +380,7 @@ def main():
                                        "achieved_GBps_per_direction": per_dir_cross,
                                        "frac_of_measured_peer_copy_770": per_dir_cross / 770.0,
                                        "frac_of_nominal_900": per_dir_cross / 900.0,
-                                       "includes": "two stream-ordered pair handshakes (NCCL send/recv of 4 bytes)"},
+                                       "includes": "two stream-ordered pair handshakes (sequence counter in the partner's memory + cuStreamWaitValue32)"},
                   "slot_exchange": {"kernel": "qb::k_swapPeer (makes a shard-selecting qubit local: half a shard each way)",
                                     "bytes_each_way_per_gpu": 8.0 * n_local, "ms": exchange_ms,
                                     "achieved_GBps_per_direction": 8.0 * n_local / (exchange_ms * 1e-3) / 1e9,
