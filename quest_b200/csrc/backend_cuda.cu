@@ -322,6 +322,12 @@ bool prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
     }
     fl.ctl[grp.count] = GateCtl{0, 0};
     for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = grp.bits[j];
+    for (int e = 0; e < (1 << kFuseBits); ++e) {
+        u64 o = 0;
+        for (int j = 0; j < kFuseBits; ++j)
+            if ((e >> j) & 1) o += 1ull << grp.bits[j];
+        fl.offBytes[e] = o * sizeof(qreal);
+    }
     fl.nGates = grp.count;
     return noisy;
 }

@@ -221,6 +221,7 @@ struct FusedLaunch {
     int nIns;                            // fused qubits + slab bits: positions held out of the thread index ...
     int ins[kFuseBits + kMaxSlabBits];   // ... ascending
     unsigned long long slabMask;         // value of the slab bits for this launch (0 for a whole-shard pass)
+    unsigned long long offBytes[1 << kFuseBits];  // byte offset of register element e from the thread's base amplitude
     unsigned long long nThreads;
     GateCtl ctl[kMaxFusedGates + 2];     // padded
     unsigned long long outerMask[kMaxFusedGates];  // control/selecting bits outside the fused qubits
@@ -359,15 +360,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
         }
     }
     const unsigned long long base = k | fl.slabMask;
-    unsigned long long off[E];
-#pragma unroll
-    for (int e = 0; e < E; ++e) {
-        unsigned long long o = 0;
-#pragma unroll
-        for (int j = 0; j < R; ++j)
-            if ((e >> j) & 1) o += 1ull << fl.pos[j];
-        off[e] = o;
-    }
+    // element e of the register block lives at base + sum of 2^pos[j] over the set bits j of e: byte offsets made by the
+    // host (FusedLaunch::offBytes), added here straight from the constant bank
+    char* const reBase = reinterpret_cast<char*>(re + base);
+    char* const imBase = reinterpret_cast<char*>(im + base);
+    auto reAt = [&](int e) { return reinterpret_cast<qreal*>(reBase + fl.offBytes[e]); };
+    auto imAt = [&](int e) { return reinterpret_cast<qreal*>(imBase + fl.offBytes[e]); };
     // Register index bit j <-> fused qubit pos[j].  When the lowest fused qubits are qubit 0 (and 1), neighbouring
     // register elements are neighbours in memory: move them as 16- or 32-byte vectors so that a warp request
     // touches each 128-byte line once per 32 B instead of once per 8 B.
@@ -376,7 +374,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
     if (lowRun == 4) {
 #pragma unroll
         for (int e = 0; e < E; e += 4) {
-            const Vec<qreal, 4> a = load<4>(re + base + off[e]), b = load<4>(im + base + off[e]);
+            const Vec<qreal, 4> a = load<4>(reAt(e)), b = load<4>(imAt(e));
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 xr[e + j] = a.v[j];
@@ -386,15 +384,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
     } else if (lowRun == 2) {
 #pragma unroll
         for (int e = 0; e < E; e += 2) {
-            const Vec<qreal, 2> a = load<2>(re + base + off[e]), b = load<2>(im + base + off[e]);
+            const Vec<qreal, 2> a = load<2>(reAt(e)), b = load<2>(imAt(e));
             xr[e] = a.v[0]; xr[e + 1] = a.v[1];
             xi[e] = b.v[0]; xi[e + 1] = b.v[1];
         }
     } else {
 #pragma unroll
         for (int e = 0; e < E; ++e) {
-            xr[e] = load<1>(re + base + off[e]).v[0];
-            xi[e] = load<1>(im + base + off[e]).v[0];
+            xr[e] = load<1>(reAt(e)).v[0];
+            xi[e] = load<1>(imAt(e)).v[0];
         }
     }
     {
@@ -425,8 +423,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
                 a.v[j] = xr[e + j];
                 b.v[j] = xi[e + j];
             }
-            store<4>(re + base + off[e], a);
-            store<4>(im + base + off[e], b);
+            store<4>(reAt(e), a);
+            store<4>(imAt(e), b);
         }
     } else if (lowRun == 2) {
 #pragma unroll
@@ -434,8 +432,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
             Vec<qreal, 2> a, b;
             a.v[0] = xr[e]; a.v[1] = xr[e + 1];
             b.v[0] = xi[e]; b.v[1] = xi[e + 1];
-            store<2>(re + base + off[e], a);
-            store<2>(im + base + off[e], b);
+            store<2>(reAt(e), a);
+            store<2>(imAt(e), b);
         }
     } else {
 #pragma unroll
@@ -443,8 +441,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
             Vec<qreal, 1> a, b;
             a.v[0] = xr[e];
             b.v[0] = xi[e];
-            store<1>(re + base + off[e], a);
-            store<1>(im + base + off[e], b);
+            store<1>(reAt(e), a);
+            store<1>(imAt(e), b);
         }
     }
 }
