@@ -310,15 +310,15 @@ void runOpNow(const Qureg& q, const PendingOp& op) {
 #endif
 FusedLaunch fl;  // ~8.5 KB: passed by value as the kernel parameter block
 
-// Fill the parameter block for one group of recorded gates; returns whether it holds noise channels.
-bool prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
-    bool noisy = false;
+// Fill the parameter block for one group of recorded gates; returns the kernel tier the group needs.
+int prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
+    int tier = 0;
     for (int i = 0; i < grp.count; ++i) {
         const FusedGate fg = describe(ops[grp.first + i], grp.bits);
         fl.ctl[i] = GateCtl{opcodeOf(fg), fg.regMask};
         fl.outerMask[i] = fg.outerMask;
         std::memcpy(fl.c[i], fg.c, sizeof fg.c);
-        noisy = noisy || isNoise(ops[grp.first + i].kind);
+        tier = std::max(tier, tierOf(fl.ctl[i].opcode));
     }
     fl.ctl[grp.count] = GateCtl{0, 0};
     for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = grp.bits[j];
@@ -329,11 +329,11 @@ bool prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
         fl.offBytes[e] = o * sizeof(qreal);
     }
     fl.nGates = grp.count;
-    return noisy;
+    return tier;
 }
 
 // One launch of k_fused over the whole shard (sp == nullptr) or over slab `slab` of it.
-void launchPrepared(QuregRec* r, bool noisy, const SlabPlan* sp, int slab) {
+void launchPrepared(QuregRec* r, int tier, const SlabPlan* sp, int slab) {
     int n = 0;
     for (int j = 0; j < kFuseBits; ++j) fl.ins[n++] = fl.pos[j];
     if (sp)
@@ -343,13 +343,17 @@ void launchPrepared(QuregRec* r, bool noisy, const SlabPlan* sp, int slab) {
     fl.slabMask = sp ? sp->valueMask(slab) : 0;
     fl.nThreads = (u64)r->n >> n;
     // 128-thread CTAs, 4 per SM (128 registers per thread): measured best of 64/128/256 threads x 2-6 CTAs
-    const unsigned int nb128 = (unsigned int)((fl.nThreads + 127) / 128);
-    if (noisy)
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+    const unsigned int nb = (unsigned int)((fl.nThreads + 127) / 128);
+    if (tier == kTierNoise)
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierNoise><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+    else if (tier == kTierAll && g.contract)
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAll, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+    else if (tier == kTierAll)
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAll><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
     else if (g.contract)
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, false, true><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierCore, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
     else
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, false><<<nb128, 128, 0, g.stream>>>(r->re, r->im, fl);
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierCore><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
     launched();
 }
 
@@ -373,10 +377,10 @@ void runGroup(const Qureg& q, const std::vector<PendingOp>& ops, const FusedGrou
         runOpNow(q, ops[grp.first]);
         return;
     }
-    const bool noisy = prepareGroup(ops, grp);
+    const int tier = prepareGroup(ops, grp);
     FusedTimer t;
     t.start();
-    launchPrepared(rec(q), noisy, nullptr, 0);
+    launchPrepared(rec(q), tier, nullptr, 0);
     t.stop();
     ++g.fusedLaunches;
     g.fusedGates += grp.count;
@@ -405,7 +409,7 @@ inline u64 bitsOf(const FusedGroup& grp) {
 // slab) and `record[s]` marks its end (the exchange after it may take that slab).
 void runGroupInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const FusedGroup& grp, const SlabPlan& sp,
                      const cudaEvent_t* waitFor, const cudaEvent_t* record) {
-    const bool noisy = prepareGroup(ops, grp);
+    const int tier = prepareGroup(ops, grp);
     FusedTimer t;
     bool started = false;
     for (int s = 0; s < (1 << sp.nBits); ++s) {
@@ -414,7 +418,7 @@ void runGroupInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const Fu
             t.start();
             started = true;
         }
-        launchPrepared(rec(q), noisy, &sp, s);
+        launchPrepared(rec(q), tier, &sp, s);
         if (record) CUDA_OK(cudaEventRecord(record[s], g.stream));
     }
     t.stop();

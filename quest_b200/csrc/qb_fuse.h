@@ -170,6 +170,13 @@ inline int opcodeOf(const FusedGate& g) {
     }
 }
 
+// Smallest kernel tier (qb_kernels.cuh: FusedTier) that understands this opcode.
+inline int tierOf(int opcode) {
+    if (opcode >= kOpNoise) return 2;
+    if ((opcode >= kOpMatrixCtl && opcode < kOpHadamard) || (opcode >= kOpPauliY && opcode < kOpPhase) || opcode >= kOpFlip) return 1;
+    return 0;
+}
+
 // What the kernel reads per gate: 8 bytes of control, the outer-bit condition and 8 coefficients, in separate arrays:
 // the conditions of 32 gates are folded into one bit mask before the gate loop, and the control word of the NEXT
 // gate is fetched while the current one computes.

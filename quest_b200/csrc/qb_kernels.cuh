@@ -308,21 +308,27 @@ __device__ __forceinline__ void noiseQuads(qreal (&xr)[1 << R], qreal (&xi)[1 <<
 
 // One recorded gate on the 2^R amplitudes a thread holds in registers: a single jump on the host-made opcode
 // (qb_fuse.h) into straight-line code for that (kind, register position) combination.
-template <int R, bool NOISE, bool FMA>
+// TIER selects how many gate families the instantiation understands: every code path through the register block costs
+// the others (measured: +16 small bodies = +27 % time, -24 bodies = -3 %), so the common families get a kernel of their own.
+enum FusedTier : int { kTierCore = 0,    // matrix (uncontrolled among the fused qubits), hadamard, swap, phase
+                       kTierAll = 1,     // + controlled matrix, pauliY, phase flip
+                       kTierNoise = 2 }; // + density-matrix noise channels and collapse
+
+template <int R, int TIER, bool FMA>
 __device__ __forceinline__ void applyGate(int opcode, unsigned int regMask, const qreal (&c)[8], qreal (&xr)[1 << R],
                                           qreal (&xi)[1 << R]) {
     using Matrix = typename std::conditional<FMA, OpMatrixFma, OpMatrix>::type;
     using DiagPhase = typename std::conditional<FMA, DiagPhaseFma, qb::DiagPhase>::type;
     switch (opcode) {
         QB_CASE4(kOpMatrix, QB_ON_POS(forEveryPair<P, R>(xr, xi, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
-        QB_CASE4(kOpMatrixCtl, QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
+        QB_CASE4(kOpMatrixCtl, if constexpr (TIER >= kTierAll) QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
         QB_CASE4(kOpHadamard, QB_ON_POS(forEveryPair<P, R>(xr, xi, OpHadamard{c[0]})))  // the API has no controlled hadamard
         QB_CASE4(kOpSwap, QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpSwap{})))
-        QB_CASE4(kOpPauliY, QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpPauliY{c[0]})))
+        QB_CASE4(kOpPauliY, if constexpr (TIER >= kTierAll) QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpPauliY{c[0]})))
         QB_CASE16(kOpPhase, QB_ON_MASK(forSelected<M, R>(xr, xi, DiagPhase{c[0], c[1]})))
-        QB_CASE16(kOpFlip, QB_ON_MASK(forSelected<M, R>(xr, xi, DiagFlip{})))
+        QB_CASE16(kOpFlip, if constexpr (TIER >= kTierAll) QB_ON_MASK(forSelected<M, R>(xr, xi, DiagFlip{})))
         default:
-            if constexpr (NOISE) {
+            if constexpr (TIER >= kTierNoise) {
                 switch (opcode) {
                     QB_CASE_NOISE(kFDephase)
                     QB_CASE_NOISE(kFDepolarise)
@@ -341,9 +347,7 @@ __device__ __forceinline__ void applyGate(int opcode, unsigned int regMask, cons
 #undef QB_CASE16
 #undef QB_CASE_NOISE
 
-// NOISE selects the instantiation that also understands the density-matrix noise kinds; state-vector groups use the
-// leaner one.
-template <int R, int BLOCK, int MINB, bool NOISE, bool FMA = false>
+template <int R, int BLOCK, int MINB, int TIER, bool FMA = false>
 __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, qreal* __restrict__ im,
                                                 const __grid_constant__ FusedLaunch fl) {
     static_assert(R == kFuseBits && (R == 3 || R == 4), "k_fused is written for 3 or 4 fused qubits");
@@ -410,7 +414,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
                 qreal c[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) c[i] = fl.c[g][i];
-                applyGate<R, NOISE, FMA>(fl.ctl[g].opcode, fl.ctl[g].regMask, c, xr, xi);
+                applyGate<R, TIER, FMA>(fl.ctl[g].opcode, fl.ctl[g].regMask, c, xr, xi);
             }
         }
     }
