@@ -1562,7 +1562,8 @@ int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* target
         for (int i = 0; i < grp.count; ++i) {
             const FusedGate fg = describe(ops[grp.first + i], grp.bits);
             unsigned long long* d = descOut + 4 * (grp.first + i);
-            d[0] = (unsigned long long)fg.kind | ((unsigned long long)opcodeOf(fg) << 8);  // what the kernel jumps on
+            // kind | what the kernel jumps on | the smallest kernel tier that understands it
+            d[0] = (unsigned long long)fg.kind | ((unsigned long long)opcodeOf(fg) << 8) | ((unsigned long long)tierOf(opcodeOf(fg)) << 16);
             d[1] = fg.pos; d[2] = fg.regMask; d[3] = fg.outerMask;
         }
     }

@@ -33,7 +33,7 @@ def fuse(lib, local_bits, ops):
     ng = lib.qb200_debugFuse(local_bits, n, kinds, targets, masks, groups, desc)
     gl = [dict(first=groups[7 * i], count=groups[7 * i + 1], bits=list(groups[7 * i + 2:7 * i + 6]), ndense=groups[7 * i + 6])
           for i in range(ng)]
-    dl = [dict(kind=desc[4 * i] & 0xFF, opcode=desc[4 * i] >> 8, pos=desc[4 * i + 1], reg=desc[4 * i + 2],
+    dl = [dict(kind=desc[4 * i] & 0xFF, opcode=(desc[4 * i] >> 8) & 0xFF, tier=desc[4 * i] >> 16, pos=desc[4 * i + 1], reg=desc[4 * i + 2],
                outer=desc[4 * i + 3]) for i in range(n)]
     return gl, dl
 
@@ -90,6 +90,8 @@ def apply_fused_group(state, local_bits, grp, descs, mats):
         active = (outer & d["outer"]) == d["outer"]
         kind, p, mask = decode_opcode(d["opcode"])  # the kernel sees only the opcode and the run-time register mask
         assert kind == d["kind"]
+        # core tier: matrix without a control among the fused qubits, hadamard, swap, phase; everything else needs tier 1
+        assert d["tier"] == (0 if kind in (K_HAD, K_SWAP, K_PHASE) or (kind == K_MATRIX and d["reg"] == 0) else 1)
         if mask is None:
             mask = d["reg"]
         assert mask == d["reg"] and (p is None or p == d["pos"])
