@@ -318,7 +318,7 @@ int prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
         fl.ctl[i] = GateCtl{opcodeOf(fg), fg.regMask};
         fl.outerMask[i] = fg.outerMask;
         std::memcpy(fl.c[i], fg.c, sizeof fg.c);
-        tier = std::max(tier, tierOf(fl.ctl[i].opcode));
+        tier |= tierOf(fl.ctl[i].opcode);
     }
     fl.ctl[grp.count] = GateCtl{0, 0};
     for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = grp.bits[j];
@@ -344,7 +344,9 @@ void launchPrepared(QuregRec* r, int tier, const SlabPlan* sp, int slab) {
     fl.nThreads = (u64)r->n >> n;
     // 128-thread CTAs, 4 per SM (128 registers per thread): measured best of 64/128/256 threads x 2-6 CTAs
     const unsigned int nb = (unsigned int)((fl.nThreads + 127) / 128);
-    if (tier == kTierNoise)
+    if (tier == kTierAllNoise)
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAllNoise><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+    else if (tier == kTierNoise)
         k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierNoise><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
     else if (tier == kTierAll && g.contract)
         k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAll, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);

@@ -170,7 +170,8 @@ inline int opcodeOf(const FusedGate& g) {
     }
 }
 
-// Smallest kernel tier (qb_kernels.cuh: FusedTier) that understands this opcode.
+// Kernel tier bits (qb_kernels.cuh: FusedTier) this opcode needs: bit 0 = the less common state-vector gates,
+// bit 1 = density-matrix noise.  A group runs on the OR over its gates.
 inline int tierOf(int opcode) {
     if (opcode >= kOpNoise) return 2;
     if ((opcode >= kOpMatrixCtl && opcode < kOpHadamard) || (opcode >= kOpPauliY && opcode < kOpPhase) || opcode >= kOpFlip) return 1;

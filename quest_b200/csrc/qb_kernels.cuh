@@ -310,9 +310,10 @@ __device__ __forceinline__ void noiseQuads(qreal (&xr)[1 << R], qreal (&xi)[1 <<
 // (qb_fuse.h) into straight-line code for that (kind, register position) combination.
 // TIER selects how many gate families the instantiation understands: every code path through the register block costs
 // the others (measured: +16 small bodies = +27 % time, -24 bodies = -3 %), so the common families get a kernel of their own.
-enum FusedTier : int { kTierCore = 0,    // matrix (uncontrolled among the fused qubits), hadamard, swap, phase
-                       kTierAll = 1,     // + controlled matrix, pauliY, phase flip
-                       kTierNoise = 2 }; // + density-matrix noise channels and collapse
+enum FusedTier : int { kTierCore = 0,       // matrix (uncontrolled among the fused qubits), hadamard, swap, phase
+                       kTierAll = 1,        // + controlled matrix, pauliY, phase flip
+                       kTierNoise = 2,      // core + density-matrix noise channels and collapse
+                       kTierAllNoise = 3 }; // everything            (bit 0: all gates, bit 1: noise)
 
 template <int R, int TIER, bool FMA>
 __device__ __forceinline__ void applyGate(int opcode, unsigned int regMask, const qreal (&c)[8], qreal (&xr)[1 << R],
@@ -321,14 +322,14 @@ __device__ __forceinline__ void applyGate(int opcode, unsigned int regMask, cons
     using DiagPhase = typename std::conditional<FMA, DiagPhaseFma, qb::DiagPhase>::type;
     switch (opcode) {
         QB_CASE4(kOpMatrix, QB_ON_POS(forEveryPair<P, R>(xr, xi, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
-        QB_CASE4(kOpMatrixCtl, if constexpr (TIER >= kTierAll) QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
+        QB_CASE4(kOpMatrixCtl, if constexpr ((TIER & kTierAll) != 0) QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
         QB_CASE4(kOpHadamard, QB_ON_POS(forEveryPair<P, R>(xr, xi, OpHadamard{c[0]})))  // the API has no controlled hadamard
         QB_CASE4(kOpSwap, QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpSwap{})))
-        QB_CASE4(kOpPauliY, if constexpr (TIER >= kTierAll) QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpPauliY{c[0]})))
+        QB_CASE4(kOpPauliY, if constexpr ((TIER & kTierAll) != 0) QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpPauliY{c[0]})))
         QB_CASE16(kOpPhase, QB_ON_MASK(forSelected<M, R>(xr, xi, DiagPhase{c[0], c[1]})))
-        QB_CASE16(kOpFlip, if constexpr (TIER >= kTierAll) QB_ON_MASK(forSelected<M, R>(xr, xi, DiagFlip{})))
+        QB_CASE16(kOpFlip, if constexpr ((TIER & kTierAll) != 0) QB_ON_MASK(forSelected<M, R>(xr, xi, DiagFlip{})))
         default:
-            if constexpr (TIER >= kTierNoise) {
+            if constexpr ((TIER & kTierNoise) != 0) {
                 switch (opcode) {
                     QB_CASE_NOISE(kFDephase)
                     QB_CASE_NOISE(kFDepolarise)
