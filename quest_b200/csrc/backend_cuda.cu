@@ -75,6 +75,7 @@ struct Engine {
     bool contract = false;          // QUEST_B200_FMA / qb200_setArithmetic: fused pass may contract a*b+c into fma
     bool remap = true;              // QUEST_B200_REMAP: make shard-selecting qubits local by slot exchange
     unsigned long long slotSwaps = 0;
+    bool distributed = false;       // QUEST_B200_DISTRIBUTED: gates on shard-selecting qubits run as distributed fused passes
     bool overlap = true;            // QUEST_B200_OVERLAP: pipeline a slot exchange with the fused pass before it
     int swapCtasPerSm = 1;          // QUEST_B200_SWAP_CTAS: footprint of a pipelined exchange
     int overlapMinBits = 24;        // ... for shards of at least 2^24 amplitudes (QUEST_B200_OVERLAP_MIN_BITS: tests)
@@ -84,7 +85,7 @@ struct Engine {
     cudaEvent_t commDone = nullptr; // communication stream: the whole exchange is
     void* pendingReg = nullptr;     // register whose last exchange the engine stream has not waited for yet ...
     SlabPlan pendingPlan{0, {0, 0, 0}};  // ... and how it was cut
-    unsigned long long overlapped = 0;
+    unsigned long long overlapped = 0, distributedPasses = 0;
     bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fusedEvents;
 } g;
@@ -310,26 +311,31 @@ void runOpNow(const Qureg& q, const PendingOp& op) {
 #endif
 FusedLaunch fl;  // ~8.5 KB: passed by value as the kernel parameter block
 
-// Fill the parameter block for one group of recorded gates; returns the kernel tier the group needs.
-int prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
+// Fill the parameter block for a run of recorded gates on the fused qubits `bits`; returns the kernel tier it needs.
+// Only bits below `localBits` contribute to element offsets: higher fused qubits select the shard (distributed pass).
+int prepareOps(const PendingOp* list, int count, const int* bits, int localBits) {
     int tier = 0;
-    for (int i = 0; i < grp.count; ++i) {
-        const FusedGate fg = describe(ops[grp.first + i], grp.bits);
+    for (int i = 0; i < count; ++i) {
+        const FusedGate fg = describe(list[i], bits);
         fl.ctl[i] = GateCtl{opcodeOf(fg), fg.regMask};
         fl.outerMask[i] = fg.outerMask;
         std::memcpy(fl.c[i], fg.c, sizeof fg.c);
         tier |= tierOf(fl.ctl[i].opcode);
     }
-    fl.ctl[grp.count] = GateCtl{0, 0};
-    for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = grp.bits[j];
+    fl.ctl[count] = GateCtl{0, 0};
+    for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = bits[j];
     for (int e = 0; e < (1 << kFuseBits); ++e) {
         u64 o = 0;
         for (int j = 0; j < kFuseBits; ++j)
-            if ((e >> j) & 1) o += 1ull << grp.bits[j];
+            if (((e >> j) & 1) && bits[j] < localBits) o += 1ull << bits[j];
         fl.offBytes[e] = o * sizeof(qreal);
     }
-    fl.nGates = grp.count;
+    fl.nGates = count;
     return tier;
+}
+
+int prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
+    return prepareOps(ops.data() + grp.first, grp.count, grp.bits, 64);
 }
 
 // One launch of k_fused over the whole shard (sp == nullptr) or over slab `slab` of it.
@@ -428,9 +434,109 @@ void runGroupInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const Fu
     g.fusedGates += grp.count;
 }
 
+// ---- distributed mode (QUEST_B200_DISTRIBUTED=1, opt-in) ----------------------------------------------------------
+// Gates are recorded with their full control masks and with targets on shard-selecting qubits left where they are, so
+// every rank holds the same queue and forms the same groups.  A group whose fused qubits are all local runs as usual
+// (controls on shard-selecting qubits resolved against this rank now).  A group with g fused shard-selecting qubits
+// runs as ONE pass over the 2^g GPUs that differ in those qubits: element e of the register block lives in shard
+// tab[e >> nLocalFused], each GPU of the group processes the slab of outer indices that carries its own group index,
+// controls on the fused shard-selecting qubits are ordinary register-mask bits.  NVLink carries (1 - 2^-g) of a shard
+// each way for the whole group instead of half a shard per exchanged qubit (and per exchange back).
+void flushDistributed(const Qureg& q) {
+    QuregRec* r = rec(q);
+    r->callsSinceFlush = 0;
+    r->denseSinceFlush = 0;
+    if (r->queue.empty()) return;
+    std::vector<PendingOp> ops;
+    ops.swap(r->queue);
+    const u64 localMask = (1ull << r->localBits) - 1ull;
+    const u64 rankBits = (u64)q.chunkId << r->localBits;  // this rank's values of the shard-selecting bits
+    for (const FusedGroup& grp : groupOps(ops, r->localBits)) {
+        u64 fusedShardBits = 0;
+        int nLocalFused = 0;
+        for (int j = 0; j < kFuseBits; ++j) {
+            if (grp.bits[j] >= r->localBits) fusedShardBits |= 1ull << grp.bits[j];
+            else ++nLocalFused;
+        }
+        // controls on shard-selecting qubits outside the block: the same for every GPU of the group
+        std::vector<PendingOp> sel;
+        for (int i = 0; i < grp.count; ++i) {
+            PendingOp op = ops[grp.first + i];
+            const u64 outside = op.mask & ~localMask & ~fusedShardBits;
+            if ((rankBits & outside) != outside) continue;
+            op.mask &= ~outside;
+            sel.push_back(op);
+        }
+        if (sel.empty()) continue;
+        if (!fusedShardBits) {
+            if (sel.size() == 1) {
+                runOpNow(q, sel[0]);
+                continue;
+            }
+            const int tier = prepareOps(sel.data(), (int)sel.size(), grp.bits, 64);
+            FusedTimer t;
+            t.start();
+            launchPrepared(r, tier, nullptr, 0);
+            t.stop();
+            ++g.fusedLaunches;
+            g.fusedGates += sel.size();
+            continue;
+        }
+        // the group of GPUs, this rank's index in it, and the slab it processes
+        const int nShard = kFuseBits - nLocalFused;
+        u64 fusedLocal = 0;
+        for (int j = 0; j < nLocalFused; ++j) fusedLocal |= 1ull << grp.bits[j];
+        const SlabPlan sp = planSlabs(r->localBits, fusedLocal, nShard, 0);
+        if (sp.nBits != nShard) comm::unsupported("a distributed pass on a shard too small to be divided among its GPUs");
+        int me = 0;
+        std::vector<int> members(1 << nShard);
+        for (int v = 0; v < (1 << nShard); ++v) {
+            int rank = q.chunkId;
+            for (int j = 0; j < nShard; ++j) {
+                const int bit = grp.bits[nLocalFused + j] - r->localBits;
+                rank = (rank & ~(1 << bit)) | (((v >> j) & 1) << bit);
+            }
+            members[v] = rank;
+            if (rank == q.chunkId) me = v;
+        }
+        prepareOps(sel.data(), (int)sel.size(), grp.bits, r->localBits);
+        fl.nLocalFused = nLocalFused;
+        for (int v = 0; v < (1 << nShard); ++v) {
+            const comm::Partner p = comm::shardOf(q, members[v]);
+            fl.tabRe[v] = p.re;
+            fl.tabIm[v] = p.im;
+        }
+        int n = 0;
+        for (int j = 0; j < nLocalFused; ++j) fl.ins[n++] = grp.bits[j];
+        for (int j = 0; j < sp.nBits; ++j) fl.ins[n++] = sp.bits[j];
+        std::sort(fl.ins, fl.ins + n);
+        fl.nIns = n;
+        fl.slabMask = sp.valueMask(me);
+        fl.nThreads = (u64)r->n >> n;
+        const unsigned int nb = (unsigned int)((fl.nThreads + 127) / 128);
+        for (int v = 0; v < (1 << nShard); ++v)  // everything the others enqueued before this pass has finished
+            if (members[v] != q.chunkId) comm::pairBarrier(members[v], g.stream);
+        FusedTimer t;
+        t.start();
+        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAllNoise, false, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+        launched();
+        t.stop();
+        for (int v = 0; v < (1 << nShard); ++v)  // the others' writes into this shard have landed
+            if (members[v] != q.chunkId) comm::pairBarrier(members[v], g.stream);
+        ++g.fusedLaunches;
+        ++g.distributedPasses;
+        g.fusedGates += sel.size();
+    }
+}
+
 // Execute everything recorded for this register: single gates through their own kernel, runs of gates through
 // k_fused (one HBM pass per group, qb_fuse.h).
 void flush(const Qureg& q) {
+    if (g.distributed && g.world > 1) {
+        if (g.pendingReg == rec(q)) settle();
+        flushDistributed(q);
+        return;
+    }
     QuregRec* r = rec(q);
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
@@ -606,6 +712,19 @@ inline QuregRec* fresh(const Qureg& q) {
 void submit(const Qureg& q, PendingOp op) {
     QuregRec* r = rec(q);
     dirty(r);
+    if (g.distributed && g.world > 1 && g.fuse && r->localBits >= kFuseBits + 3) {
+        // distributed mode: record the gate as it is (bit positions through the qubit map, which is the identity unless
+        // a two-qubit channel moved something); nothing is decided per rank before the groups are formed
+        if (!isDiagonal(op.kind)) {
+            op.target = r->map.phys[op.target];
+            if (op.target2 >= 0) op.target2 = r->map.phys[op.target2];
+        }
+        op.mask = r->map.physMask(op.mask);
+        if (r->callsSinceFlush >= kQueueCap) flush(q);
+        ++r->callsSinceFlush;
+        r->queue.push_back(op);
+        return;
+    }
     // logical qubits -> current bit positions; a dense target living in a shard-selecting slot is first made local
     if (g.world > 1) {
         if (!isDiagonal(op.kind)) {
@@ -867,6 +986,7 @@ QuESTEnv createQuESTEnv(void) {
     if (g.world > 1) {
         comm::init(ln, g.device, g.stream);
         if (const char* s = std::getenv("QUEST_B200_OVERLAP")) g.overlap = std::atoi(s) != 0;
+        if (const char* s = std::getenv("QUEST_B200_DISTRIBUTED")) g.distributed = std::atoi(s) != 0;
         if (const char* s = std::getenv("QUEST_B200_SWAP_CTAS")) g.swapCtasPerSm = std::max(1, std::min(8, std::atoi(s)));
         if (const char* s = std::getenv("QUEST_B200_OVERLAP_MIN_BITS")) g.overlapMinBits = std::max(8, std::atoi(s));
         int lowPrio = 0, highPrio = 0;
@@ -1030,6 +1150,15 @@ void qb200_setOverlap(int enabled) {
     g.overlap = enabled != 0;
 }
 unsigned long long qb200_getOverlappedExchangeCount(void) { return g.overlapped; }
+
+// Pending gates are executed under the old setting first (and the identity layout is restored: the two modes record
+// differently).
+void qb200_setDistributed(int enabled) {
+    requireEngine();
+    qb200_setRemap(g.remap ? 1 : 0);
+    g.distributed = enabled != 0;
+}
+unsigned long long qb200_getDistributedPassCount(void) { return g.distributedPasses; }
 
 unsigned long long qb200_getPipelinedTransferCount(void) { return io::pipelinedTransfers(); }
 

@@ -388,6 +388,16 @@ Partner partnerOf(const Qureg& q, int gbit) {
     return p;
 }
 
+Partner shardOf(const Qureg& q, int rank) {
+    auto it = peers.find(q.pairStateVec.real);
+    if (it == peers.end()) die("distributed pass on a register without peer mappings");
+    Partner p;
+    p.rank = rank;
+    p.re = it->second.re[rank];
+    p.im = it->second.im[rank];
+    return p;
+}
+
 // Stream-ordered handshake with one partner: work enqueued on `stream` after this call starts only after the partner's
 // stream has reached its matching call (same partner pair, same channel), i.e. after everything the partner enqueued
 // before it has completed and is visible here.

@@ -37,6 +37,7 @@ struct Partner {
     int rank;
 };
 Partner partnerOf(const Qureg& q, int gbit);
+Partner shardOf(const Qureg& q, int rank);  // any rank's shard as mapped into this process (own rank: own pointers)
 void pairBarrier(int partnerRank, cudaStream_t stream, int channel = 0);  // channel: 0 engine stream, 1 communication stream
 
 }  // namespace comm

@@ -222,6 +222,11 @@ struct FusedLaunch {
     int ins[kFuseBits + kMaxSlabBits];   // ... ascending
     unsigned long long slabMask;         // value of the slab bits for this launch (0 for a whole-shard pass)
     unsigned long long offBytes[1 << kFuseBits];  // byte offset of register element e from the thread's base amplitude
+    // distributed pass only (DIST): the highest fused qubits select the GPU.  Element e lives in shard
+    // tab[e >> nLocalFused] (peer mappings of the GPUs that differ in those qubits, own shard included).
+    int nLocalFused;
+    qreal* tabRe[1 << kMaxSlabBits];
+    qreal* tabIm[1 << kMaxSlabBits];
     unsigned long long nThreads;
     GateCtl ctl[kMaxFusedGates + 2];     // padded
     unsigned long long outerMask[kMaxFusedGates];  // control/selecting bits outside the fused qubits
@@ -348,7 +353,7 @@ __device__ __forceinline__ void applyGate(int opcode, unsigned int regMask, cons
 #undef QB_CASE16
 #undef QB_CASE_NOISE
 
-template <int R, int BLOCK, int MINB, int TIER, bool FMA = false>
+template <int R, int BLOCK, int MINB, int TIER, bool FMA = false, bool DIST = false>
 __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, qreal* __restrict__ im,
                                                 const __grid_constant__ FusedLaunch fl) {
     static_assert(R == kFuseBits && (R == 3 || R == 4), "k_fused is written for 3 or 4 fused qubits");
@@ -369,8 +374,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, q
     // host (FusedLaunch::offBytes), added here straight from the constant bank
     char* const reBase = reinterpret_cast<char*>(re + base);
     char* const imBase = reinterpret_cast<char*>(im + base);
-    auto reAt = [&](int e) { return reinterpret_cast<qreal*>(reBase + fl.offBytes[e]); };
-    auto imAt = [&](int e) { return reinterpret_cast<qreal*>(imBase + fl.offBytes[e]); };
+    auto reAt = [&](int e) {
+        if constexpr (DIST) return reinterpret_cast<qreal*>(reinterpret_cast<char*>(fl.tabRe[e >> fl.nLocalFused] + base) + fl.offBytes[e]);
+        else return reinterpret_cast<qreal*>(reBase + fl.offBytes[e]);
+    };
+    auto imAt = [&](int e) {
+        if constexpr (DIST) return reinterpret_cast<qreal*>(reinterpret_cast<char*>(fl.tabIm[e >> fl.nLocalFused] + base) + fl.offBytes[e]);
+        else return reinterpret_cast<qreal*>(imBase + fl.offBytes[e]);
+    };
     // Register index bit j <-> fused qubit pos[j].  When the lowest fused qubits are qubit 0 (and 1), neighbouring
     // register elements are neighbours in memory: move them as 16- or 32-byte vectors so that a warp request
     // touches each 128-byte line once per 32 B instead of once per 8 B.
