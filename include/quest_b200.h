@@ -107,6 +107,10 @@ void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long l
 int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, const unsigned long long* masks,
                      int* eventsOut, int* physOut, int* canonOut);
 
+/* Test hook (host logic only, makes no CUDA call): the plan of a distributed fused pass for rank chunkId.  Layout at the
+ * definition. */
+int qb200_debugDistributed(int localBits, int chunkId, const int* bits, int* out);
+
 /* Test hook (host logic only, makes no CUDA call): the slab bits chosen for pipelining a fused pass with a slot
  * exchange, and every k_swapPeer launch plan of that exchange.  Layouts at the definition. */
 int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int lowestAllowed, int vec, int localSlot,

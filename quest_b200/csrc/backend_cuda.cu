@@ -483,22 +483,12 @@ void flushDistributed(const Qureg& q) {
             continue;
         }
         // the group of GPUs, this rank's index in it, and the slab it processes
-        const int nShard = kFuseBits - nLocalFused;
-        u64 fusedLocal = 0;
-        for (int j = 0; j < nLocalFused; ++j) fusedLocal |= 1ull << grp.bits[j];
-        const SlabPlan sp = planSlabs(r->localBits, fusedLocal, nShard, 0);
-        if (sp.nBits != nShard) comm::unsupported("a distributed pass on a shard too small to be divided among its GPUs");
-        int me = 0;
-        std::vector<int> members(1 << nShard);
-        for (int v = 0; v < (1 << nShard); ++v) {
-            int rank = q.chunkId;
-            for (int j = 0; j < nShard; ++j) {
-                const int bit = grp.bits[nLocalFused + j] - r->localBits;
-                rank = (rank & ~(1 << bit)) | (((v >> j) & 1) << bit);
-            }
-            members[v] = rank;
-            if (rank == q.chunkId) me = v;
-        }
+        DistPlan dp;
+        if (!planDistributed(r->localBits, q.chunkId, grp.bits, kFuseBits, dp))
+            comm::unsupported("a distributed pass on a shard too small to be divided among its GPUs");
+        const int nShard = dp.nShard, me = dp.me;
+        const SlabPlan& sp = dp.slabs;
+        const int* members = dp.members;
         prepareOps(sel.data(), (int)sel.size(), grp.bits, r->localBits);
         fl.nLocalFused = nLocalFused;
         for (int v = 0; v < (1 << nShard); ++v) {
@@ -1669,6 +1659,17 @@ int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int l
             o += 11;
         }
     return sp.nBits;
+}
+
+// Host logic of the distributed fused pass (qb::planDistributed), exposed for CPU-only tests (no CUDA call).
+// out: nLocalFused, nShard, me, nSlabBits, slabBits[3], members[8]; returns 0 if the group cannot be planned.
+int qb200_debugDistributed(int localBits, int chunkId, const int* bits, int* out) {
+    DistPlan dp;
+    if (!planDistributed(localBits, chunkId, bits, kFuseBits, dp)) return 0;
+    out[0] = dp.nLocalFused; out[1] = dp.nShard; out[2] = dp.me; out[3] = dp.slabs.nBits;
+    for (int j = 0; j < 3; ++j) out[4 + j] = j < dp.slabs.nBits ? dp.slabs.bits[j] : -1;
+    for (int v = 0; v < 8; ++v) out[7 + v] = v < (1 << dp.nShard) ? dp.members[v] : -1;
+    return 1;
 }
 
 // Host grouping logic of the fusion queue, exposed for CPU-only tests (no CUDA call): groups the given gate list

@@ -326,3 +326,61 @@ def test_slab_exchanges_cover_the_exchange_exactly_once(local_bits, vec, local_s
                         seen[j] += 1
         want_seen = np.array([0 if (j >> local_slot) & 1 else 1 for j in range(1 << local_bits)], dtype=np.int32)
         assert np.array_equal(seen, want_seen)
+
+
+# ---- distributed fused pass (qb::planDistributed) ---------------------------------------------------------------
+
+def _dist_plan(lib, local_bits, chunk, bits):
+    out = (ctypes.c_int * 15)()
+    ok = lib.qb200_debugDistributed(local_bits, chunk, (ctypes.c_int * 4)(*bits), out)
+    assert ok == 1
+    n_local, n_shard, me, n_slab = out[0], out[1], out[2], out[3]
+    return dict(n_local=n_local, n_shard=n_shard, me=me, slab_bits=list(out[4:4 + n_slab]), members=list(out[7:7 + (1 << n_shard)]))
+
+
+@pytest.mark.parametrize("world,local_bits,bits", [(2, 8, [1, 4, 7, 8]), (4, 7, [0, 3, 7, 8]), (4, 8, [2, 5, 6, 9]),
+                                                   (8, 7, [3, 7, 8, 9]), (8, 9, [0, 1, 4, 11]), (8, 8, [5, 8, 9, 10])])
+def test_distributed_pass_plan_partitions_the_work_and_applies_the_gate(world, local_bits, bits):
+    """Every rank plans the same group; the members' slabs partition the outer indices of every shard of the group; a
+    gate on a shard-selecting fused qubit executed block by block - element e in shard members[e >> nLocalFused] -
+    equals the same gate on the unsharded state."""
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    lib.qb200_debugDistributed.restype = ctypes.c_int
+    nq = local_bits + world.bit_length() - 1
+    rng = np.random.default_rng(sum(bits) + world)
+    full = rng.standard_normal(1 << nq) + 1j * rng.standard_normal(1 << nq)
+    shards = [full[r << local_bits:(r + 1) << local_bits].copy() for r in range(world)]
+    plans = [_dist_plan(lib, local_bits, r, bits) for r in range(world)]
+    u = rand_u(np.random.default_rng(5))
+    target_pos = 3  # the highest fused qubit: always shard-selecting in these cases
+    touched = [np.zeros(1 << local_bits, dtype=np.int32) for _ in range(world)]
+    for r, p in enumerate(plans):
+        assert p["n_local"] + p["n_shard"] == 4 and p["members"][p["me"]] == r
+        for m in p["members"]:  # every member plans the same group and the same slab bits
+            assert plans[m]["members"] == p["members"] and plans[m]["slab_bits"] == p["slab_bits"]
+        assert len({plans[m]["me"] for m in p["members"]}) == len(p["members"])
+        fused_local = bits[:p["n_local"]]
+        assert all(b < local_bits and b not in fused_local for b in p["slab_bits"]) and len(p["slab_bits"]) == p["n_shard"]
+        held_out = sorted(fused_local + p["slab_bits"])
+        slab_val = sum(((p["me"] >> j) & 1) << p["slab_bits"][j] for j in range(p["n_shard"]))
+        for k in range((1 << local_bits) >> len(held_out)):
+            base = k
+            for b in held_out:  # the kernel's index expansion
+                base = ((base >> b) << (b + 1)) | (base & ((1 << b) - 1))
+            base |= slab_val
+            block = []
+            for e in range(16):
+                off = sum(1 << bits[j] for j in range(p["n_local"]) if (e >> j) & 1)
+                shard = p["members"][e >> p["n_local"]]
+                block.append((shard, base + off))
+                touched[shard][base + off] += 1
+            for e in range(16):
+                if (e >> target_pos) & 1:
+                    continue
+                (s0, i0), (s1, i1) = block[e], block[e | (1 << target_pos)]
+                a, b = shards[s0][i0], shards[s1][i1]
+                shards[s0][i0], shards[s1][i1] = u[0, 0] * a + u[0, 1] * b, u[1, 0] * a + u[1, 1] * b
+    for t in touched:
+        assert np.all(t == 1)  # every amplitude of every shard belongs to exactly one block of exactly one member
+    want = dense_reference(full, nq, bits[target_pos], 0, u)
+    np.testing.assert_allclose(np.concatenate(shards), want, atol=1e-12)
