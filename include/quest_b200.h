@@ -41,8 +41,8 @@ void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long*
 void qb200_setOverlap(int enabled);
 unsigned long long qb200_getOverlappedExchangeCount(void);
 
-/* Sharded registers, opt-in (QUEST_B200_DISTRIBUTED=1 / qb200_setDistributed(1); off by default while it is validated on
- * 2 GPUs only): a run of gates whose fused qubits include g shard-selecting qubits runs as ONE pass over the 2^g GPUs
+/* Sharded registers, opt-in (QUEST_B200_DISTRIBUTED=1 / qb200_setDistributed(1); off by default: validated on 2 GPUs
+ * only, and faster than remapping only when a shard-selecting qubit is not reused by later groups): a run of gates whose fused qubits include g shard-selecting qubits runs as ONE pass over the 2^g GPUs
  * that differ in those qubits, each GPU processing its slab of the pairs over the peer mappings, instead of one slot
  * exchange per such qubit.  The counter reports how many such passes ran.  No reference counterpart. */
 void qb200_setDistributed(int enabled);
