@@ -384,3 +384,28 @@ def test_distributed_pass_plan_partitions_the_work_and_applies_the_gate(world, l
         assert np.all(t == 1)  # every amplitude of every shard belongs to exactly one block of exactly one member
     want = dense_reference(full, nq, bits[target_pos], 0, u)
     np.testing.assert_allclose(np.concatenate(shards), want, atol=1e-12)
+
+
+def test_swap_in_prefers_high_slots_and_falls_back_to_low_ones():
+    """A shard-selecting qubit is exchanged with a slot >= 10 of a large shard (long contiguous runs over NVLink); only
+    when every such slot is pinned by the gate itself (or hosts a guest) does the search drop to the low slots."""
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    lib.qb200_debugRemap.restype = ctypes.c_int
+    nq, L = 15, 13  # 4 shards of 2^13 amplitudes: preferred victims are slots 10, 11, 12
+
+    def run(targets, masks):
+        n = len(targets)
+        ev, phys, canon = (ctypes.c_int * (3 * n))(), (ctypes.c_int * nq)(), (ctypes.c_int * 128)()
+        lib.qb200_debugRemap(nq, L, n, (ctypes.c_int * n)(*targets), (ctypes.c_ulonglong * n)(*masks), ev, phys, canon)
+        return [(ev[3 * i], ev[3 * i + 1]) for i in range(n)], list(phys)
+
+    events, _ = run([13], [0])
+    assert events[0][0] == 13 and events[0][1] >= 10
+    pinned = (1 << 10) | (1 << 11) | (1 << 12)
+    events, _ = run([13], [pinned])           # all preferred slots are controls of the gate
+    assert events[0][0] == 13 and 0 <= events[0][1] < 10
+    # one preferred slot already hosts a guest, the other two are pinned
+    events, phys = run([13, 14], [0, (1 << 13) | sum(1 << s for s in (10, 11, 12) if s != 0)])
+    first_victim = events[0][1]
+    assert first_victim >= 10 and events[1][0] == 14 and events[1][1] not in (10, 11, 12)
+    assert sorted(phys) == list(range(nq))    # still a permutation
