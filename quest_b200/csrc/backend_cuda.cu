@@ -75,7 +75,8 @@ struct Engine {
     bool contract = false;          // QUEST_B200_FMA / qb200_setArithmetic: fused pass may contract a*b+c into fma
     bool remap = true;              // QUEST_B200_REMAP: make shard-selecting qubits local by slot exchange
     unsigned long long slotSwaps = 0;
-    bool distributed = false;       // QUEST_B200_DISTRIBUTED: gates on shard-selecting qubits run as distributed fused passes
+    int distributed = 0;            // QUEST_B200_DISTRIBUTED: 1 gates on shard-selecting qubits run as distributed fused
+                                    // passes, 2 ... unless the recorded queue uses the qubit again (then it is made local)
     bool overlap = true;            // QUEST_B200_OVERLAP: pipeline a slot exchange with the fused pass before it
     int swapCtasPerSm = 1;          // QUEST_B200_SWAP_CTAS: footprint of a pipelined exchange
     int overlapMinBits = 24;        // ... for shards of at least 2^24 amplitudes (QUEST_B200_OVERLAP_MIN_BITS: tests)
@@ -102,6 +103,7 @@ struct QuregRec {
     u64 denseSinceFlush = 0;
     // calcProbOfOutcome: the second query on an unchanged state computes P(qubit = 0) for every qubit in one pass;
     // later queries are answered from here until the state changes (dirty()).
+    bool logicalQueue = false;  // distributed mode: the queue holds logical qubits and full control masks
     bool probValid = false;
     bool exposed = false;  // device pointers were handed out (qb200_getDevicePointers): the state can change unseen
     int probQueries = 0;
@@ -442,87 +444,140 @@ void runGroupInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const Fu
 // tab[e >> nLocalFused], each GPU of the group processes the slab of outer indices that carries its own group index,
 // controls on the fused shard-selecting qubits are ordinary register-mask bits.  NVLink carries (1 - 2^-g) of a shard
 // each way for the whole group instead of half a shard per exchanged qubit (and per exchange back).
+// One group of the distributed mode, already in bit positions: `list` holds its gates with full control masks.
+void runDistributedGroup(const Qureg& q, const std::vector<PendingOp>& list, const FusedGroup& grp) {
+    QuregRec* r = rec(q);
+    const u64 localMask = (1ull << r->localBits) - 1ull;
+    const u64 rankBits = (u64)q.chunkId << r->localBits;  // this rank's values of the shard-selecting bits
+    u64 fusedShardBits = 0;
+    int nLocalFused = 0;
+    for (int j = 0; j < kFuseBits; ++j) {
+        if (grp.bits[j] >= r->localBits) fusedShardBits |= 1ull << grp.bits[j];
+        else ++nLocalFused;
+    }
+    // controls on shard-selecting qubits outside the block: the same for every GPU of the group
+    std::vector<PendingOp> sel;
+    for (int i = 0; i < grp.count; ++i) {
+        PendingOp op = list[grp.first + i];
+        const u64 outside = op.mask & ~localMask & ~fusedShardBits;
+        if ((rankBits & outside) != outside) continue;
+        op.mask &= ~outside;
+        sel.push_back(op);
+    }
+    if (sel.empty()) return;
+    if (!fusedShardBits) {
+        if (sel.size() == 1) {
+            runOpNow(q, sel[0]);
+            return;
+        }
+        const int tier = prepareOps(sel.data(), (int)sel.size(), grp.bits, 64);
+        FusedTimer t;
+        t.start();
+        launchPrepared(r, tier, nullptr, 0);
+        t.stop();
+        ++g.fusedLaunches;
+        g.fusedGates += sel.size();
+        return;
+    }
+    // the group of GPUs, this rank's index in it, and the slab it processes
+    DistPlan dp;
+    if (!planDistributed(r->localBits, q.chunkId, grp.bits, kFuseBits, dp))
+        comm::unsupported("a distributed pass on a shard too small to be divided among its GPUs");
+    const int nShard = dp.nShard, me = dp.me;
+    const SlabPlan& sp = dp.slabs;
+    const int* members = dp.members;
+    prepareOps(sel.data(), (int)sel.size(), grp.bits, r->localBits);
+    fl.nLocalFused = nLocalFused;
+    for (int v = 0; v < (1 << nShard); ++v) {
+        const comm::Partner p = comm::shardOf(q, members[v]);
+        fl.tabRe[v] = p.re;
+        fl.tabIm[v] = p.im;
+    }
+    int n = 0;
+    for (int j = 0; j < nLocalFused; ++j) fl.ins[n++] = grp.bits[j];
+    for (int j = 0; j < sp.nBits; ++j) fl.ins[n++] = sp.bits[j];
+    std::sort(fl.ins, fl.ins + n);
+    fl.nIns = n;
+    fl.slabMask = sp.valueMask(me);
+    fl.nThreads = (u64)r->n >> n;
+    const unsigned int nb = (unsigned int)((fl.nThreads + 127) / 128);
+    for (int v = 0; v < (1 << nShard); ++v)  // everything the others enqueued before this pass has finished
+        if (members[v] != q.chunkId) comm::pairBarrier(members[v], g.stream);
+    FusedTimer t;
+    t.start();
+    k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAllNoise, false, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+    launched();
+    t.stop();
+    for (int v = 0; v < (1 << nShard); ++v)  // the others' writes into this shard have landed
+        if (members[v] != q.chunkId) comm::pairBarrier(members[v], g.stream);
+    ++g.fusedLaunches;
+    ++g.distributedPasses;
+    g.fusedGates += sel.size();
+}
+
+void exchangeSlots(const Qureg& q, SlotSwap sw);
+
+// The queue of the distributed mode holds LOGICAL qubits and full control masks - the same on every rank.  It is walked
+// in program order, one group (a run of gates on at most kFuseBits dense qubits) at a time.  For every dense qubit of
+// the group that currently sits in a shard-selecting slot there are two ways to serve it: leave it there and run the
+// group as a distributed pass, or make it local first (a slot exchange, qb_plan.h).  g.distributed == 2 decides by
+// looking ahead in the recorded queue: a qubit that later groups use again is made local, a qubit this group is the
+// last recorded user of stays where it is.  g.distributed == 1 never exchanges.
 void flushDistributed(const Qureg& q) {
     QuregRec* r = rec(q);
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
+    r->logicalQueue = false;
     if (r->queue.empty()) return;
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
-    const u64 localMask = (1ull << r->localBits) - 1ull;
-    const u64 rankBits = (u64)q.chunkId << r->localBits;  // this rank's values of the shard-selecting bits
-    for (const FusedGroup& grp : groupOps(ops, r->localBits)) {
-        u64 fusedShardBits = 0;
-        int nLocalFused = 0;
-        for (int j = 0; j < kFuseBits; ++j) {
-            if (grp.bits[j] >= r->localBits) fusedShardBits |= 1ull << grp.bits[j];
-            else ++nLocalFused;
-        }
-        // controls on shard-selecting qubits outside the block: the same for every GPU of the group
-        std::vector<PendingOp> sel;
-        for (int i = 0; i < grp.count; ++i) {
-            PendingOp op = ops[grp.first + i];
-            const u64 outside = op.mask & ~localMask & ~fusedShardBits;
-            if ((rankBits & outside) != outside) continue;
-            op.mask &= ~outside;
-            sel.push_back(op);
-        }
-        if (sel.empty()) continue;
-        if (!fusedShardBits) {
-            if (sel.size() == 1) {
-                runOpNow(q, sel[0]);
-                continue;
+    const int n = (int)ops.size();
+    int i = 0;
+    while (i < n) {
+        // the next group, in logical qubits
+        u64 dense = 0;
+        int j = i;
+        while (j < n && j - i < kMaxFusedGates) {
+            const PendingOp& op = ops[j];
+            if (!isDiagonal(op.kind)) {
+                u64 need = 1ull << op.target;
+                if (op.target2 >= 0) need |= 1ull << op.target2;
+                if (__builtin_popcountll(dense | need) > kFuseBits) break;
+                dense |= need;
             }
-            const int tier = prepareOps(sel.data(), (int)sel.size(), grp.bits, 64);
-            FusedTimer t;
-            t.start();
-            launchPrepared(r, tier, nullptr, 0);
-            t.stop();
-            ++g.fusedLaunches;
-            g.fusedGates += sel.size();
-            continue;
+            ++j;
         }
-        // the group of GPUs, this rank's index in it, and the slab it processes
-        DistPlan dp;
-        if (!planDistributed(r->localBits, q.chunkId, grp.bits, kFuseBits, dp))
-            comm::unsupported("a distributed pass on a shard too small to be divided among its GPUs");
-        const int nShard = dp.nShard, me = dp.me;
-        const SlabPlan& sp = dp.slabs;
-        const int* members = dp.members;
-        prepareOps(sel.data(), (int)sel.size(), grp.bits, r->localBits);
-        fl.nLocalFused = nLocalFused;
-        for (int v = 0; v < (1 << nShard); ++v) {
-            const comm::Partner p = comm::shardOf(q, members[v]);
-            fl.tabRe[v] = p.re;
-            fl.tabIm[v] = p.im;
+        for (u64 m = dense; m; m &= m - 1) {
+            const int lq = __builtin_ctzll(m);
+            if (r->map.phys[lq] >= r->localBits && g.distributed == 2 && g.remap) {
+                bool usedLater = false;
+                for (int k = j; k < n && !usedLater; ++k)
+                    usedLater = !isDiagonal(ops[k].kind) && (ops[k].target == lq || ops[k].target2 == lq);
+                if (usedLater) {
+                    const SlotSwap sw = planSwapIn(r->map, lq, dense);
+                    if (sw.globalSlot >= 0) exchangeSlots(q, sw);
+                }
+            }
+            r->map.touch(lq);
         }
-        int n = 0;
-        for (int j = 0; j < nLocalFused; ++j) fl.ins[n++] = grp.bits[j];
-        for (int j = 0; j < sp.nBits; ++j) fl.ins[n++] = sp.bits[j];
-        std::sort(fl.ins, fl.ins + n);
-        fl.nIns = n;
-        fl.slabMask = sp.valueMask(me);
-        fl.nThreads = (u64)r->n >> n;
-        const unsigned int nb = (unsigned int)((fl.nThreads + 127) / 128);
-        for (int v = 0; v < (1 << nShard); ++v)  // everything the others enqueued before this pass has finished
-            if (members[v] != q.chunkId) comm::pairBarrier(members[v], g.stream);
-        FusedTimer t;
-        t.start();
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAllNoise, false, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
-        launched();
-        t.stop();
-        for (int v = 0; v < (1 << nShard); ++v)  // the others' writes into this shard have landed
-            if (members[v] != q.chunkId) comm::pairBarrier(members[v], g.stream);
-        ++g.fusedLaunches;
-        ++g.distributedPasses;
-        g.fusedGates += sel.size();
+        // the group in bit positions under the layout that now holds
+        std::vector<PendingOp> list(ops.begin() + i, ops.begin() + j);
+        for (PendingOp& op : list) {
+            if (!isDiagonal(op.kind)) {
+                op.target = r->map.phys[op.target];
+                if (op.target2 >= 0) op.target2 = r->map.phys[op.target2];
+            }
+            op.mask = r->map.physMask(op.mask);
+        }
+        for (const FusedGroup& grp : groupOps(list, r->localBits)) runDistributedGroup(q, list, grp);
+        i = j;
     }
 }
 
 // Execute everything recorded for this register: single gates through their own kernel, runs of gates through
 // k_fused (one HBM pass per group, qb_fuse.h).
 void flush(const Qureg& q) {
-    if (g.distributed && g.world > 1) {
+    if (rec(q)->logicalQueue) {
         if (g.pendingReg == rec(q)) settle();
         flushDistributed(q);
         return;
@@ -691,6 +746,7 @@ inline QuregRec* fresh(const Qureg& q) {
     if (g.pendingReg == r) settle();
     dirty(r);
     r->queue.clear();
+    r->logicalQueue = false;
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
     r->map.reset(r->map.nQubits, r->localBits);
@@ -703,15 +759,11 @@ void submit(const Qureg& q, PendingOp op) {
     QuregRec* r = rec(q);
     dirty(r);
     if (g.distributed && g.world > 1 && g.fuse && r->localBits >= kFuseBits + 3) {
-        // distributed mode: record the gate as it is (bit positions through the qubit map, which is the identity unless
-        // a two-qubit channel moved something); nothing is decided per rank before the groups are formed
-        if (!isDiagonal(op.kind)) {
-            op.target = r->map.phys[op.target];
-            if (op.target2 >= 0) op.target2 = r->map.phys[op.target2];
-        }
-        op.mask = r->map.physMask(op.mask);
+        // distributed mode: the gate is recorded as it came, in logical qubits with its full control mask; nothing is
+        // decided per rank - and no layout is fixed - before the queue is walked (flushDistributed)
         if (r->callsSinceFlush >= kQueueCap) flush(q);
         ++r->callsSinceFlush;
+        r->logicalQueue = true;
         r->queue.push_back(op);
         return;
     }
@@ -976,7 +1028,7 @@ QuESTEnv createQuESTEnv(void) {
     if (g.world > 1) {
         comm::init(ln, g.device, g.stream);
         if (const char* s = std::getenv("QUEST_B200_OVERLAP")) g.overlap = std::atoi(s) != 0;
-        if (const char* s = std::getenv("QUEST_B200_DISTRIBUTED")) g.distributed = std::atoi(s) != 0;
+        if (const char* s = std::getenv("QUEST_B200_DISTRIBUTED")) g.distributed = std::max(0, std::min(2, std::atoi(s)));
         if (const char* s = std::getenv("QUEST_B200_SWAP_CTAS")) g.swapCtasPerSm = std::max(1, std::min(8, std::atoi(s)));
         if (const char* s = std::getenv("QUEST_B200_OVERLAP_MIN_BITS")) g.overlapMinBits = std::max(8, std::atoi(s));
         int lowPrio = 0, highPrio = 0;
@@ -1146,7 +1198,7 @@ unsigned long long qb200_getOverlappedExchangeCount(void) { return g.overlapped;
 void qb200_setDistributed(int enabled) {
     requireEngine();
     qb200_setRemap(g.remap ? 1 : 0);
-    g.distributed = enabled != 0;
+    g.distributed = std::max(0, std::min(2, enabled));
 }
 unsigned long long qb200_getDistributedPassCount(void) { return g.distributedPasses; }
 
