@@ -45,7 +45,7 @@ unsigned long long qb200_getOverlappedExchangeCount(void);
  * only, and faster than remapping only when a shard-selecting qubit is not reused by later groups): a run of gates whose fused qubits include g shard-selecting qubits runs as ONE pass over the 2^g GPUs
  * that differ in those qubits, each GPU processing its slab of the pairs over the peer mappings, instead of one slot
  * exchange per such qubit.  The counter reports how many such passes ran.  No reference counterpart. */
-void qb200_setDistributed(int enabled);
+void qb200_setDistributed(int mode);  /* 0 off, 1 always distributed, 2 make a qubit local first if the recorded queue uses it again */
 unsigned long long qb200_getDistributedPassCount(void);
 
 /* calcProbOfOutcome on state-vectors: the second query on an unchanged state computes P(qubit = 0) for EVERY qubit in
