@@ -107,6 +107,11 @@ void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long l
 int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, const unsigned long long* masks,
                      int* eventsOut, int* physOut, int* canonOut);
 
+/* Test hook (host logic only, makes no CUDA call): how the distributed mode cuts a queue of logical gates into groups and
+ * which slot exchanges it places before each.  Layout at the definition. */
+int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* kinds, const int* targets, const int* targets2,
+                    const unsigned long long* masks, int lookahead, int* stepsOut);
+
 /* Test hook (host logic only, makes no CUDA call): the plan of a distributed fused pass for rank chunkId.  Layout at the
  * definition. */
 int qb200_debugDistributed(int localBits, int chunkId, const int* bits, int* out);

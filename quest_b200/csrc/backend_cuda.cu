@@ -531,37 +531,12 @@ void flushDistributed(const Qureg& q) {
     if (r->queue.empty()) return;
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
-    const int n = (int)ops.size();
-    int i = 0;
-    while (i < n) {
-        // the next group, in logical qubits
-        u64 dense = 0;
-        int j = i;
-        while (j < n && j - i < kMaxFusedGates) {
-            const PendingOp& op = ops[j];
-            if (!isDiagonal(op.kind)) {
-                u64 need = 1ull << op.target;
-                if (op.target2 >= 0) need |= 1ull << op.target2;
-                if (__builtin_popcountll(dense | need) > kFuseBits) break;
-                dense |= need;
-            }
-            ++j;
-        }
-        for (u64 m = dense; m; m &= m - 1) {
-            const int lq = __builtin_ctzll(m);
-            if (r->map.phys[lq] >= r->localBits && g.distributed == 2 && g.remap) {
-                bool usedLater = false;
-                for (int k = j; k < n && !usedLater; ++k)
-                    usedLater = !isDiagonal(ops[k].kind) && (ops[k].target == lq || ops[k].target2 == lq);
-                if (usedLater) {
-                    const SlotSwap sw = planSwapIn(r->map, lq, dense);
-                    if (sw.globalSlot >= 0) exchangeSlots(q, sw);
-                }
-            }
-            r->map.touch(lq);
-        }
+    // decisions first (qb::planWalk, host bookkeeping on a copy of the layout), then the same steps on the GPUs
+    for (const WalkStep& st : planWalk(r->map, ops, g.distributed == 2 && g.remap)) {
+        for (int k = 0; k < st.nSwaps; ++k) exchangeSlots(q, st.swaps[k]);
+        for (u64 m = st.dense; m; m &= m - 1) r->map.touch(__builtin_ctzll(m));
         // the group in bit positions under the layout that now holds
-        std::vector<PendingOp> list(ops.begin() + i, ops.begin() + j);
+        std::vector<PendingOp> list(ops.begin() + st.first, ops.begin() + st.first + st.count);
         for (PendingOp& op : list) {
             if (!isDiagonal(op.kind)) {
                 op.target = r->map.phys[op.target];
@@ -570,7 +545,6 @@ void flushDistributed(const Qureg& q) {
             op.mask = r->map.physMask(op.mask);
         }
         for (const FusedGroup& grp : groupOps(list, r->localBits)) runDistributedGroup(q, list, grp);
-        i = j;
     }
 }
 
@@ -1711,6 +1685,33 @@ int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int l
             o += 11;
         }
     return sp.nBits;
+}
+
+// Host walk of a logical gate queue (qb::planWalk), exposed for CPU-only tests (no CUDA call).  Gates: kind, logical
+// target, second target (-1 if none), logical control mask.  stepsOut: per step first, count, nSwaps, then up to 4 pairs
+// (globalSlot, localSlot) = 11 ints.  Returns the number of steps.
+int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* kinds, const int* targets, const int* targets2,
+                    const unsigned long long* masks, int lookahead, int* stepsOut) {
+    QubitMap m;
+    m.reset(nQubits, localBits);
+    std::vector<PendingOp> ops(nOps);
+    for (int i = 0; i < nOps; ++i) {
+        std::memset(&ops[i], 0, sizeof(PendingOp));
+        ops[i].kind = kinds[i];
+        ops[i].target = targets[i];
+        ops[i].target2 = targets2[i];
+        ops[i].mask = masks[i];
+    }
+    const std::vector<WalkStep> steps = planWalk(m, ops, lookahead != 0);
+    for (size_t k = 0; k < steps.size(); ++k) {
+        int* o = stepsOut + 11 * k;
+        o[0] = steps[k].first; o[1] = steps[k].count; o[2] = steps[k].nSwaps;
+        for (int j = 0; j < 4; ++j) {
+            o[3 + 2 * j] = j < steps[k].nSwaps ? steps[k].swaps[j].globalSlot : -1;
+            o[4 + 2 * j] = j < steps[k].nSwaps ? steps[k].swaps[j].localSlot : -1;
+        }
+    }
+    return (int)steps.size();
 }
 
 // Host logic of the distributed fused pass (qb::planDistributed), exposed for CPU-only tests (no CUDA call).

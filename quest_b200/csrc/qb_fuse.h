@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "QuEST_precision.h"
+#include "qb_plan.h"
 
 namespace qb {
 
@@ -138,6 +139,62 @@ inline FusedGate describe(const PendingOp& op, const int* bits) {
     fg.outerMask = outer;
     for (int k = 0; k < 8; ++k) fg.c[k] = op.c[k];
     return fg;
+}
+
+// ---- walking a queue of LOGICAL gates (distributed mode of sharded registers) ------------------------------------
+// The queue holds gates in logical qubits with full control masks, the same on every rank.  It is cut, in program
+// order, into groups (runs of gates on at most kFuseBits dense qubits); before each group the dense qubits that sit in
+// shard-selecting slots are either left there (the group runs as a distributed pass) or exchanged with a local slot
+// first.  With `lookahead` a qubit is made local iff a later gate of the queue uses it as a dense target again; without,
+// never.  Pure bookkeeping on a copy of the qubit map: the executor replays the same exchanges on the real one.
+struct WalkStep {
+    int first, count;   // gates [first, first + count) of the queue form the group ...
+    int nSwaps;
+    SlotSwap swaps[kFuseBits];  // ... which runs after these slot exchanges
+    unsigned long long dense;   // its dense logical qubits
+};
+
+inline std::vector<WalkStep> planWalk(QubitMap map, const std::vector<PendingOp>& ops, bool lookahead) {
+    std::vector<WalkStep> steps;
+    const int n = (int)ops.size();
+    int i = 0;
+    while (i < n) {
+        WalkStep st;
+        st.first = i;
+        st.nSwaps = 0;
+        st.dense = 0;
+        int j = i;
+        while (j < n && j - i < kMaxFusedGates) {
+            const PendingOp& op = ops[j];
+            if (!isDiagonal(op.kind)) {
+                unsigned long long need = 1ull << op.target;
+                if (op.target2 >= 0) need |= 1ull << op.target2;
+                if (__builtin_popcountll(st.dense | need) > kFuseBits) break;
+                st.dense |= need;
+            }
+            ++j;
+        }
+        st.count = j - i;
+        for (unsigned long long m = st.dense; m; m &= m - 1) {
+            const int lq = __builtin_ctzll(m);
+            if (lookahead && map.phys[lq] >= map.localBits) {
+                bool usedLater = false;
+                for (int k = j; k < n && !usedLater; ++k)
+                    usedLater = !isDiagonal(ops[k].kind) && (ops[k].target == lq || ops[k].target2 == lq);
+                if (usedLater) {
+                    const SlotSwap sw = planSwapIn(map, lq, st.dense);
+                    if (sw.globalSlot >= 0) {
+                        map.applySwap(sw.globalSlot, sw.localSlot);
+                        st.swaps[st.nSwaps++] = sw;
+                    }
+                }
+            }
+            map.touch(lq);
+        }
+        steps.push_back(st);
+        i = j;
+    }
+    return steps;
 }
 
 // ---- device dispatch ---------------------------------------------------------------------------------------

@@ -409,3 +409,83 @@ def test_swap_in_prefers_high_slots_and_falls_back_to_low_ones():
     first_victim = events[0][1]
     assert first_victim >= 10 and events[1][0] == 14 and events[1][1] not in (10, 11, 12)
     assert sorted(phys) == list(range(nq))    # still a permutation
+
+
+# ---- walking a queue of logical gates (qb::planWalk: distributed mode, with and without look-ahead) -----------------
+
+def _walk(lib, nq, local_bits, ops, lookahead):
+    n = len(ops)
+    out = (ctypes.c_int * (11 * n))()
+    ns = lib.qb200_debugWalk(nq, local_bits, n, (ctypes.c_int * n)(*[o[0] for o in ops]), (ctypes.c_int * n)(*[o[1] for o in ops]),
+                             (ctypes.c_int * n)(*[-1] * n), (ctypes.c_ulonglong * n)(*[o[2] for o in ops]), int(lookahead), out)
+    steps = []
+    for k in range(ns):
+        o = out[11 * k:11 * (k + 1)]
+        steps.append(dict(first=o[0], count=o[1], swaps=[(o[3 + 2 * j], o[4 + 2 * j]) for j in range(o[2])]))
+    return steps
+
+
+@pytest.mark.parametrize("world,seed,lookahead", [(2, 11, False), (2, 12, True), (4, 13, True), (8, 14, True), (8, 15, False)])
+def test_walk_of_a_logical_queue_reproduces_the_circuit(world, seed, lookahead):
+    """The steps cover the queue in order with at most four dense qubits each; replaying them - slot exchanges as bit
+    swaps, then the group's gates at the bit positions of the layout that then holds (shard-selecting positions
+    included: that is what a distributed pass executes) - gives the circuit's result once the layout is undone.
+    With look-ahead a qubit is exchanged exactly when a later gate uses it again; without, never."""
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    lib.qb200_debugWalk.restype = ctypes.c_int
+    K_MATRIX = 0
+    rng = random.Random(seed)
+    nq = 10
+    L = nq - (world.bit_length() - 1)
+    ops, mats = [], []
+    for _ in range(90):
+        t = rng.randrange(nq) if rng.random() < 0.6 else rng.randrange(L, nq)
+        cs = rng.sample([q for q in range(nq) if q != t], rng.choice([0, 0, 1, 2]))
+        ops.append((K_MATRIX, t, sum(1 << c for c in cs)))
+        mats.append(rand_u(rng))
+    steps = _walk(lib, nq, L, ops, lookahead)
+    assert steps[0]["first"] == 0 and sum(s["count"] for s in steps) == len(ops)
+    state = circuits.random_state(1 << nq, seed)
+    want = state.copy()
+    for op, u in zip(ops, mats):
+        want = dense_reference(want, nq, op[1], op[2], u)
+    cur = state.copy()
+    layout = list(range(nq))  # logical -> bit position
+    pos = 0
+    n_swaps = 0
+    for s in steps:
+        assert s["first"] == pos
+        group = range(s["first"], s["first"] + s["count"])
+        dense = {ops[i][1] for i in group}
+        assert 1 <= len(dense) <= 4
+        later = {ops[i][1] for i in range(s["first"] + s["count"], len(ops))}
+        brought_in = set()
+        for g, l in s["swaps"]:
+            assert g >= L > l
+            brought_in.add(layout.index(g))
+            cur = _swap_bits(cur, g, l)
+            a, b = layout.index(g), layout.index(l)
+            layout[a], layout[b] = l, g
+            n_swaps += 1
+        if lookahead:
+            # exactly the dense qubits that were shard-selecting before this step AND are used again later came in
+            assert brought_in <= dense and all(q in later for q in brought_in)
+            for q in dense:
+                if layout[q] >= L:
+                    assert q not in later
+        else:
+            assert not s["swaps"]
+        for i in group:
+            _, t, m = ops[i]
+            pm = sum(1 << layout[c] for c in range(nq) if (m >> c) & 1)
+            cur = dense_reference(cur, nq, layout[t], pm, mats[i])
+        pos += s["count"]
+    # undo the layout: bring every logical qubit back to its own bit position
+    for q in range(nq):
+        if layout[q] != q:
+            other = layout.index(q)
+            cur = _swap_bits(cur, layout[q], q)
+            layout[other], layout[q] = layout[q], q
+    np.testing.assert_allclose(cur, want, atol=1e-12)
+    if lookahead:
+        assert n_swaps > 0
