@@ -97,17 +97,38 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------------------
-# reference arm / cpu_baseline: the reference's own CPU library on a bounded sample of the sweep
+# the reference's own CPU library: reference arm, cpu_baseline and the parity leg
 # ------------------------------------------------------------------------------------------------------------
 
-def cpu_sample_ops(nq, targets):
-    ops = []
-    for t in targets:
-        ops.append(("hadamard", t))
-        ops.append(("compactUnitary", t, circuits.SWEEP_ALPHA, circuits.SWEEP_BETA))
-        ops.append(("controlledNot", (t + 1) % nq, t))
-        ops.append(("multiControlledPhaseShift", [t, (t + 1) % nq, (t + 2) % nq], 0.7))
-    return ops
+METRIC = "gates/sec (30q double state-vector single-gate sweep)"
+CLASSES = ("hadamard", "compactUnitary", "controlledNot", "multiControlledPhaseShift")
+
+
+def sweep_config(nq, world, shard_bits, n_ops):
+    """`config` of the JSON line: the same dict on both arms (the driver compares them)."""
+    if world == 1:
+        workload = (f"configs[1]: {nq}-qubit state-vector single-gate sweep, every target, 4 gate classes "
+                    f"({n_ops} gates/step), state = initPlusState + rotateY(t, 0.1(t+1)) on every qubit")
+    else:
+        workload = (f"configs[1] sweep weak-scaled: {nq}-qubit state-vector sharded over {world} GPUs (2^{shard_bits} "
+                    f"amplitudes per GPU), every target, 4 gate classes ({n_ops} gates/step, "
+                    f"{4 * int(math.log2(world))} of them on shard-selecting qubits); value counts one gate call on the "
+                    f"sharded register as {world} shard-gates (gates/s x {world})")
+    return {"workload": workload, "qubits": nq, "amps_per_gpu": 1 << shard_bits, "gates_per_step": n_ops,
+            "l2": "state (16 GiB per GPU) is far larger than L2: every pass streams from HBM"}
+
+
+def sweep_prepare(lib, q, nq):
+    """The dense, non-trivial input state of the sweep - the same calls on every arm."""
+    lib.initPlusState(q)
+    for t in range(nq):
+        lib.rotateY(q, t, 0.1 * (t + 1))
+
+
+def use_all_host_cores():
+    # torchrun pins OMP_NUM_THREADS=1 for its workers; the CPU arm is meant to use every host core
+    os.environ["OMP_NUM_THREADS"] = os.environ.get("QUEST_BENCH_THREADS", str(os.cpu_count() or 1))
+    return int(os.environ["OMP_NUM_THREADS"])
 
 
 def load_cpu_library():
@@ -118,44 +139,138 @@ def load_cpu_library():
     return capi.load(capi.ORACLE_LIB), "port"
 
 
-def time_cpu(nq, targets, steps, warmup):
-    """Wall-clock the CPU library on `steps` repetitions of the sample; returns (gates/s, cores, kind, seconds)."""
-    lib, kind = load_cpu_library()
-    env = lib.createQuESTEnv()
-    q = lib.createQureg(nq, env)
-    lib.initPlusState(q)
-    ops = cpu_sample_ops(nq, targets)
-    for _ in range(warmup):
-        circuits.run_circuit(lib, q, ops[:4])
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        circuits.run_circuit(lib, q, ops)
-    dt = time.perf_counter() - t0
-    lib.destroyQureg(q, env)
-    cores = int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
-    return steps * len(ops) / dt, cores, kind, dt, len(ops)
+def sampled_step_ops(nq, step):
+    """The reference arm's bounded step: every target once, the gate class rotating with target and step, so that four
+    consecutive steps are exactly one full sweep (120 gates at 30 qubits) and every step holds all four classes."""
+    full = circuits.config2_sweep(nq)
+    return [full[4 * t + (t + step) % 4] for t in range(nq)]
 
 
 def run_reference_arm(args, rank, world):
     if rank != 0:
         return
-    # torchrun pins OMP_NUM_THREADS=1 for its workers; the CPU arm is meant to use every host core
-    os.environ["OMP_NUM_THREADS"] = os.environ.get("QUEST_BENCH_THREADS", str(os.cpu_count() or 1))
-    nq = args.qubits
-    targets = [0, 15, nq - 1]
-    value, cores, kind, dt, per_step = time_cpu(nq, targets, args.steps, min(args.warmup, 1))
-    sample = (f"{per_step} gates per step: config-2 sweep restricted to targets {targets} at {nq} qubits, "
-              f"{args.steps} steps, wall clock {dt:.1f} s")
+    cores = use_all_host_cores()
+    nq = args.qubits  # at N > 1 too: a gate on the (nq + log2 N)-qubit register is N shard-gates of 2^nq amplitudes
+    lib, kind = load_cpu_library()
+    env = lib.createQuESTEnv()
+    q = lib.createQureg(nq, env)
+    sweep_prepare(lib, q, nq)
+    warmup = max(args.warmup, 0)
+    for w in range(warmup):
+        circuits.run_circuit(lib, q, sampled_step_ops(nq, w))
+    n_gates = 0
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        ops = sampled_step_ops(nq, warmup + s)
+        circuits.run_circuit(lib, q, ops)
+        n_gates += len(ops)
+    dt = time.perf_counter() - t0
+    prob = lib.calcTotalProb(q)
+    lib.destroyQureg(q, env)
+    assert abs(prob - 1.0) < 1e-9, prob
+    value = n_gates / dt
+    n_full = len(circuits.config2_sweep(nq + int(math.log2(world))))
+    sample = (f"{nq} gates per step ({args.steps} steps, {warmup} warm-up): every target of the configs[1] sweep once, the "
+              f"gate class (hadamard / compactUnitary / controlledNot / multiControlledPhaseShift) rotating with target and "
+              f"step so that 4 steps = one full 120-gate sweep; same state preparation as the quest_b200 arm; wall clock "
+              f"{dt:.1f} s on {cores} threads"
+              + ("" if world == 1 else f"; timed at the shard size ({nq} qubits), where one gate is one shard-gate"))
     line = {
-        "impl": "reference", "metric": "gates/sec (30q double state-vector single-gate sweep)", "value": value,
-        "unit": "gates/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "impl": "reference", "metric": METRIC, "value": value,
+        "unit": "gates/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": warmup,
         "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"configs[1] sweep, bounded sample on host CPU ({nq} qubits)", "qubits": nq},
+        "config": sweep_config(nq + int(math.log2(world)), world, nq, n_full),
         "cpu_baseline": {"value": value, "unit": "gates/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "gates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def parity_leg(lib, env, rank, world, nq, torch, dist):
+    """Outside every timed region: ONE configs[1] sweep step (state preparation + every gate of the sweep) on a fresh
+    nq-qubit register through the product, and the same calls through the reference's own CPU library (oracle/_ref) on
+    rank 0; every amplitude is compared, then three measurements and a collapseToOutcome under the same seed, then
+    every amplitude again.  Returns (parity dict, cpu_baseline dict) on rank 0, (None, None) elsewhere."""
+    import numpy as np
+
+    ops = circuits.config2_sweep(nq)
+    tail = [("measure", 0), ("measure", nq // 2), ("measure", nq - 1), ("collapseToOutcome", 1, 0), ("calcTotalProb",)]
+    q = lib.createQureg(nq, env)
+    n_local = int(q.numAmpsPerChunk)
+    sweep_prepare(lib, q, nq)
+    circuits.run_circuit(lib, q, ops)
+
+    cpu = cq = cenv = None
+    cpu_info = None
+    if rank == 0:
+        cores = use_all_host_cores()
+        cpu, kind = load_cpu_library()
+        cenv = cpu.createQuESTEnv()
+        cq = cpu.createQureg(nq, cenv)
+        sweep_prepare(cpu, cq, nq)
+        t0 = time.perf_counter()
+        circuits.run_circuit(cpu, cq, ops)
+        cpu_dt = time.perf_counter() - t0
+        cpu_info = {"value": len(ops) / cpu_dt, "unit": "gates/s", "cores": cores, "kind": kind,
+                    "sample": f"one full configs[1] sweep step ({len(ops)} gates) at {nq} qubits on the state the parity "
+                              f"check compares, wall clock {cpu_dt:.1f} s"}
+
+    chunk = 1 << 24
+
+    def compare():
+        """max |diff| / max |amp| over the whole register and whether every double is bit-identical."""
+        worst, biggest, same = 0.0, 0.0, True
+        if world == 1:
+            re = np.empty(min(chunk, n_local), dtype=np.float64)
+            im = np.empty_like(re)
+            for at in range(0, n_local, chunk):
+                n = min(chunk, n_local - at)
+                lib.qb200_copyAmpsToHost(q, at, n, lib.real_ptr(re), lib.real_ptr(im))
+                for got, want_ptr in ((re, cq.stateVec.real), (im, cq.stateVec.imag)):
+                    want = np.ctypeslib.as_array(want_ptr, shape=(n_local,))[at:at + n]
+                    same = same and np.array_equal(got[:n], want)
+                    worst = max(worst, float(np.abs(got[:n] - want).max()))
+                    biggest = max(biggest, float(np.abs(want).max()))
+            return worst / biggest, same
+        shard = lib.get_state(q)  # this rank's shard, identity layout restored
+        mine = torch.from_numpy(shard.view(np.float64).copy()).cuda()
+        gathered = [torch.empty_like(mine) for _ in range(world)] if rank == 0 else None
+        dist.gather(mine, gathered, dst=0)
+        if rank != 0:
+            return None, None
+        want_re = np.ctypeslib.as_array(cq.stateVec.real, shape=(n_local * world,))
+        want_im = np.ctypeslib.as_array(cq.stateVec.imag, shape=(n_local * world,))
+        for r, t in enumerate(gathered):
+            got = t.cpu().numpy().view(np.complex128)
+            sl = slice(r * n_local, (r + 1) * n_local)
+            same = same and np.array_equal(got.real, want_re[sl]) and np.array_equal(got.imag, want_im[sl])
+            worst = max(worst, float(np.abs(got.real - want_re[sl]).max()), float(np.abs(got.imag - want_im[sl]).max()))
+            biggest = max(biggest, float(np.abs(want_re[sl]).max()), float(np.abs(want_im[sl]).max()))
+        return worst / biggest, same
+
+    rel1, same1 = compare()
+    got_tail = circuits.run_circuit(lib, q, tail, seed=77)
+    want_tail = circuits.run_circuit(cpu, cq, tail, seed=77) if rank == 0 else None
+    rel2, same2 = compare()
+    lib.destroyQureg(q, env)
+    if rank != 0:
+        return None, None
+    cpu.destroyQureg(cq, cenv)
+    outcomes_equal = [int(x) for x in got_tail[:3]] == [int(x) for x in want_tail[:3]]
+    scalars_rel = max(abs(a - b) / max(abs(b), 1e-300) for a, b in zip(got_tail[3:], want_tail[3:]))
+    ok = rel1 <= 1e-12 and rel2 <= 1e-12 and outcomes_equal and scalars_rel <= 1e-12
+    parity = {"qubits": nq, "n_gpus": world, "against": "oracle/_ref (the reference's own CPU/OpenMP build)" if kind == "reference"
+              else "oracle/ (CPU restatement)", "gates": nq + len(ops), "amplitudes_compared": n_local * world,
+              "max_rel_diff": rel1, "bit_identical": bool(same1),
+              "measurement_outcomes": [int(x) for x in got_tail[:3]], "outcomes_equal": outcomes_equal,
+              "collapse_prob_and_total_prob_rel_diff": scalars_rel,
+              "max_rel_diff_after_measurements": rel2, "bit_identical_after_measurements": bool(same2),
+              "tolerance": 1e-12, "ok": bool(ok),
+              "what": "initPlusState + rotateY on every qubit + one full configs[1] sweep step, every amplitude compared "
+                      "(max |diff| / max |amp|); then measure x3 + collapseToOutcome under seedQuEST({77,155}) and every "
+                      "amplitude again"}
+    return parity, cpu_info
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -169,7 +284,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="quest_b200", choices=["quest_b200", "reference"])
     ap.add_argument("--qubits", type=int, default=30, help="qubits per 1-GPU shard (default 30 = BASELINE config)")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity leg (and with it cpu_baseline)")
+    ap.add_argument("--parity-qubits", type=int, default=0, help="register size of the parity leg (default: 30 at N=1, 28 sharded at N>1)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-34q", action="store_true")
     args = ap.parse_args()
@@ -204,20 +320,10 @@ def main():
 
     shard_bits = args.qubits
     nq = shard_bits + int(math.log2(world))
-    if world == 1:
-        ops = circuits.config2_sweep(nq)
-        workload = f"configs[1]: {nq}-qubit state-vector single-gate sweep, every target, 4 gate classes (120 gates/step)"
-    else:
-        ops = circuits.config2_sweep(nq)
-        workload = (f"configs[1] sweep weak-scaled: {nq}-qubit state-vector sharded over {world} GPUs (2^{shard_bits} "
-                    f"amplitudes per GPU), every target, 4 gate classes ({len(ops)} gates/step, "
-                    f"{4 * int(math.log2(world))} of them on shard-selecting qubits)")
+    ops = circuits.config2_sweep(nq)
     q = lib.createQureg(nq, env)
     n_local = int(q.numAmpsPerChunk)
-    lib.initPlusState(q)
-    # a dense, non-trivial state: one rotation per qubit (same recipe on the CPU arm)
-    for t in range(nq):
-        lib.rotateY(q, t, 0.1 * (t + 1))
+    sweep_prepare(lib, q, nq)  # a dense, non-trivial state: one rotation per qubit (same calls on the CPU arm)
 
     lib.lib.qb200_setFusion.argtypes = [ctypes.c_int]
     lib.lib.qb200_setKernelTiming.argtypes = [ctypes.c_int]
@@ -469,23 +575,24 @@ def main():
         else:
             circuit33 = {"skipped": f"only {free_b >> 30} GiB of HBM free"}
 
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        targets = list(range(0, nq, 2))  # every second target of the sweep: ~11 s of CPU work at 30 qubits
-        v, cores, kind, dt, per_step = time_cpu(nq, targets, 1, 1)
-        cpu = {"value": v, "unit": "gates/s", "cores": cores, "kind": kind,
-               "sample": f"{per_step} gates: config-2 sweep restricted to targets {targets} at {nq} qubits, wall clock {dt:.1f} s"}
+    # parity at the size the numbers are quoted on (N = 1: 30 qubits; N > 1: 28 qubits sharded over all GPUs so that the
+    # CPU can follow), against the reference's own CPU library; its timed sweep step doubles as cpu_baseline
+    parity = cpu = None
+    if not args.no_parity:
+        parity_nq = args.parity_qubits or (nq if world == 1 else 28)
+        parity, cpu = parity_leg(lib, env, rank, world, parity_nq, torch, dist if world > 1 else None)
+        if world > 1:
+            cpu = None  # contract: cpu_baseline on rank 0 at N = 1 only
 
     if rank == 0:
         line = {
-            "metric": "gates/sec (30q double state-vector single-gate sweep)" if world == 1 else
-                      "shard-gates/sec summed over GPUs (configs[1] sweep weak-scaled, 2^30-amplitude shards)",
+            "metric": METRIC,
             "value": value, "unit": "gates/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload, "qubits": nq, "amps_per_gpu": n_local, "gates_per_step": len(ops),
-                       "l2": "state (16 GiB per GPU) is far larger than L2: every pass streams from HBM"},
+            "config": sweep_config(nq, world, shard_bits, len(ops)),
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+            "parity": parity,
         }
         if contracted:
             line["contracted_arithmetic"] = contracted
@@ -499,6 +606,8 @@ def main():
     if world > 1:
         dist.destroy_process_group()
     lib.destroyQuESTEnv(env)
+    if rank == 0 and parity is not None and not parity["ok"]:
+        raise SystemExit(f"bench.py: PARITY FAILED against the reference CPU library: {parity}")
 
 
 if __name__ == "__main__":

@@ -52,7 +52,10 @@ unsigned long long qb200_getDistributedPassCount(void);
  * one pass over HBM; further queries are answered from that result until any call changes the state (e.g. the per-qubit
  * read-out after a QFT costs two passes instead of one per qubit).  QUEST_B200_PROB_CACHE=0 disables it.  Registers whose
  * device pointers were handed out (qb200_getDevicePointers) are never cached.  The reference recomputes every query
- * (QuEST_cpu_local.c:267, QuEST_cpu.c:2844). */
+ * (QuEST_cpu_local.c:267, QuEST_cpu.c:2844).  Numerical note: the all-qubit pass adds the same terms in another order
+ * than the one-qubit pass, so the first and a later query on an unchanged state may differ in the last bits (~1e-16
+ * relative); measure() draws against whichever value it is given, so an outcome can differ from the uncached path only
+ * when the random draw lands within that distance of P(0). */
 
 /* Bulk state I/O.  setAmps / initStateFromAmps / setDensityAmps and qb200_copyAmpsToHost accept any host pointer.  From
  * pinned memory the copy runs at the PCIe rate as it is; from pageable memory (malloc, numpy) transfers of 8 MiB and more
@@ -86,7 +89,12 @@ void qb200_getFusedKernelTime(double* totalMs, unsigned long long* launches);
 int qb200_getDevice(void);
 
 /* Device addresses of this rank's shard: real[numAmpsPerChunk], imag[numAmpsPerChunk] of qreal.
- * Stands in for the reference's Qureg.stateVec host arrays (QuEST.h:100), which this library never allocates. */
+ * Stands in for the reference's Qureg.stateVec host arrays (QuEST.h:100), which this library never allocates.
+ * The call first executes every gate recorded for the register (and restores the identity qubit layout of a sharded
+ * one).  From then on the register takes no part in gate fusion: each later gate call enqueues its own kernel on the
+ * engine stream at once, so work the caller enqueues on that stream (qb200_getStream) afterwards sees the amplitudes
+ * all earlier API calls produce, and nothing recorded can later overwrite what the caller wrote.  Work on OTHER
+ * streams must be ordered against the engine stream by the caller (events, or syncQuESTEnv). */
 void qb200_getDevicePointers(Qureg qureg, void** real, void** imag);
 
 /* Copy n amplitudes of this rank's shard, from local index start, to host arrays.  Synchronises.
@@ -135,7 +143,8 @@ int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* target
  * kept until the process exits.  Limits: numAmps <= QB200_NOALLOC_MAX_AMPS (2^31), larger sizes are refused.  All
  * calls on a GPU share that array (the call clears the counter it needs itself): calls that overlap in time on
  * one GPU race and must be serialised by the caller.  The first call on each GPU performs a one-time address
- * look-up and should be made outside of any stream capture. */
+ * look-up and should be made outside of any stream capture.  The GPU that holds dReal/dImag must be the current
+ * device (cudaSetDevice) and own cudaStream; a state on another GPU is refused. */
 #define QB200_NOALLOC_MAX_AMPS (1LL << 31)
 int qb200_calcTotalProbNoAlloc(const qreal* dReal, const qreal* dImag, long long int numAmps, double* dSumOut,
                                void* cudaStream);

@@ -241,8 +241,8 @@ def config4_noisy(nq: int = 15, layers: int = 10) -> List[Op]:
 
 
 def config5_sharded(nq: int = 34, layers: int = 3, seed: int = 34) -> List[Op]:
-    """configs[4]: random circuit with >=25% of targets on the top three (shard-crossing) qubits, then
-    measurements, one of them on a global qubit.  Same seed => same circuit for every GPU count."""
+    """configs[4]: random circuit with >=25% of targets on the top three (shard-crossing) qubits, then three
+    measurements (one on a global qubit) and a collapseToOutcome on another global qubit.  Same seed => same circuit for every GPU count."""
     rng = random.Random(seed)
     ops: List[Op] = []
     for _ in range(layers):
@@ -261,6 +261,9 @@ def config5_sharded(nq: int = 34, layers: int = 3, seed: int = 34) -> List[Op]:
     ops.append(("measure", nq - 1))
     ops.append(("measure", 3))
     ops.append(("measure", nq // 2))
+    # ... and a collapse onto a GIVEN outcome of a shard-selecting qubit (reference QuEST.c:546): every shard is either
+    # renormalised as a whole or cleared (QuEST_cpu_distributed.c:1274-1292)
+    ops.append(("collapseToOutcome", nq - 2, 0))
     ops.append(("calcTotalProb",))
     return ops
 

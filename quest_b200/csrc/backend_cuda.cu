@@ -761,7 +761,9 @@ void submit(const Qureg& q, PendingOp op) {
         }
         op.mask = r->map.physMask(op.mask);
     }
-    const bool recording = g.fuse && r->localBits >= kFuseBits;
+    // registers whose device pointers were handed out run every gate at once: whoever holds the raw pointers sees the
+    // amplitudes the API calls so far produce (stream-ordered), and nothing queued can overwrite what they write
+    const bool recording = g.fuse && !r->exposed && r->localBits >= kFuseBits;
     if (recording) {  // before any rank-dependent decision: every rank counts every gate call
         if (r->callsSinceFlush >= kQueueCap) flush(q);
         ++r->callsSinceFlush;

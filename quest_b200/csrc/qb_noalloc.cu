@@ -24,6 +24,7 @@
 // The function calls no cudaMalloc, cudaFree, cudaHostAlloc or any library routine that allocates.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdio>
 
 #include "qb_device.cuh"
@@ -77,7 +78,9 @@ __global__ void __launch_bounds__(kThreads) k_totalProbSlabs(const qreal* __rest
     if (threadIdx.x == 0) *out = total[0];
 }
 
-unsigned char* g_scratchAddr[kMaxDevices] = {nullptr};
+// Per-device address of g_scratch, looked up on the first call on that device.  Atomic: two host threads may make
+// their first call on one GPU at the same time (both then store the same value).
+std::atomic<unsigned char*> g_scratchAddr[kMaxDevices];
 
 int fail(const char* what, cudaError_t e = cudaSuccess) {
     if (e != cudaSuccess)
@@ -104,13 +107,19 @@ extern "C" int qb200_calcTotalProbNoAlloc(const qreal* dReal, const qreal* dImag
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return fail("cudaGetDevice", e);
     if (dev < 0 || dev >= kMaxDevices) return fail("device ordinal out of range");
-    if (!g_scratchAddr[dev]) {  // set-up, once per device, with that device current
+    // The scratch belongs to the CURRENT device, so the amplitudes must live there too: a pointer into another GPU's
+    // memory would be paired with the wrong scratch (and a kernel launched on the wrong device).
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, dReal) == cudaSuccess && attr.type == cudaMemoryTypeDevice && attr.device != dev)
+        return fail("dReal lives on another GPU than the current device; call cudaSetDevice for the GPU that holds the state");
+    unsigned char* scratch = g_scratchAddr[dev].load(std::memory_order_acquire);
+    if (!scratch) {  // set-up, once per device, with that device current
         void* p = nullptr;
         e = cudaGetSymbolAddress(&p, g_scratch);
         if (e != cudaSuccess || !p) return fail("cudaGetSymbolAddress(scratch)", e);
-        g_scratchAddr[dev] = static_cast<unsigned char*>(p);
+        scratch = static_cast<unsigned char*>(p);
+        g_scratchAddr[dev].store(scratch, std::memory_order_release);
     }
-    unsigned char* scratch = g_scratchAddr[dev];
     cudaStream_t stream = static_cast<cudaStream_t>(cudaStream);
     // the scratch still holds whatever the previous call left: only the arrival counter has to start at zero
     e = cudaMemsetAsync(scratch, 0, kHeaderBytes, stream);

@@ -558,6 +558,10 @@ void reportStateToScreen(Qureg qureg, QuESTEnv env, int reportRank) {
         return;
     }
     std::vector<qreal> re(qureg.numAmpsPerChunk), im(qureg.numAmpsPerChunk);
+    // Every rank reads its shard back BEFORE the rank-by-rank printing: on a sharded register the copy may first have
+    // to restore the identity qubit layout, which is a collective exchange with partner ranks - it must not sit inside
+    // the one-rank-at-a-time loop below, whose host barrier the partner would already be waiting in.
+    qb200_copyAmpsToHost(qureg, 0, qureg.numAmpsPerChunk, re.data(), im.data());
     for (int rank = 0; rank < qureg.numChunks; ++rank) {
         if (qureg.chunkId == rank) {
             if (reportRank) {
@@ -567,7 +571,6 @@ void reportStateToScreen(Qureg qureg, QuESTEnv env, int reportRank) {
                 std::printf("Reporting state [\n");
                 std::printf("real, imag\n");
             }
-            qb200_copyAmpsToHost(qureg, 0, qureg.numAmpsPerChunk, re.data(), im.data());
             for (long long i = 0; i < qureg.numAmpsPerChunk; ++i)
                 std::printf(REAL_STRING_FORMAT ", " REAL_STRING_FORMAT "\n", re[i], im[i]);
             if (reportRank || rank == qureg.numChunks - 1) std::printf("]\n");

@@ -89,3 +89,23 @@ def check_golden_case(case, got, tol=1e-10, rtol=0):
 def seed(lib, keys):
     arr = (ctypes.c_ulong * len(keys))(*keys)
     lib.seedQuEST(arr, len(keys))
+
+
+def compare_with_cpu_register(product, q, cpu_q, chunk=1 << 24):
+    """Amplitude-by-amplitude comparison of a product register with a register of a CPU library that keeps its
+    state in host arrays (the reference build, the oracle), without materialising either as one complex array.
+    Returns (max |diff| / max |amp|, every double bit-identical)."""
+    n = int(q.numAmpsPerChunk)
+    re = np.empty(min(chunk, n), dtype=product.np_real)
+    im = np.empty_like(re)
+    want_re = np.ctypeslib.as_array(cpu_q.stateVec.real, shape=(n,))
+    want_im = np.ctypeslib.as_array(cpu_q.stateVec.imag, shape=(n,))
+    worst, biggest, same = 0.0, 0.0, True
+    for at in range(0, n, chunk):
+        m = min(chunk, n - at)
+        product.qb200_copyAmpsToHost(q, at, m, product.real_ptr(re), product.real_ptr(im))
+        for got, want in ((re[:m], want_re[at:at + m]), (im[:m], want_im[at:at + m])):
+            same = same and np.array_equal(got, want)
+            worst = max(worst, float(np.abs(got - want).max()))
+            biggest = max(biggest, float(np.abs(want).max()))
+    return (worst / biggest if biggest else worst), same

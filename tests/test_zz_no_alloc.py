@@ -57,6 +57,17 @@ def test_no_alloc_total_prob_matches_calcTotalProb_twice(product, product_env):
     np.testing.assert_allclose(second, product.calcTotalProb(q), rtol=1e-12)
     np.testing.assert_allclose(second, 1.0, rtol=1e-12)
     assert abs(first - second) > 1.0  # the two calls really saw different data
+
+    # third call on the lower half of the amplitudes only: that sum is P(qubit 21 = 0), which the rotateY on qubit 21
+    # above moved away from 1/2 - so this check fails if the gates issued before the call had not reached the
+    # amplitudes the raw pointers show (a register whose pointers were handed out runs its gates at once)
+    assert fn(re, im, n // 2, out.data_ptr(), stream) == 0
+    product.syncQuESTEnv(product_env)
+    torch.cuda.synchronize()
+    half = float(out.item())
+    expect = product.calcProbOfOutcome(q, 21, 0)
+    assert abs(expect - 0.5) > 0.05
+    np.testing.assert_allclose(half, expect, rtol=1e-12)
     product.destroyQureg(q, product_env)
 
 
