@@ -24,8 +24,9 @@ unsigned long long qb200_getLaunchCount(void);
 
 /* Gate fusion.  Gate calls may return before the GPU has run them (the reference GPU backend launches
  * asynchronously too, QuEST_gpu.cu:591); with fusion enabled (default; QUEST_B200_FUSE=0 disables) they are recorded
- * and executed at the next call that needs the amplitudes, consecutive gates on up to four distinct target qubits
- * sharing ONE pass over HBM.  Results are bit-identical to gate-at-a-time execution.
+ * and executed at the next call that needs the amplitudes, consecutive gates whose targets fall on up to eleven index
+ * bits (the four lowest included) sharing ONE pass over HBM through a shared-memory tile.  Results are bit-identical to
+ * gate-at-a-time execution.
  * qb200_setFusion(0) drains every queue and returns to one kernel per gate call; qb200_flush() drains the queues
  * without waiting for the GPU; qb200_getFusionStats reports how many fused passes ran and how many gates they held. */
 void qb200_setFusion(int enabled);
@@ -40,13 +41,6 @@ void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long*
  * reference exchanges whole shards with a blocking MPI_Sendrecv (QuEST_cpu_distributed.c:451-479). */
 void qb200_setOverlap(int enabled);
 unsigned long long qb200_getOverlappedExchangeCount(void);
-
-/* Sharded registers, opt-in (QUEST_B200_DISTRIBUTED=1 / qb200_setDistributed(1); off by default: validated on 2 GPUs
- * only, and faster than remapping only when a shard-selecting qubit is not reused by later groups): a run of gates whose fused qubits include g shard-selecting qubits runs as ONE pass over the 2^g GPUs
- * that differ in those qubits, each GPU processing its slab of the pairs over the peer mappings, instead of one slot
- * exchange per such qubit.  The counter reports how many such passes ran.  No reference counterpart. */
-void qb200_setDistributed(int mode);  /* 0 off, 1 always distributed, 2 make a qubit local first if the recorded queue uses it again */
-unsigned long long qb200_getDistributedPassCount(void);
 
 /* calcProbOfOutcome on state-vectors: the second query on an unchanged state computes P(qubit = 0) for EVERY qubit in
  * one pass over HBM; further queries are answered from that result until any call changes the state (e.g. the per-qubit
@@ -100,39 +94,6 @@ void qb200_getDevicePointers(Qureg qureg, void** real, void** imag);
 /* Copy n amplitudes of this rank's shard, from local index start, to host arrays.  Synchronises.
  * Stands in for direct reads of Qureg.stateVec (QuEST_common.c:174-177). */
 void qb200_copyAmpsToHost(Qureg qureg, long long int start, long long int n, qreal* reals, qreal* imags);
-
-/* Test hook (host logic only, makes no CUDA call): the plan rank `chunkId` of a register with 2^localBits amplitudes
- * per shard would execute for a one-target gate.  Stands in for the reference's per-gate local/distributed decision
- * (halfMatrixBlockFitsInChunk / chunkIsUpper / getChunkPairId, QuEST_cpu_distributed.c:231-365).  Layout of `out`
- * (18 words) is documented at the definition. */
-void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long long ctrlMask, int vec,
-                         unsigned long long* out);
-
-/* Test hook (host logic only, makes no CUDA call): the qubit-slot exchanges a sharded register would perform for a
- * sequence of dense gates, and the exchanges that restore the identity layout afterwards.  Layouts at the definition.
- * No counterpart in the reference, which exchanges whole shards for every gate on a shard-selecting qubit
- * (QuEST_cpu_distributed.c:451-479). */
-int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, const unsigned long long* masks,
-                     int* eventsOut, int* physOut, int* canonOut);
-
-/* Test hook (host logic only, makes no CUDA call): how the distributed mode cuts a queue of logical gates into groups and
- * which slot exchanges it places before each.  Layout at the definition. */
-int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* kinds, const int* targets, const int* targets2,
-                    const unsigned long long* masks, int lookahead, int* stepsOut);
-
-/* Test hook (host logic only, makes no CUDA call): the plan of a distributed fused pass for rank chunkId.  Layout at the
- * definition. */
-int qb200_debugDistributed(int localBits, int chunkId, const int* bits, int* out);
-
-/* Test hook (host logic only, makes no CUDA call): the slab bits chosen for pipelining a fused pass with a slot
- * exchange, and every k_swapPeer launch plan of that exchange.  Layouts at the definition. */
-int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int lowestAllowed, int vec, int localSlot,
-                     int* bitsOut, unsigned long long* swapOut);
-
-/* Test hook (host logic only, makes no CUDA call): how the fusion queue would group a gate list for a shard of
- * 2^localBits amplitudes.  kinds: 0 matrix, 1 hadamard, 2 swap, 3 pauliY, 4 phase, 5 flip.  Layouts at the definition. */
-int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* targets, const unsigned long long* masks,
-                    int* groupsOut, unsigned long long* descOut);
 
 /* Sum of |amplitude|^2 over numAmps amplitudes held in device arrays dReal/dImag, written as one double to device
  * memory at dSumOut, enqueued on cudaStream (0 = default stream).  Returns 0 on success, non-zero after printing the

@@ -23,6 +23,8 @@
 #include "qb_io.h"
 #include "qb_fuse.h"
 #include "qb_kernels.cuh"
+#include "qb_tile.cuh"
+#include "qb_debug.h"
 #include "quest_b200.h"
 #include "quest_internal.h"
 
@@ -75,8 +77,6 @@ struct Engine {
     bool contract = false;          // QUEST_B200_FMA / qb200_setArithmetic: fused pass may contract a*b+c into fma
     bool remap = true;              // QUEST_B200_REMAP: make shard-selecting qubits local by slot exchange
     unsigned long long slotSwaps = 0;
-    int distributed = 0;            // QUEST_B200_DISTRIBUTED: 1 gates on shard-selecting qubits run as distributed fused
-                                    // passes, 2 ... unless the recorded queue uses the qubit again (then it is made local)
     bool overlap = true;            // QUEST_B200_OVERLAP: pipeline a slot exchange with the fused pass before it
     int swapCtasPerSm = 1;          // QUEST_B200_SWAP_CTAS: footprint of a pipelined exchange
     int overlapMinBits = 24;        // ... for shards of at least 2^24 amplitudes (QUEST_B200_OVERLAP_MIN_BITS: tests)
@@ -86,7 +86,7 @@ struct Engine {
     cudaEvent_t commDone = nullptr; // communication stream: the whole exchange is
     void* pendingReg = nullptr;     // register whose last exchange the engine stream has not waited for yet ...
     SlabPlan pendingPlan{0, {0, 0, 0}};  // ... and how it was cut
-    unsigned long long overlapped = 0, distributedPasses = 0;
+    unsigned long long overlapped = 0;
     bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fusedEvents;
 } g;
@@ -103,7 +103,6 @@ struct QuregRec {
     u64 denseSinceFlush = 0;
     // calcProbOfOutcome: the second query on an unchanged state computes P(qubit = 0) for every qubit in one pass;
     // later queries are answered from here until the state changes (dirty()).
-    bool logicalQueue = false;  // distributed mode: the queue holds logical qubits and full control masks
     bool probValid = false;
     bool exposed = false;  // device pointers were handed out (qb200_getDevicePointers): the state can change unseen
     int probQueries = 0;
@@ -308,62 +307,64 @@ void runOpNow(const Qureg& q, const PendingOp& op) {
     }
 }
 
-#ifndef QB_FUSED_MINB
-#define QB_FUSED_MINB 4
-#endif
-FusedLaunch fl;  // ~8.5 KB: passed by value as the kernel parameter block
+TileLaunch tl;  // ~21 KB: passed by value as the kernel parameter block
 
-// Fill the parameter block for a run of recorded gates on the fused qubits `bits`; returns the kernel tier it needs.
-// Only bits below `localBits` contribute to element offsets: higher fused qubits select the shard (distributed pass).
-int prepareOps(const PendingOp* list, int count, const int* bits, int localBits) {
+// Fill the parameter block for one planned pass (qb_fuse.h); returns the kernel tier it needs.
+int preparePass(const std::vector<PendingOp>& ops, const TilePass& p) {
     int tier = 0;
-    for (int i = 0; i < count; ++i) {
-        const FusedGate fg = describe(list[i], bits);
-        fl.ctl[i] = GateCtl{opcodeOf(fg), fg.regMask};
-        fl.outerMask[i] = fg.outerMask;
-        std::memcpy(fl.c[i], fg.c, sizeof fg.c);
-        tier |= tierOf(fl.ctl[i].opcode);
+    tl.nTile = p.nTile;
+    tl.nLow = std::min(kTileLow, p.nTile);
+    tl.nSub = (int)p.subs.size();
+    tl.nGates = p.count;
+    for (int s = 0; s < tl.nSub; ++s) {
+        const TileSub& sg = p.subs[s];
+        TileSubDesc& d = tl.sub[s];
+        d.first = sg.first - p.first;
+        d.count = sg.count;
+        for (int j = 0; j < kSubBits; ++j) d.rb[j] = sg.rb[j];
+        for (int e = 0; e < kSubElems; ++e) {
+            unsigned int off = 0;
+            for (int j = 0; j < kSubBits; ++j)
+                if ((e >> j) & 1) off |= 1u << sg.rb[j];
+            d.place[e] = tilePlace(off);
+        }
+        for (int k = sg.first; k < sg.first + sg.count; ++k) {
+            const TileGate tg = describe(ops[k], p, sg);
+            const int g = k - p.first;
+            tl.ctl[g] = TileGateCtl{tg.opcode, tg.regMask, tg.tileMask, 0};
+            tl.outerMask[g] = tg.outerMask;
+            std::memcpy(tl.c[g], ops[k].c, sizeof ops[k].c);
+            tier |= tierOf(tg.opcode);
+        }
     }
-    fl.ctl[count] = GateCtl{0, 0};
-    for (int j = 0; j < kFuseBits; ++j) fl.pos[j] = bits[j];
-    for (int e = 0; e < (1 << kFuseBits); ++e) {
+    // amplitude offset of every row of the tile: tile-index bits [nLow, nTile) deposited at their index positions
+    for (unsigned int r = 0; r < (1u << (p.nTile - tl.nLow)); ++r) {
         u64 o = 0;
-        for (int j = 0; j < kFuseBits; ++j)
-            if (((e >> j) & 1) && bits[j] < localBits) o += 1ull << bits[j];
-        fl.offBytes[e] = o * sizeof(qreal);
+        for (int j = tl.nLow; j < p.nTile; ++j)
+            if ((r >> (j - tl.nLow)) & 1) o |= 1ull << p.tileBits[j];
+        tl.rowOff[r] = o;
     }
-    fl.nGates = count;
     return tier;
 }
 
-int prepareGroup(const std::vector<PendingOp>& ops, const FusedGroup& grp) {
-    return prepareOps(ops.data() + grp.first, grp.count, grp.bits, 64);
-}
-
-// One launch of k_fused over the whole shard (sp == nullptr) or over slab `slab` of it.
-void launchPrepared(QuregRec* r, int tier, const SlabPlan* sp, int slab) {
+// One launch of k_tile over the whole shard (sp == nullptr) or over slab `slab` of it.
+void launchPrepared(QuregRec* r, const TilePass& p, int tier, const SlabPlan* sp, int slab) {
     int n = 0;
-    for (int j = 0; j < kFuseBits; ++j) fl.ins[n++] = fl.pos[j];
+    for (int j = 0; j < p.nTile; ++j) tl.ins[n++] = p.tileBits[j];
     if (sp)
-        for (int j = 0; j < sp->nBits; ++j) fl.ins[n++] = sp->bits[j];
-    std::sort(fl.ins, fl.ins + n);
-    fl.nIns = n;
-    fl.slabMask = sp ? sp->valueMask(slab) : 0;
-    fl.nThreads = (u64)r->n >> n;
-    // 128-thread CTAs, 4 per SM (128 registers per thread): measured best of 64/128/256 threads x 2-6 CTAs
-    const unsigned int nb = (unsigned int)((fl.nThreads + 127) / 128);
-    if (tier == kTierAllNoise)
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAllNoise><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+        for (int j = 0; j < sp->nBits; ++j) tl.ins[n++] = sp->bits[j];
+    std::sort(tl.ins, tl.ins + n);
+    tl.nIns = n;
+    tl.slabMask = sp ? sp->valueMask(slab) : 0;
+    const unsigned int nb = (unsigned int)((u64)r->n >> n);
+    if (tier == kTierNoise && g.contract)
+        k_tile<kTierNoise, true><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
     else if (tier == kTierNoise)
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierNoise><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
-    else if (tier == kTierAll && g.contract)
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAll, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
-    else if (tier == kTierAll)
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAll><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+        k_tile<kTierNoise, false><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
     else if (g.contract)
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierCore, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+        k_tile<kTierGates, true><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
     else
-        k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierCore><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
+        k_tile<kTierGates, false><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
     launched();
 }
 
@@ -382,18 +383,18 @@ struct FusedTimer {  // qb200_setKernelTiming: one event pair per fused pass (a 
     }
 };
 
-void runGroup(const Qureg& q, const std::vector<PendingOp>& ops, const FusedGroup& grp) {
-    if (grp.count == 1) {
-        runOpNow(q, ops[grp.first]);
+void runPass(const Qureg& q, const std::vector<PendingOp>& ops, const TilePass& p) {
+    if (p.count == 1) {
+        runOpNow(q, ops[p.first]);
         return;
     }
-    const int tier = prepareGroup(ops, grp);
+    const int tier = preparePass(ops, p);
     FusedTimer t;
     t.start();
-    launchPrepared(rec(q), tier, nullptr, 0);
+    launchPrepared(rec(q), p, tier, nullptr, 0);
     t.stop();
     ++g.fusedLaunches;
-    g.fusedGates += grp.count;
+    g.fusedGates += p.count;
 }
 
 // A pipelined exchange (flushThenExchange) returns while its last slabs are still moving; the engine stream catches
@@ -409,17 +410,17 @@ inline u64 bitsOf(const SlabPlan& sp) {
     for (int j = 0; j < sp.nBits; ++j) m |= 1ull << sp.bits[j];
     return m;
 }
-inline u64 bitsOf(const FusedGroup& grp) {
+inline u64 bitsOf(const TilePass& p) {
     u64 m = 0;
-    for (int j = 0; j < kFuseBits; ++j) m |= 1ull << grp.bits[j];
+    for (int j = 0; j < p.nTile; ++j) m |= 1ull << p.tileBits[j];
     return m;
 }
 
-// One fused group cut along `sp`: slab s starts once `waitFor[s]` has happened (the exchange before it delivered that
+// One fused pass cut along `sp`: slab s starts once `waitFor[s]` has happened (the exchange before it delivered that
 // slab) and `record[s]` marks its end (the exchange after it may take that slab).
-void runGroupInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const FusedGroup& grp, const SlabPlan& sp,
-                     const cudaEvent_t* waitFor, const cudaEvent_t* record) {
-    const int tier = prepareGroup(ops, grp);
+void runPassInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const TilePass& p, const SlabPlan& sp,
+                    const cudaEvent_t* waitFor, const cudaEvent_t* record) {
+    const int tier = preparePass(ops, p);
     FusedTimer t;
     bool started = false;
     for (int s = 0; s < (1 << sp.nBits); ++s) {
@@ -428,134 +429,19 @@ void runGroupInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const Fu
             t.start();
             started = true;
         }
-        launchPrepared(rec(q), tier, &sp, s);
+        launchPrepared(rec(q), p, tier, &sp, s);
         if (record) CUDA_OK(cudaEventRecord(record[s], g.stream));
     }
     t.stop();
     ++g.fusedLaunches;
-    g.fusedGates += grp.count;
-}
-
-// ---- distributed mode (QUEST_B200_DISTRIBUTED=1, opt-in) ----------------------------------------------------------
-// Gates are recorded with their full control masks and with targets on shard-selecting qubits left where they are, so
-// every rank holds the same queue and forms the same groups.  A group whose fused qubits are all local runs as usual
-// (controls on shard-selecting qubits resolved against this rank now).  A group with g fused shard-selecting qubits
-// runs as ONE pass over the 2^g GPUs that differ in those qubits: element e of the register block lives in shard
-// tab[e >> nLocalFused], each GPU of the group processes the slab of outer indices that carries its own group index,
-// controls on the fused shard-selecting qubits are ordinary register-mask bits.  NVLink carries (1 - 2^-g) of a shard
-// each way for the whole group instead of half a shard per exchanged qubit (and per exchange back).
-// One group of the distributed mode, already in bit positions: `list` holds its gates with full control masks.
-void runDistributedGroup(const Qureg& q, const std::vector<PendingOp>& list, const FusedGroup& grp) {
-    QuregRec* r = rec(q);
-    const u64 localMask = (1ull << r->localBits) - 1ull;
-    const u64 rankBits = (u64)q.chunkId << r->localBits;  // this rank's values of the shard-selecting bits
-    u64 fusedShardBits = 0;
-    int nLocalFused = 0;
-    for (int j = 0; j < kFuseBits; ++j) {
-        if (grp.bits[j] >= r->localBits) fusedShardBits |= 1ull << grp.bits[j];
-        else ++nLocalFused;
-    }
-    // controls on shard-selecting qubits outside the block: the same for every GPU of the group
-    std::vector<PendingOp> sel;
-    for (int i = 0; i < grp.count; ++i) {
-        PendingOp op = list[grp.first + i];
-        const u64 outside = op.mask & ~localMask & ~fusedShardBits;
-        if ((rankBits & outside) != outside) continue;
-        op.mask &= ~outside;
-        sel.push_back(op);
-    }
-    if (sel.empty()) return;
-    if (!fusedShardBits) {
-        if (sel.size() == 1) {
-            runOpNow(q, sel[0]);
-            return;
-        }
-        const int tier = prepareOps(sel.data(), (int)sel.size(), grp.bits, 64);
-        FusedTimer t;
-        t.start();
-        launchPrepared(r, tier, nullptr, 0);
-        t.stop();
-        ++g.fusedLaunches;
-        g.fusedGates += sel.size();
-        return;
-    }
-    // the group of GPUs, this rank's index in it, and the slab it processes
-    DistPlan dp;
-    if (!planDistributed(r->localBits, q.chunkId, grp.bits, kFuseBits, dp))
-        comm::unsupported("a distributed pass on a shard too small to be divided among its GPUs");
-    const int nShard = dp.nShard, me = dp.me;
-    const SlabPlan& sp = dp.slabs;
-    const int* members = dp.members;
-    prepareOps(sel.data(), (int)sel.size(), grp.bits, r->localBits);
-    fl.nLocalFused = nLocalFused;
-    for (int v = 0; v < (1 << nShard); ++v) {
-        const comm::Partner p = comm::shardOf(q, members[v]);
-        fl.tabRe[v] = p.re;
-        fl.tabIm[v] = p.im;
-    }
-    int n = 0;
-    for (int j = 0; j < nLocalFused; ++j) fl.ins[n++] = grp.bits[j];
-    for (int j = 0; j < sp.nBits; ++j) fl.ins[n++] = sp.bits[j];
-    std::sort(fl.ins, fl.ins + n);
-    fl.nIns = n;
-    fl.slabMask = sp.valueMask(me);
-    fl.nThreads = (u64)r->n >> n;
-    const unsigned int nb = (unsigned int)((fl.nThreads + 127) / 128);
-    for (int v = 0; v < (1 << nShard); ++v)  // everything the others enqueued before this pass has finished
-        if (members[v] != q.chunkId) comm::pairBarrier(members[v], g.stream);
-    FusedTimer t;
-    t.start();
-    k_fused<kFuseBits, 128, QB_FUSED_MINB, kTierAllNoise, false, true><<<nb, 128, 0, g.stream>>>(r->re, r->im, fl);
-    launched();
-    t.stop();
-    for (int v = 0; v < (1 << nShard); ++v)  // the others' writes into this shard have landed
-        if (members[v] != q.chunkId) comm::pairBarrier(members[v], g.stream);
-    ++g.fusedLaunches;
-    ++g.distributedPasses;
-    g.fusedGates += sel.size();
+    g.fusedGates += p.count;
 }
 
 void exchangeSlots(const Qureg& q, SlotSwap sw);
 
-// The queue of the distributed mode holds LOGICAL qubits and full control masks - the same on every rank.  It is walked
-// in program order, one group (a run of gates on at most kFuseBits dense qubits) at a time.  For every dense qubit of
-// the group that currently sits in a shard-selecting slot there are two ways to serve it: leave it there and run the
-// group as a distributed pass, or make it local first (a slot exchange, qb_plan.h).  g.distributed == 2 decides by
-// looking ahead in the recorded queue: a qubit that later groups use again is made local, a qubit this group is the
-// last recorded user of stays where it is.  g.distributed == 1 never exchanges.
-void flushDistributed(const Qureg& q) {
-    QuregRec* r = rec(q);
-    r->callsSinceFlush = 0;
-    r->denseSinceFlush = 0;
-    r->logicalQueue = false;
-    if (r->queue.empty()) return;
-    std::vector<PendingOp> ops;
-    ops.swap(r->queue);
-    // decisions first (qb::planWalk, host bookkeeping on a copy of the layout), then the same steps on the GPUs
-    for (const WalkStep& st : planWalk(r->map, ops, g.distributed == 2 && g.remap)) {
-        for (int k = 0; k < st.nSwaps; ++k) exchangeSlots(q, st.swaps[k]);
-        for (u64 m = st.dense; m; m &= m - 1) r->map.touch(__builtin_ctzll(m));
-        // the group in bit positions under the layout that now holds
-        std::vector<PendingOp> list(ops.begin() + st.first, ops.begin() + st.first + st.count);
-        for (PendingOp& op : list) {
-            if (!isDiagonal(op.kind)) {
-                op.target = r->map.phys[op.target];
-                if (op.target2 >= 0) op.target2 = r->map.phys[op.target2];
-            }
-            op.mask = r->map.physMask(op.mask);
-        }
-        for (const FusedGroup& grp : groupOps(list, r->localBits)) runDistributedGroup(q, list, grp);
-    }
-}
-
 // Execute everything recorded for this register: single gates through their own kernel, runs of gates through
-// k_fused (one HBM pass per group, qb_fuse.h).
+// k_tile (one HBM pass per planned pass, qb_fuse.h).
 void flush(const Qureg& q) {
-    if (rec(q)->logicalQueue) {
-        if (g.pendingReg == rec(q)) settle();
-        flushDistributed(q);
-        return;
-    }
     QuregRec* r = rec(q);
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
@@ -566,19 +452,19 @@ void flush(const Qureg& q) {
     }
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
-    const std::vector<FusedGroup> groups = groupOps(ops, r->localBits, pending ? bitsOf(g.pendingPlan) : 0);
+    const std::vector<TilePass> passes = planPasses(ops, r->localBits, pending ? bitsOf(g.pendingPlan) : 0);
     size_t first = 0;
     if (pending) {
         // the first pass follows the exchange slab by slab if it can be cut the same way
-        if (groups[0].count > 1 && !(bitsOf(groups[0]) & bitsOf(g.pendingPlan))) {
-            runGroupInSlabs(q, ops, groups[0], g.pendingPlan, g.xDone, nullptr);
+        if (passes[0].count > 1 && !(bitsOf(passes[0]) & bitsOf(g.pendingPlan))) {
+            runPassInSlabs(q, ops, passes[0], g.pendingPlan, g.xDone, nullptr);
             g.pendingReg = nullptr;  // the last slab waited for the last piece of the exchange
             first = 1;
         } else {
             settle();
         }
     }
-    for (size_t i = first; i < groups.size(); ++i) runGroup(q, ops, groups[i]);
+    for (size_t i = first; i < passes.size(); ++i) runPass(q, ops, passes[i]);
 }
 
 void flushAll() {
@@ -642,7 +528,7 @@ void flushThenExchange(const Qureg& q, SlotSwap sw) {
     // Both GPUs of the pair must cut along the same bits and issue the same handshakes, whatever their own queues hold:
     // everything below that shapes the protocol derives from rank-independent state.
     const u64 busy = r->denseSinceFlush | (1ull << sw.localSlot);
-    const int spare = r->localBits - __builtin_popcountll(busy & ((1ull << r->localBits) - 1)) - kFuseBits;
+    const int spare = r->localBits - __builtin_popcountll((busy | ((1ull << kTileLow) - 1ull)) & ((1ull << r->localBits) - 1)) - kTileBits;
     SlabPlan sp{0, {0, 0, 0}};
     const bool eligible = g.overlap && g.comm && r->callsSinceFlush > 0 && r->localBits >= g.overlapMinBits;
     bool chained = false;  // the previous exchange of this register is still in flight and is cut the same way
@@ -662,7 +548,7 @@ void flushThenExchange(const Qureg& q, SlotSwap sw) {
     ops.swap(r->queue);
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
-    const std::vector<FusedGroup> groups = groupOps(ops, r->localBits, bitsOf(sp));
+    const std::vector<TilePass> groups = planPasses(ops, r->localBits, bitsOf(sp));
     const int nSlabs = 1 << sp.nBits;
     bool signalled = false;  // the last pass recorded slabEv[] itself
     for (size_t i = 0; i < groups.size(); ++i) {
@@ -671,10 +557,10 @@ void flushThenExchange(const Qureg& q, SlotSwap sw) {
         const bool follow = chained && isFirst && fusedPass;  // dense targets never sit on slab bits: see `busy`
         if (chained && isFirst && !follow) settle();
         if (fusedPass && (follow || isLast)) {
-            runGroupInSlabs(q, ops, groups[i], sp, follow ? g.xDone : nullptr, isLast ? g.slabEv : nullptr);
+            runPassInSlabs(q, ops, groups[i], sp, follow ? g.xDone : nullptr, isLast ? g.slabEv : nullptr);
             signalled = signalled || isLast;
         } else {
-            runGroup(q, ops, groups[i]);
+            runPass(q, ops, groups[i]);
         }
     }
     // (with an empty queue a chained exchange simply queues up behind the previous one on the communication stream)
@@ -720,7 +606,6 @@ inline QuregRec* fresh(const Qureg& q) {
     if (g.pendingReg == r) settle();
     dirty(r);
     r->queue.clear();
-    r->logicalQueue = false;
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
     r->map.reset(r->map.nQubits, r->localBits);
@@ -732,15 +617,6 @@ inline QuregRec* fresh(const Qureg& q) {
 void submit(const Qureg& q, PendingOp op) {
     QuregRec* r = rec(q);
     dirty(r);
-    if (g.distributed && g.world > 1 && g.fuse && r->localBits >= kFuseBits + 3) {
-        // distributed mode: the gate is recorded as it came, in logical qubits with its full control mask; nothing is
-        // decided per rank - and no layout is fixed - before the queue is walked (flushDistributed)
-        if (r->callsSinceFlush >= kQueueCap) flush(q);
-        ++r->callsSinceFlush;
-        r->logicalQueue = true;
-        r->queue.push_back(op);
-        return;
-    }
     // logical qubits -> current bit positions; a dense target living in a shard-selecting slot is first made local
     if (g.world > 1) {
         if (!isDiagonal(op.kind)) {
@@ -763,7 +639,7 @@ void submit(const Qureg& q, PendingOp op) {
     }
     // registers whose device pointers were handed out run every gate at once: whoever holds the raw pointers sees the
     // amplitudes the API calls so far produce (stream-ordered), and nothing queued can overwrite what they write
-    const bool recording = g.fuse && !r->exposed && r->localBits >= kFuseBits;
+    const bool recording = g.fuse && !r->exposed && r->localBits >= kSubBits;
     if (recording) {  // before any rank-dependent decision: every rank counts every gate call
         if (r->callsSinceFlush >= kQueueCap) flush(q);
         ++r->callsSinceFlush;
@@ -1004,7 +880,6 @@ QuESTEnv createQuESTEnv(void) {
     if (g.world > 1) {
         comm::init(ln, g.device, g.stream);
         if (const char* s = std::getenv("QUEST_B200_OVERLAP")) g.overlap = std::atoi(s) != 0;
-        if (const char* s = std::getenv("QUEST_B200_DISTRIBUTED")) g.distributed = std::max(0, std::min(2, std::atoi(s)));
         if (const char* s = std::getenv("QUEST_B200_SWAP_CTAS")) g.swapCtasPerSm = std::max(1, std::min(8, std::atoi(s)));
         if (const char* s = std::getenv("QUEST_B200_OVERLAP_MIN_BITS")) g.overlapMinBits = std::max(8, std::atoi(s));
         int lowPrio = 0, highPrio = 0;
@@ -1168,15 +1043,6 @@ void qb200_setOverlap(int enabled) {
     g.overlap = enabled != 0;
 }
 unsigned long long qb200_getOverlappedExchangeCount(void) { return g.overlapped; }
-
-// Pending gates are executed under the old setting first (and the identity layout is restored: the two modes record
-// differently).
-void qb200_setDistributed(int enabled) {
-    requireEngine();
-    qb200_setRemap(g.remap ? 1 : 0);
-    g.distributed = std::max(0, std::min(2, enabled));
-}
-unsigned long long qb200_getDistributedPassCount(void) { return g.distributedPasses; }
 
 unsigned long long qb200_getPipelinedTransferCount(void) { return io::pipelinedTransfers(); }
 
@@ -1689,13 +1555,14 @@ int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int l
     return sp.nBits;
 }
 
-// Host walk of a logical gate queue (qb::planWalk), exposed for CPU-only tests (no CUDA call).  Gates: kind, logical
-// target, second target (-1 if none), logical control mask.  stepsOut: per step first, count, nSwaps, then up to 4 pairs
-// (globalSlot, localSlot) = 11 ints.  Returns the number of steps.
-int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* kinds, const int* targets, const int* targets2,
-                    const unsigned long long* masks, int lookahead, int* stepsOut) {
-    QubitMap m;
-    m.reset(nQubits, localBits);
+// Host pass-planning logic of the fusion queue, exposed for CPU-only tests (no CUDA call): plans the given gate list
+// exactly as flush() would for a shard of 2^localBits amplitudes.  Gates: kind (qb_fuse.h FusedKind), target, second target
+// (-1 if none), mask.  passesOut, per pass: first, count, nTile, nSub, tileBits[kTileBits] (= 4 + 11 ints); subsOut, per
+// sub-group in pass order: pass index, first, count, rb[3] (6 ints); descOut, per gate: opcode, regMask, tileMask, outerMask
+// (4 words).  Returns the number of passes; *nSubsOut receives the number of sub-groups.
+int qb200_debugTilePlan(int localBits, int nOps, const int* kinds, const int* targets, const int* targets2,
+                        const unsigned long long* masks, int* passesOut, int* subsOut, unsigned long long* descOut,
+                        int* nSubsOut) {
     std::vector<PendingOp> ops(nOps);
     for (int i = 0; i < nOps; ++i) {
         std::memset(&ops[i], 0, sizeof(PendingOp));
@@ -1704,57 +1571,26 @@ int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* kinds, cons
         ops[i].target2 = targets2[i];
         ops[i].mask = masks[i];
     }
-    const std::vector<WalkStep> steps = planWalk(m, ops, lookahead != 0);
-    for (size_t k = 0; k < steps.size(); ++k) {
-        int* o = stepsOut + 11 * k;
-        o[0] = steps[k].first; o[1] = steps[k].count; o[2] = steps[k].nSwaps;
-        for (int j = 0; j < 4; ++j) {
-            o[3 + 2 * j] = j < steps[k].nSwaps ? steps[k].swaps[j].globalSlot : -1;
-            o[4 + 2 * j] = j < steps[k].nSwaps ? steps[k].swaps[j].localSlot : -1;
+    const std::vector<TilePass> passes = planPasses(ops, localBits);
+    int nSubs = 0;
+    for (size_t pi = 0; pi < passes.size(); ++pi) {
+        const TilePass& p = passes[pi];
+        int* o = passesOut + (4 + kTileBits) * pi;
+        o[0] = p.first; o[1] = p.count; o[2] = p.nTile; o[3] = (int)p.subs.size();
+        for (int j = 0; j < kTileBits; ++j) o[4 + j] = j < p.nTile ? p.tileBits[j] : -1;
+        for (const TileSub& sg : p.subs) {
+            int* so = subsOut + 6 * nSubs++;
+            so[0] = (int)pi; so[1] = sg.first; so[2] = sg.count;
+            for (int j = 0; j < kSubBits; ++j) so[3 + j] = sg.rb[j];
+            for (int k = sg.first; k < sg.first + sg.count; ++k) {
+                const TileGate tg = describe(ops[k], p, sg);
+                unsigned long long* d = descOut + 4 * k;
+                d[0] = (unsigned long long)tg.opcode; d[1] = tg.regMask; d[2] = tg.tileMask; d[3] = tg.outerMask;
+            }
         }
     }
-    return (int)steps.size();
-}
-
-// Host logic of the distributed fused pass (qb::planDistributed), exposed for CPU-only tests (no CUDA call).
-// out: nLocalFused, nShard, me, nSlabBits, slabBits[3], members[8]; returns 0 if the group cannot be planned.
-int qb200_debugDistributed(int localBits, int chunkId, const int* bits, int* out) {
-    DistPlan dp;
-    if (!planDistributed(localBits, chunkId, bits, kFuseBits, dp)) return 0;
-    out[0] = dp.nLocalFused; out[1] = dp.nShard; out[2] = dp.me; out[3] = dp.slabs.nBits;
-    for (int j = 0; j < 3; ++j) out[4 + j] = j < dp.slabs.nBits ? dp.slabs.bits[j] : -1;
-    for (int v = 0; v < 8; ++v) out[7 + v] = v < (1 << dp.nShard) ? dp.members[v] : -1;
-    return 1;
-}
-
-// Host grouping logic of the fusion queue, exposed for CPU-only tests (no CUDA call): groups the given gate list
-// exactly as flush() would for a shard of 2^localBits amplitudes.  groupsOut: 7 ints per group (first, count,
-// bits[4], nDenseBits); descOut: 4 words per gate (kind, pos, regMask, outerMask).  Returns the number of groups.
-int qb200_debugFuse(int localBits, int nOps, const int* kinds, const int* targets, const unsigned long long* masks,
-                    int* groupsOut, unsigned long long* descOut) {
-    std::vector<PendingOp> ops(nOps);
-    for (int i = 0; i < nOps; ++i) {
-        std::memset(&ops[i], 0, sizeof(PendingOp));
-        ops[i].kind = kinds[i];
-        ops[i].target = targets[i];
-        ops[i].target2 = -1;
-        ops[i].mask = masks[i];
-    }
-    const std::vector<FusedGroup> groups = groupOps(ops, localBits);
-    for (size_t gi = 0; gi < groups.size(); ++gi) {
-        const FusedGroup& grp = groups[gi];
-        int* o = groupsOut + 7 * gi;
-        o[0] = grp.first; o[1] = grp.count; o[6] = grp.nDenseBits;
-        for (int j = 0; j < kFuseBits; ++j) o[2 + j] = grp.bits[j];
-        for (int i = 0; i < grp.count; ++i) {
-            const FusedGate fg = describe(ops[grp.first + i], grp.bits);
-            unsigned long long* d = descOut + 4 * (grp.first + i);
-            // kind | what the kernel jumps on | the smallest kernel tier that understands it
-            d[0] = (unsigned long long)fg.kind | ((unsigned long long)opcodeOf(fg) << 8) | ((unsigned long long)tierOf(opcodeOf(fg)) << 16);
-            d[1] = fg.pos; d[2] = fg.regMask; d[3] = fg.outerMask;
-        }
-    }
-    return (int)groups.size();
+    *nSubsOut = nSubs;
+    return (int)passes.size();
 }
 
 }  // extern "C"

@@ -1,14 +1,24 @@
-// quest-b200 gate fusion: host-side queue and grouping (CUDA-free, unit-tested on CPU through qb200_debugFuse).
+// quest-b200 gate fusion: host-side queue and pass planning (CUDA-free, unit-tested on CPU through qb200_debugTilePlan).
 //
 // Every gate of the QuEST API is one pass over HBM (16 GiB read + 16 GiB written at 30 qubits) however little
 // arithmetic it does.  The API lets a gate call return before the GPU has run it (the reference GPU backend
 // launches asynchronously, QuEST_gpu.cu:591), so gate calls are recorded in a per-register queue and executed at
 // the next call that needs the amplitudes (any value-returning call, a copy, syncQuESTEnv, a shard-crossing gate).
-// At that point consecutive gates are grouped: a group is a run of gates, in program order, whose dense (non-
-// diagonal) targets fall on at most kFuseBits distinct qubits; diagonal gates and control qubits are unrestricted.
-// One launch of k_fused then loads 2^kFuseBits amplitudes per thread - the sub-block spanned by those qubits -
-// applies the whole run in registers, gate after gate in the original order with the original per-gate
-// arithmetic, and writes the block back: one HBM pass for the whole group, bit-identical results.
+// At that point the queue is cut, in program order, into PASSES and each pass into SUB-GROUPS:
+//
+//   pass       a run of gates whose dense (non-diagonal) targets, together with the lowest kTileLow index bits, fall
+//              on at most kTileBits distinct index bits - the TILE BITS.  One launch of k_tile (qb_tile.cuh) serves
+//              the pass: every CTA stages the 2^kTileBits amplitudes that differ only in the tile bits in shared
+//              memory (rows of 2^kTileLow contiguous amplitudes, so HBM sees whole 128-byte lines), runs all gates
+//              of the pass on them, and writes them back - ONE read and ONE write of the state for the whole pass.
+//   sub-group  a run of gates inside a pass whose dense targets fall on at most kSubBits tile bits.  Each thread
+//              loads the 2^kSubBits amplitudes spanned by those bits from shared memory into registers, applies the
+//              sub-group's gates in program order with the per-gate arithmetic of the single-gate kernels, and
+//              stores them back; the next sub-group re-blocks the tile along other bits.
+//
+// Diagonal gates and control qubits never restrict a pass: a selecting bit outside the tile is a per-CTA condition,
+// one inside the tile a per-thread condition, one among the sub-group's register bits a per-element condition.
+// Results are bit-identical to gate-at-a-time execution.
 #pragma once
 
 #include <algorithm>
@@ -20,11 +30,15 @@
 
 namespace qb {
 
-#ifndef QB_FUSE_BITS
-#define QB_FUSE_BITS 4
+#ifndef QB_TILE_BITS
+#define QB_TILE_BITS 11
 #endif
-constexpr int kFuseBits = QB_FUSE_BITS;  // qubits resolved in registers per launch (2^kFuseBits amplitudes per thread)
-constexpr int kMaxFusedGates = 96;  // gates per launch: descriptors travel as kernel parameters (constant bank)
+constexpr int kTileBits = QB_TILE_BITS;  // amplitudes staged per CTA: 2^kTileBits (2 x 16 KiB of shared memory in double)
+constexpr int kTileLow = 4;              // the lowest index bits are always tile bits: 2^4 doubles = one 128-byte line
+constexpr int kSubBits = 3;              // qubits resolved in registers per sub-group (2^3 amplitudes per thread)
+constexpr int kMaxTileGates = 192;       // gates per pass: descriptors travel as kernel parameters (constant bank)
+constexpr int kMaxTileSubs = 64;         // sub-groups per pass
+constexpr int kMaxSlabBits = 3;          // a launch may be confined to the amplitudes with given values on up to 3 bits
 
 enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, kFPhase = 4, kFFlip = 5,
                        // one-qubit noise channels of a density matrix: act on the 2x2 block structure spanned by the
@@ -48,199 +62,190 @@ struct PendingOp {
                                    // coherences, c[1]=level, c[2]=1-level (see k_noise1)
 };
 
-// What the kernel reads per gate.
-struct FusedGate {
-    int kind;
-    int pos;                       // dense: which of the kFuseBits register bits is the target (noise: the lower one)
-    unsigned int regMask;          // control/selecting bits that are register bits (bit j = j-th fused qubit)
-    int pos2;                      // noise: register bit of the higher of the two targets
-    unsigned long long outerMask;  // control/selecting bits outside the fused qubits (amplitude-index space)
-    qreal c[8];
-};
+inline unsigned long long denseBitsOf(const PendingOp& op) {
+    if (isDiagonal(op.kind)) return 0;
+    unsigned long long m = 1ull << op.target;
+    if (op.target2 >= 0) m |= 1ull << op.target2;
+    return m;
+}
 
-struct FusedGroup {
+struct TileSub {
     int first, count;              // ops [first, first+count) of the queue
-    int bits[kFuseBits];           // fused qubits, ascending; padded with unused qubits when the group needs fewer
-    int nDenseBits;                // how many of them are targets of dense gates
+    int rb[kSubBits];              // register bits, ascending, as positions in TILE-INDEX space (bit j of a tile index
+                                   // is amplitude-index bit tileBits[j]); -1 = unused (registers of fewer than 3 qubits)
 };
 
-// Greedy, order-preserving grouping.
-// `avoidMask`: bits that must not be used to pad a group (they are held out for slab pipelining, qb_plan.h); they
-// never hold a dense target of these ops.
-inline std::vector<FusedGroup> groupOps(const std::vector<PendingOp>& ops, int localBits, unsigned long long avoidMask = 0) {
-    std::vector<FusedGroup> out;
+struct TilePass {
+    int first, count;              // ops [first, first+count) of the queue
+    int nTile;                     // number of tile bits = min(kTileBits, localBits)
+    int tileBits[kTileBits];       // amplitude-index bit positions, ascending
+    unsigned long long denseMask;  // amplitude-index bits that are dense targets of the pass
+    std::vector<TileSub> subs;
+};
+
+// Greedy, order-preserving planning.
+// `avoidMask`: amplitude-index bits that must not become tile bits by padding (they are held out for slab pipelining,
+// qb_plan.h); the caller guarantees they hold no dense target of these ops and none of the kTileLow lowest bits.
+inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int localBits, unsigned long long avoidMask = 0) {
+    std::vector<TilePass> out;
     const int n = (int)ops.size();
+    const int T = std::min(kTileBits, localBits);
+    const int R = std::min(kSubBits, T);
+    const unsigned long long lowMask = (1ull << std::min(kTileLow, T)) - 1ull;
     int i = 0;
     while (i < n) {
-        FusedGroup g;
-        g.first = i;
-        g.count = 0;
-        g.nDenseBits = 0;
-        unsigned long long chosen = 0;
-        while (i < n && g.count < kMaxFusedGates) {
-            const PendingOp& op = ops[i];
-            if (!isDiagonal(op.kind)) {
-                unsigned long long need = 1ull << op.target;
-                if (op.target2 >= 0) need |= 1ull << op.target2;
-                need &= ~chosen;
-                const int extra = __builtin_popcountll(need);
-                if (g.nDenseBits + extra > kFuseBits) break;
-                chosen |= need;
-                g.nDenseBits += extra;
+        TilePass p;
+        p.first = i;
+        p.count = 0;
+        p.nTile = T;
+        p.denseMask = 0;
+        unsigned long long subDense = 0;
+        TileSub cur{i, 0, {0, 0, 0}};
+        std::vector<unsigned long long> subMasks;  // dense bits of each closed sub-group (amplitude-index space)
+        while (i < n && p.count < kMaxTileGates) {
+            const unsigned long long need = denseBitsOf(ops[i]);
+            if (__builtin_popcountll(p.denseMask | need | lowMask) > T) break;
+            if (__builtin_popcountll(subDense | need) > R) {  // the gate opens a new sub-group
+                if ((int)p.subs.size() + 1 == kMaxTileSubs) break;
+                p.subs.push_back(cur);
+                subMasks.push_back(subDense);
+                cur = TileSub{i, 0, {0, 0, 0}};
+                subDense = 0;
             }
-            ++g.count;
+            subDense |= need;
+            p.denseMask |= need;
+            ++cur.count;
+            ++p.count;
             ++i;
         }
-        // pad with qubits the group's gates mention (keeps their predicates in registers), then with the
-        // highest unused qubits (keeps the remaining index bits low => consecutive threads, consecutive amplitudes)
-        int have = g.nDenseBits;
-        for (int k = g.first; k < g.first + g.count && have < kFuseBits; ++k) {
-            unsigned long long m = ops[k].mask & ~chosen;
-            while (m && have < kFuseBits) {
-                const int b = __builtin_ctzll(m);
-                m &= m - 1;
-                if (b < localBits && !((avoidMask >> b) & 1)) {
+        p.subs.push_back(cur);
+        subMasks.push_back(subDense);
+        // tile bits: dense targets + the low run, padded with the lowest free bits (longer contiguous rows in HBM)
+        unsigned long long chosen = p.denseMask | lowMask;
+        int have = __builtin_popcountll(chosen);
+        for (int round = 0; round < 2 && have < T; ++round)
+            for (int b = 0; b < localBits && have < T; ++b)
+                if (!((chosen >> b) & 1) && (round == 1 || !((avoidMask >> b) & 1))) {
                     chosen |= 1ull << b;
                     ++have;
                 }
+        int j = 0;
+        int tilePosOf[64];
+        for (int b = 0; b < 64; ++b) {
+            tilePosOf[b] = -1;
+            if (j < T && ((chosen >> b) & 1)) {
+                tilePosOf[b] = j;
+                p.tileBits[j++] = b;
             }
         }
-        for (int b = localBits - 1; b >= 0 && have < kFuseBits; --b)
-            if (!((chosen >> b) & 1) && !((avoidMask >> b) & 1)) {
-                chosen |= 1ull << b;
-                ++have;
-            }
-        int j = 0;
-        for (int b = 0; b < 64 && j < kFuseBits; ++b)
-            if ((chosen >> b) & 1) g.bits[j++] = b;
-        out.push_back(g);
+        // register bits of every sub-group: its dense targets, then tile bits its gates use as controls / selecting bits
+        // (a per-element condition instead of a per-thread one), then the highest free tile bits (keeps the threads of
+        // a warp on the lowest tile-index bits: neighbouring shared-memory words)
+        for (size_t s = 0; s < p.subs.size(); ++s) {
+            TileSub& sg = p.subs[s];
+            unsigned int reg = 0;
+            for (unsigned long long m = subMasks[s]; m; m &= m - 1) reg |= 1u << tilePosOf[__builtin_ctzll(m)];
+            int nreg = __builtin_popcount(reg);
+            for (int k = sg.first; k < sg.first + sg.count && nreg < R; ++k)
+                for (unsigned long long m = ops[k].mask; m && nreg < R; m &= m - 1) {
+                    const int tp = tilePosOf[__builtin_ctzll(m)];
+                    if (tp >= 0 && !((reg >> tp) & 1)) {
+                        reg |= 1u << tp;
+                        ++nreg;
+                    }
+                }
+            for (int tp = T - 1; tp >= 0 && nreg < R; --tp)
+                if (!((reg >> tp) & 1)) {
+                    reg |= 1u << tp;
+                    ++nreg;
+                }
+            int q = 0;
+            for (int tp = 0; tp < T; ++tp)
+                if ((reg >> tp) & 1) sg.rb[q++] = tp;
+            for (; q < kSubBits; ++q) sg.rb[q] = -1;
+        }
+        out.push_back(p);
     }
     return out;
 }
 
-// Translate one queued op into the kernel's descriptor for a group with fused qubits `bits`.
-inline FusedGate describe(const PendingOp& op, const int* bits) {
-    FusedGate fg;
-    std::memset(&fg, 0, sizeof fg);
-    fg.kind = op.kind;
-    fg.pos = 0;
-    fg.pos2 = 0;
-    unsigned long long outer = op.mask;
-    const int lowT = op.target2 >= 0 && op.target2 < op.target ? op.target2 : op.target;
-    const int highT = op.target2 >= 0 ? (op.target2 < op.target ? op.target : op.target2) : -1;
-    for (int j = 0; j < kFuseBits; ++j) {
-        if (!isDiagonal(op.kind) && bits[j] == lowT) fg.pos = j;
-        if (bits[j] == highT) fg.pos2 = j;
-        if ((op.mask >> bits[j]) & 1) {
-            fg.regMask |= 1u << j;
-            outer &= ~(1ull << bits[j]);
-        }
-    }
-    fg.outerMask = outer;
-    for (int k = 0; k < 8; ++k) fg.c[k] = op.c[k];
-    return fg;
-}
-
-// ---- walking a queue of LOGICAL gates (distributed mode of sharded registers) ------------------------------------
-// The queue holds gates in logical qubits with full control masks, the same on every rank.  It is cut, in program
-// order, into groups (runs of gates on at most kFuseBits dense qubits); before each group the dense qubits that sit in
-// shard-selecting slots are either left there (the group runs as a distributed pass) or exchanged with a local slot
-// first.  With `lookahead` a qubit is made local iff a later gate of the queue uses it as a dense target again; without,
-// never.  Pure bookkeeping on a copy of the qubit map: the executor replays the same exchanges on the real one.
-struct WalkStep {
-    int first, count;   // gates [first, first + count) of the queue form the group ...
-    int nSwaps;
-    SlotSwap swaps[kFuseBits];  // ... which runs after these slot exchanges
-    unsigned long long dense;   // its dense logical qubits
-};
-
-inline std::vector<WalkStep> planWalk(QubitMap map, const std::vector<PendingOp>& ops, bool lookahead) {
-    std::vector<WalkStep> steps;
-    const int n = (int)ops.size();
-    int i = 0;
-    while (i < n) {
-        WalkStep st;
-        st.first = i;
-        st.nSwaps = 0;
-        st.dense = 0;
-        int j = i;
-        while (j < n && j - i < kMaxFusedGates) {
-            const PendingOp& op = ops[j];
-            if (!isDiagonal(op.kind)) {
-                unsigned long long need = 1ull << op.target;
-                if (op.target2 >= 0) need |= 1ull << op.target2;
-                if (__builtin_popcountll(st.dense | need) > kFuseBits) break;
-                st.dense |= need;
-            }
-            ++j;
-        }
-        st.count = j - i;
-        for (unsigned long long m = st.dense; m; m &= m - 1) {
-            const int lq = __builtin_ctzll(m);
-            if (lookahead && map.phys[lq] >= map.localBits) {
-                bool usedLater = false;
-                for (int k = j; k < n && !usedLater; ++k)
-                    usedLater = !isDiagonal(ops[k].kind) && (ops[k].target == lq || ops[k].target2 == lq);
-                if (usedLater) {
-                    const SlotSwap sw = planSwapIn(map, lq, st.dense);
-                    if (sw.globalSlot >= 0) {
-                        map.applySwap(sw.globalSlot, sw.localSlot);
-                        st.swaps[st.nSwaps++] = sw;
-                    }
-                }
-            }
-            map.touch(lq);
-        }
-        steps.push_back(st);
-        i = j;
-    }
-    return steps;
-}
-
 // ---- device dispatch ---------------------------------------------------------------------------------------
-// The kernel resolves a gate with ONE table jump: kind, target position (dense gates), register mask (diagonal
-// gates) or position pair (noise) are folded into a dense opcode on the host.
-enum FusedOpcode : int {
-    kOpMatrix = 0,      // +pos           uncontrolled among the fused qubits: straight-line arithmetic on all pairs
-    kOpMatrixCtl = 4,   // +pos           some control is a fused qubit: per-pair predicate on regMask
-    kOpHadamard = 8,    // +pos
-    kOpSwap = 12,       // +pos
-    kOpPauliY = 16,     // +pos           (20..31 unused: every family starts on a multiple of 4, diagonal ones of 16)
-    kOpPhase = 32,      // +regMask (16)
-    kOpFlip = 48,       // +regMask (16)
-    kOpNoise = 64,      // +(kind - kFDephase) * 6 + pairSlot(pos, pos2)
-    kOpCount = 88
+// The kernel resolves a gate with ONE table jump: kind and target position among the sub-group's register bits
+// (dense gates) or position pair (noise) are folded into a dense opcode on the host.
+enum TileOpcode : int {
+    kOpMatrix = 0,      // +pos (0..2)
+    kOpHadamard = 4,    // +pos
+    kOpSwap = 8,        // +pos
+    kOpPauliY = 12,     // +pos
+    kOpPhase = 16,
+    kOpFlip = 17,
+    kOpNoise = 20,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
+    kOpCount = 32
 };
 
-// (p, q), p < q < 4  ->  0..5
-inline int pairSlot(int p, int q) { return p == 0 ? q - 1 : (p == 1 ? q + 1 : 5); }
+// (p, q), p < q < 3  ->  0..2
+inline int pairSlot(int p, int q) { return p + q - 1; }
 
-inline int opcodeOf(const FusedGate& g) {
-    switch (g.kind) {
-        case kFMatrix: return (g.regMask ? kOpMatrixCtl : kOpMatrix) + g.pos;
-        case kFHadamard: return kOpHadamard + g.pos;
-        case kFSwap: return kOpSwap + g.pos;
-        case kFPauliY: return kOpPauliY + g.pos;
-        case kFPhase: return kOpPhase + (int)(g.regMask & 15u);
-        case kFFlip: return kOpFlip + (int)(g.regMask & 15u);
-        default: return kOpNoise + (g.kind - kFDephase) * 6 + pairSlot(g.pos, g.pos2);
-    }
-}
-
-// Kernel tier bits (qb_kernels.cuh: FusedTier) this opcode needs: bit 0 = the less common state-vector gates,
-// bit 1 = density-matrix noise.  A group runs on the OR over its gates.
-inline int tierOf(int opcode) {
-    if (opcode >= kOpNoise) return 2;
-    if ((opcode >= kOpMatrixCtl && opcode < kOpHadamard) || (opcode >= kOpPauliY && opcode < kOpPhase) || opcode >= kOpFlip) return 1;
-    return 0;
-}
-
-// What the kernel reads per gate: 8 bytes of control, the outer-bit condition and 8 coefficients, in separate arrays:
-// the conditions of 32 gates are folded into one bit mask before the gate loop, and the control word of the NEXT
-// gate is fetched while the current one computes.
-struct GateCtl {
+// What the kernel reads per gate.
+struct TileGate {
     int opcode;
-    unsigned int regMask;
+    unsigned int regMask;          // control/selecting bits that are register bits (bit j = rb[j])
+    unsigned int tileMask;         // ... that are other tile bits (tile-index space): a per-thread condition
+    unsigned long long outerMask;  // ... outside the tile (amplitude-index space): a per-CTA condition
+    int pos, pos2;                 // register bit of the target (noise: of the lower and the higher of the two)
 };
+
+// Translate one queued op into the kernel's descriptor for a sub-group with register bits `rb` of a pass with tile
+// bits `tileBits`.
+inline TileGate describe(const PendingOp& op, const TilePass& p, const TileSub& sg) {
+    TileGate tg;
+    std::memset(&tg, 0, sizeof tg);
+    int tilePosOf[64];
+    for (int b = 0; b < 64; ++b) tilePosOf[b] = -1;
+    for (int j = 0; j < p.nTile; ++j) tilePosOf[p.tileBits[j]] = j;
+    int regOf[kTileBits];
+    for (int j = 0; j < kTileBits; ++j) regOf[j] = -1;
+    for (int j = 0; j < kSubBits; ++j)
+        if (sg.rb[j] >= 0) regOf[sg.rb[j]] = j;
+    for (unsigned long long m = op.mask; m; m &= m - 1) {
+        const int b = __builtin_ctzll(m);
+        const int tp = tilePosOf[b];
+        if (tp < 0) tg.outerMask |= 1ull << b;
+        else if (regOf[tp] >= 0) tg.regMask |= 1u << regOf[tp];
+        else tg.tileMask |= 1u << tp;
+    }
+    if (!isDiagonal(op.kind)) {
+        const int a = regOf[tilePosOf[op.target]];
+        const int b = op.target2 >= 0 ? regOf[tilePosOf[op.target2]] : -1;
+        tg.pos = (b >= 0 && b < a) ? b : a;
+        tg.pos2 = b >= 0 ? (b < a ? a : b) : 0;
+    }
+    switch (op.kind) {
+        case kFMatrix: tg.opcode = kOpMatrix + tg.pos; break;
+        case kFHadamard: tg.opcode = kOpHadamard + tg.pos; break;
+        case kFSwap: tg.opcode = kOpSwap + tg.pos; break;
+        case kFPauliY: tg.opcode = kOpPauliY + tg.pos; break;
+        case kFPhase: tg.opcode = kOpPhase; break;
+        case kFFlip: tg.opcode = kOpFlip; break;
+        default: tg.opcode = kOpNoise + (op.kind - kFDephase) * 3 + pairSlot(tg.pos, tg.pos2); break;
+    }
+    return tg;
+}
+
+// Shared-memory placement of tile index i (qb_tile.cuh uses the same function on the device): the low four bits are
+// XOR-ed with a linear function of the higher ones, so that the 16 threads of a half-warp - which differ in the lowest
+// tile-index bits that are not register bits, whatever those are - fall into different banks (counted over all 165
+// choices of 3 register bits out of 11: at most 2-way conflicts, 1.22 on average; the identity placement reaches 8-way).
+// Linear over GF(2): place(a ^ b) = place(a) ^ place(b), which lets the host precompute element offsets.
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline unsigned int tilePlace(unsigned int i) {
+    const unsigned int h = i >> 4;
+    return i ^ ((h ^ (h << 1) ^ (h << 3)) & 15u);
+}
+
+// Kernel tier this opcode needs: 0 = state-vector gates, 1 = + density-matrix noise and collapse.
+inline int tierOf(int opcode) { return opcode >= kOpNoise ? 1 : 0; }
 
 }  // namespace qb

@@ -207,263 +207,6 @@ __global__ void __launch_bounds__(kBlock) k_diag(qreal* __restrict__ re, qreal* 
 }
 
 // ======================================================================================================
-// fused multi-gate pass (qb_fuse.h): each thread owns the 2^R amplitudes spanned by the R fused qubits, keeps them
-// in registers, and runs the recorded gates over them in program order.  Dense gates use exactly the per-pair
-// arithmetic of the single-gate kernels (OpMatrix also serves compactUnitary: with r01=-bR, i01=bI, r10=bR,
-// i10=bI, r11=aR, i11=-aI its expression tree evaluates to the same IEEE bits as the reference's compact form).
-// ======================================================================================================
-
-constexpr int kMaxSlabBits = 3;        // a launch may be confined to the amplitudes with given values on up to 3 bits
-
-struct FusedLaunch {
-    int pos[kFuseBits];                  // fused qubits, ascending (amplitude-index bit positions)
-    int nGates;
-    int nIns;                            // fused qubits + slab bits: positions held out of the thread index ...
-    int ins[kFuseBits + kMaxSlabBits];   // ... ascending
-    unsigned long long slabMask;         // value of the slab bits for this launch (0 for a whole-shard pass)
-    unsigned long long offBytes[1 << kFuseBits];  // byte offset of register element e from the thread's base amplitude
-    // distributed pass only (DIST): the highest fused qubits select the GPU.  Element e lives in shard
-    // tab[e >> nLocalFused] (peer mappings of the GPUs that differ in those qubits, own shard included).
-    int nLocalFused;
-    qreal* tabRe[1 << kMaxSlabBits];
-    qreal* tabIm[1 << kMaxSlabBits];
-    unsigned long long nThreads;
-    GateCtl ctl[kMaxFusedGates + 2];     // padded
-    unsigned long long outerMask[kMaxFusedGates];  // control/selecting bits outside the fused qubits
-    qreal c[kMaxFusedGates][8];          // coefficients (meaning per kind: qb_fuse.h PendingOp::c)
-};
-
-template <int P, int R, class PairFn>
-__device__ __forceinline__ void forEachPair(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
-#pragma unroll
-    for (int e = 0; e < (1 << R); ++e) {
-        if ((e >> P) & 1) continue;
-        if ((e & regMask) == regMask) fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
-    }
-}
-
-// no control among the fused qubits: straight-line arithmetic on all pairs (no per-pair select)
-template <int P, int R, class PairFn>
-__device__ __forceinline__ void forEveryPair(qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
-#pragma unroll
-    for (int e = 0; e < (1 << R); ++e) {
-        if ((e >> P) & 1) continue;
-        fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
-    }
-}
-
-// Diagonal gates touch only the register elements whose fused-qubit bits contain MASK.  MASK is a compile-time
-// constant here (the caller switches on the 16 possible values), so exactly the selected elements are computed.
-template <int MASK, int R, class ElemFn>
-__device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 << R], ElemFn fn) {
-#pragma unroll
-    for (int e = 0; e < (1 << R); ++e)
-        if ((e & MASK) == MASK) fn(xr[e], xi[e]);
-}
-
-// One-qubit noise channel on the (row bit P, column bit Q) block structure, P < Q register bits.  Same arithmetic as
-// k_noise1 (reference QuEST_cpu.c:36-65, 118-215): coherences (1,0),(0,1) scaled by c0; populations (0,0),(1,1)
-// mixed (depolarising) or decayed (damping).  The channels are symmetric under exchanging the two bits.
-template <int KIND, int P, int Q, int R>
-__device__ __forceinline__ void noiseQuads(qreal (&xr)[1 << R], qreal (&xi)[1 << R], qreal c0, qreal c1, qreal c2) {
-#pragma unroll
-    for (int e = 0; e < (1 << R); ++e) {
-        if (((e >> P) & 1) || ((e >> Q) & 1)) continue;
-        const int e10 = e | (1 << P), e01 = e | (1 << Q), e11 = e10 | e01;
-        if (KIND == kFDensCollapse) {  // reference QuEST_cpu.c:778-852: kept block divided by the outcome probability
-            const int keep = (c1 != 0) ? e11 : e, drop = (c1 != 0) ? e : e11;
-            xr[keep] /= c0; xi[keep] /= c0;
-            xr[drop] = 0; xi[drop] = 0;
-            xr[e10] = 0; xi[e10] = 0;
-            xr[e01] = 0; xi[e01] = 0;
-            continue;
-        }
-        xr[e10] = c0 * xr[e10]; xi[e10] = c0 * xi[e10];
-        xr[e01] = c0 * xr[e01]; xi[e01] = c0 * xi[e01];
-        if (KIND == kFDepolarise) {
-            const qreal avR = (xr[e] + xr[e11]) / 2, avI = (xi[e] + xi[e11]) / 2;
-            xr[e] = c2 * xr[e] + c1 * avR;     xi[e] = c2 * xi[e] + c1 * avI;
-            xr[e11] = c2 * xr[e11] + c1 * avR; xi[e11] = c2 * xi[e11] + c1 * avI;
-        } else if (KIND == kFDamping) {
-            xr[e] = xr[e] + c1 * xr[e11];      xi[e] = xi[e] + c1 * xi[e11];
-            xr[e11] = c2 * xr[e11];            xi[e11] = c2 * xi[e11];
-        }
-    }
-}
-
-#define QB_CASE4(BASE, ...)                                                                 \
-    case (BASE) + 0: { constexpr int P = 0; __VA_ARGS__; } break;                           \
-    case (BASE) + 1: { constexpr int P = 1; __VA_ARGS__; } break;                           \
-    case (BASE) + 2: { constexpr int P = 2; __VA_ARGS__; } break;                           \
-    case (BASE) + 3: { constexpr int P = 3; __VA_ARGS__; } break;
-#define QB_ON_POS(...) if constexpr (P < R) { __VA_ARGS__; }
-#define QB_ON_MASK(...) if constexpr (M < (1 << R)) { __VA_ARGS__; }
-#define QB_NOISE_AT(KIND, SLOT, PP, QQ)                                                                  \
-    case kOpNoise + ((KIND) - kFDephase) * 6 + (SLOT):                                                   \
-        if constexpr ((QQ) < R) noiseQuads<KIND, PP, (QQ) < R ? (QQ) : (PP) + 1, R>(xr, xi, c[0], c[1], c[2]); \
-        break;
-#define QB_CASE16(BASE, ...)                                                                \
-    QB_CASE4((BASE) + 0, { constexpr int M = P; __VA_ARGS__; })                             \
-    QB_CASE4((BASE) + 4, { constexpr int M = 4 + P; __VA_ARGS__; })                         \
-    QB_CASE4((BASE) + 8, { constexpr int M = 8 + P; __VA_ARGS__; })                         \
-    QB_CASE4((BASE) + 12, { constexpr int M = 12 + P; __VA_ARGS__; })
-#define QB_CASE_NOISE(KIND)                                                                              \
-    QB_NOISE_AT(KIND, 0, 0, 1) QB_NOISE_AT(KIND, 1, 0, 2) QB_NOISE_AT(KIND, 2, 0, 3)                         \
-    QB_NOISE_AT(KIND, 3, 1, 2) QB_NOISE_AT(KIND, 4, 1, 3) QB_NOISE_AT(KIND, 5, 2, 3)
-
-// One recorded gate on the 2^R amplitudes a thread holds in registers: a single jump on the host-made opcode
-// (qb_fuse.h) into straight-line code for that (kind, register position) combination.
-// TIER selects how many gate families the instantiation understands: every code path through the register block costs
-// the others (measured: +16 small bodies = +27 % time, -24 bodies = -3 %), so the common families get a kernel of their own.
-enum FusedTier : int { kTierCore = 0,       // matrix (uncontrolled among the fused qubits), hadamard, swap, phase
-                       kTierAll = 1,        // + controlled matrix, pauliY, phase flip
-                       kTierNoise = 2,      // core + density-matrix noise channels and collapse
-                       kTierAllNoise = 3 }; // everything            (bit 0: all gates, bit 1: noise)
-
-template <int R, int TIER, bool FMA>
-__device__ __forceinline__ void applyGate(int opcode, unsigned int regMask, const qreal (&c)[8], qreal (&xr)[1 << R],
-                                          qreal (&xi)[1 << R]) {
-    using Matrix = typename std::conditional<FMA, OpMatrixFma, OpMatrix>::type;
-    using DiagPhase = typename std::conditional<FMA, DiagPhaseFma, qb::DiagPhase>::type;
-    switch (opcode) {
-        QB_CASE4(kOpMatrix, QB_ON_POS(forEveryPair<P, R>(xr, xi, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
-        QB_CASE4(kOpMatrixCtl, if constexpr ((TIER & kTierAll) != 0) QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, Matrix{c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]})))
-        QB_CASE4(kOpHadamard, QB_ON_POS(forEveryPair<P, R>(xr, xi, OpHadamard{c[0]})))  // the API has no controlled hadamard
-        QB_CASE4(kOpSwap, QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpSwap{})))
-        QB_CASE4(kOpPauliY, if constexpr ((TIER & kTierAll) != 0) QB_ON_POS(forEachPair<P, R>(xr, xi, regMask, OpPauliY{c[0]})))
-        QB_CASE16(kOpPhase, QB_ON_MASK(forSelected<M, R>(xr, xi, DiagPhase{c[0], c[1]})))
-        QB_CASE16(kOpFlip, if constexpr ((TIER & kTierAll) != 0) QB_ON_MASK(forSelected<M, R>(xr, xi, DiagFlip{})))
-        default:
-            if constexpr ((TIER & kTierNoise) != 0) {
-                switch (opcode) {
-                    QB_CASE_NOISE(kFDephase)
-                    QB_CASE_NOISE(kFDepolarise)
-                    QB_CASE_NOISE(kFDamping)
-                    QB_CASE_NOISE(kFDensCollapse)
-                    default: break;
-                }
-            }
-            break;
-    }
-}
-#undef QB_CASE4
-#undef QB_ON_POS
-#undef QB_ON_MASK
-#undef QB_NOISE_AT
-#undef QB_CASE16
-#undef QB_CASE_NOISE
-
-template <int R, int BLOCK, int MINB, int TIER, bool FMA = false, bool DIST = false>
-__global__ void __launch_bounds__(BLOCK, MINB) k_fused(qreal* __restrict__ re, qreal* __restrict__ im,
-                                                const __grid_constant__ FusedLaunch fl) {
-    static_assert(R == kFuseBits && (R == 3 || R == 4), "k_fused is written for 3 or 4 fused qubits");
-    constexpr int E = 1 << R;
-    unsigned long long k = (unsigned long long)blockIdx.x * BLOCK + threadIdx.x;
-    if (k >= fl.nThreads) return;
-    // outer index: this thread's amplitude index with the fused qubits at 0 (and the slab bits at their fixed value)
-#pragma unroll
-    for (int j = 0; j < R + kMaxSlabBits; ++j) {
-        if (j < fl.nIns) {
-            const int b = fl.ins[j];
-            const unsigned long long low = k & ((1ull << b) - 1ull);
-            k = ((k >> b) << (b + 1)) | low;
-        }
-    }
-    const unsigned long long base = k | fl.slabMask;
-    // element e of the register block lives at base + sum of 2^pos[j] over the set bits j of e: byte offsets made by the
-    // host (FusedLaunch::offBytes), added here straight from the constant bank
-    char* const reBase = reinterpret_cast<char*>(re + base);
-    char* const imBase = reinterpret_cast<char*>(im + base);
-    auto reAt = [&](int e) {
-        if constexpr (DIST) return reinterpret_cast<qreal*>(reinterpret_cast<char*>(fl.tabRe[e >> fl.nLocalFused] + base) + fl.offBytes[e]);
-        else return reinterpret_cast<qreal*>(reBase + fl.offBytes[e]);
-    };
-    auto imAt = [&](int e) {
-        if constexpr (DIST) return reinterpret_cast<qreal*>(reinterpret_cast<char*>(fl.tabIm[e >> fl.nLocalFused] + base) + fl.offBytes[e]);
-        else return reinterpret_cast<qreal*>(imBase + fl.offBytes[e]);
-    };
-    // Register index bit j <-> fused qubit pos[j].  When the lowest fused qubits are qubit 0 (and 1), neighbouring
-    // register elements are neighbours in memory: move them as 16- or 32-byte vectors so that a warp request
-    // touches each 128-byte line once per 32 B instead of once per 8 B.
-    const int lowRun = (fl.pos[0] == 0) ? ((fl.pos[1] == 1) ? 4 : 2) : 1;
-    qreal xr[E], xi[E];
-    if (lowRun == 4) {
-#pragma unroll
-        for (int e = 0; e < E; e += 4) {
-            const Vec<qreal, 4> a = load<4>(reAt(e)), b = load<4>(imAt(e));
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                xr[e + j] = a.v[j];
-                xi[e + j] = b.v[j];
-            }
-        }
-    } else if (lowRun == 2) {
-#pragma unroll
-        for (int e = 0; e < E; e += 2) {
-            const Vec<qreal, 2> a = load<2>(reAt(e)), b = load<2>(imAt(e));
-            xr[e] = a.v[0]; xr[e + 1] = a.v[1];
-            xi[e] = b.v[0]; xi[e + 1] = b.v[1];
-        }
-    } else {
-#pragma unroll
-        for (int e = 0; e < E; ++e) {
-            xr[e] = load<1>(reAt(e)).v[0];
-            xi[e] = load<1>(imAt(e)).v[0];
-        }
-    }
-    {
-        const int nGates = fl.nGates;
-        for (int g0 = 0; g0 < nGates; g0 += 32) {
-            const int cnt = min(32, nGates - g0);
-            unsigned int act = 0;
-            for (int j = 0; j < cnt; ++j) {
-                const unsigned long long m = fl.outerMask[g0 + j];
-                act |= ((base & m) == m ? 1u : 0u) << j;
-            }
-            for (int j = 0; j < cnt; ++j, act >>= 1) {
-                if (!(act & 1u)) continue;
-                const int g = g0 + j;
-                qreal c[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) c[i] = fl.c[g][i];
-                applyGate<R, TIER, FMA>(fl.ctl[g].opcode, fl.ctl[g].regMask, c, xr, xi);
-            }
-        }
-    }
-    if (lowRun == 4) {
-#pragma unroll
-        for (int e = 0; e < E; e += 4) {
-            Vec<qreal, 4> a, b;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                a.v[j] = xr[e + j];
-                b.v[j] = xi[e + j];
-            }
-            store<4>(reAt(e), a);
-            store<4>(imAt(e), b);
-        }
-    } else if (lowRun == 2) {
-#pragma unroll
-        for (int e = 0; e < E; e += 2) {
-            Vec<qreal, 2> a, b;
-            a.v[0] = xr[e]; a.v[1] = xr[e + 1];
-            b.v[0] = xi[e]; b.v[1] = xi[e + 1];
-            store<2>(reAt(e), a);
-            store<2>(imAt(e), b);
-        }
-    } else {
-#pragma unroll
-        for (int e = 0; e < E; ++e) {
-            Vec<qreal, 1> a, b;
-            a.v[0] = xr[e];
-            b.v[0] = xi[e];
-            store<1>(reAt(e), a);
-            store<1>(imAt(e), b);
-        }
-    }
-}
-
-// ======================================================================================================
 // reductions.  scratch layout: partials[j * gridDim.x + block] for j < NV, one ticket counter, result[NV].
 // The last block to take a ticket adds the per-block partials in index order (deterministic for a fixed grid)
 // and the counter wraps to 0 by itself, so the scratch needs no clearing between launches.

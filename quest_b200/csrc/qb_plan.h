@@ -254,41 +254,6 @@ inline SlabPlan planSlabs(int localBits, unsigned long long busyMask, int want, 
     return p;
 }
 
-// Distributed fused pass (backend_cuda.cu: flushDistributed): the fused qubits `bits` (ascending) of a group include
-// nShard >= 1 shard-selecting ones.  The 2^nShard GPUs that differ in exactly those bits form the group; member v has
-// the bits of v at those positions.  The pass is divided among them along the nShard highest local bits that are not
-// fused: member v processes the outer indices whose slab bits hold v.
-struct DistPlan {
-    int nLocalFused, nShard;
-    int members[8];  // rank of member v
-    int me;          // this rank's index v
-    SlabPlan slabs;
-};
-
-inline bool planDistributed(int localBits, int chunkId, const int* bits, int nBits, DistPlan& out) {
-    out.nLocalFused = 0;
-    unsigned long long fusedLocal = 0;
-    for (int j = 0; j < nBits; ++j)
-        if (bits[j] < localBits) {
-            ++out.nLocalFused;
-            fusedLocal |= 1ull << bits[j];
-        }
-    out.nShard = nBits - out.nLocalFused;
-    if (out.nShard < 1 || out.nShard > 3) return false;
-    out.me = 0;
-    for (int v = 0; v < (1 << out.nShard); ++v) {
-        int rank = chunkId;
-        for (int j = 0; j < out.nShard; ++j) {
-            const int bit = bits[out.nLocalFused + j] - localBits;
-            rank = (rank & ~(1 << bit)) | (((v >> j) & 1) << bit);
-        }
-        out.members[v] = rank;
-        if (rank == chunkId) out.me = v;
-    }
-    out.slabs = planSlabs(localBits, fusedLocal, out.nShard, 0);
-    return out.slabs.nBits == out.nShard;
-}
-
 // This rank's k_swapPeer launch for exchanging local slot l with a shard-selecting slot: the pairs
 // a[j | 2^l] <-> b[j] (j with bit l clear) are divided between the two GPUs on `split`, the highest local bit that
 // is neither l nor a slab bit; the upper rank (shard-selecting bit 0) takes split = 0.  With a slab plan only the

@@ -1,0 +1,250 @@
+// quest-b200 fused pass (sm_100a): ONE read and ONE write of the state for a whole run of recorded gates.
+//
+// Planning is done on the host (qb_fuse.h): a PASS is a run of gates whose dense targets, together with the lowest
+// kTileLow index bits, fall on at most kTileBits index bits - the tile bits.  Here, every CTA
+//   1. stages the 2^kTileBits amplitudes that differ only in the tile bits in shared memory.  They lie in HBM as
+//      2^(kTileBits-kTileLow) rows of 2^kTileLow contiguous amplitudes per array, so each row is a whole 128-byte line
+//      (more when padding bits extend the low run); the copies are asynchronous (LDGSTS), all in flight at once;
+//   2. meanwhile decides, once per CTA, which gates of the pass its tile takes part in (controls / phase-mask bits
+//      outside the tile are the same for all of its amplitudes);
+//   3. runs the pass SUB-GROUP by sub-group: each thread pulls the 2^kSubBits amplitudes spanned by the sub-group's
+//      register bits out of shared memory, applies the sub-group's gates in program order - the same per-pair
+//      expressions as the single-gate kernels (qb_kernels.cuh), so results are bit-identical to gate-at-a-time
+//      execution -, and puts them back; a barrier, and the next sub-group re-blocks the tile along other bits;
+//   4. writes the tile back.
+// Shared memory is addressed through qb::tilePlace, an XOR placement that keeps the re-blocking loads of any register
+// bit choice (nearly) free of bank conflicts.  With 3 register bits the gate bodies are 4 pairs long and exist in only
+// 3 positions each: the whole dispatch table is ~14 KB of code and stays in the 32 KB instruction cache, which the
+// register-resident 4-qubit design it replaces (16 amplitudes per thread, ~55 KB of gate bodies) did not.
+#pragma once
+
+#include "qb_fuse.h"
+#include "qb_kernels.cuh"
+
+namespace qb {
+
+constexpr int kTileThreads = 256;
+constexpr int kSubElems = 1 << kSubBits;
+
+struct TileSubDesc {
+    int first, count;                  // gates [first, first + count) of the launch
+    int rb[kSubBits];                  // register bits (tile-index space, ascending)
+    unsigned int place[kSubElems];     // tilePlace() of register element e's offset from the thread's base tile index
+};
+
+struct TileGateCtl {
+    int opcode;
+    unsigned int regMask;
+    unsigned int tileMask;
+    unsigned int pad_;
+};
+
+struct TileLaunch {
+    int nTile;                         // tile bits of this pass (<= kTileBits)
+    int nLow;                          // min(kTileLow, nTile): tile-index bits [0, nLow) are amplitude-index bits [0, nLow)
+    int nSub, nGates;
+    int nIns;                          // tile bits + slab bits: positions held out of the CTA index ...
+    int ins[kTileBits + kMaxSlabBits]; // ... ascending
+    unsigned long long slabMask;       // value of the slab bits for this launch (0 for a whole-shard pass)
+    unsigned long long rowOff[1 << (kTileBits - kTileLow)];  // amplitude offset of tile index (r << nLow) from the tile base
+    TileSubDesc sub[kMaxTileSubs];
+    TileGateCtl ctl[kMaxTileGates];
+    unsigned long long outerMask[kMaxTileGates];  // control/selecting bits outside the tile
+    qreal c[kMaxTileGates][8];         // coefficients (meaning per kind: qb_fuse.h PendingOp::c)
+};
+
+template <int P, int R, class PairFn>
+__device__ __forceinline__ void forEachPair(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e) {
+        if ((e >> P) & 1) continue;
+        if ((e & regMask) == regMask) fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
+    }
+}
+
+// Diagonal gates touch only the register elements whose register bits contain regMask.
+template <int R, class ElemFn>
+__device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, ElemFn fn) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e)
+        if ((e & regMask) == regMask) fn(xr[e], xi[e]);
+}
+
+// One-qubit noise channel on the (row bit P, column bit Q) block structure, P < Q register bits.  Same arithmetic as
+// k_noise1 (reference QuEST_cpu.c:36-65, 118-215): coherences (1,0),(0,1) scaled by c0; populations (0,0),(1,1)
+// mixed (depolarising) or decayed (damping).  The channels are symmetric under exchanging the two bits.
+template <int KIND, int P, int Q, int R>
+__device__ __forceinline__ void noiseQuads(qreal (&xr)[1 << R], qreal (&xi)[1 << R], qreal c0, qreal c1, qreal c2) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e) {
+        if (((e >> P) & 1) || ((e >> Q) & 1)) continue;
+        const int e10 = e | (1 << P), e01 = e | (1 << Q), e11 = e10 | e01;
+        if (KIND == kFDensCollapse) {  // reference QuEST_cpu.c:778-852: kept block divided by the outcome probability
+            const bool one = c1 != 0;
+            const qreal kR = (one ? xr[e11] : xr[e]) / c0, kI = (one ? xi[e11] : xi[e]) / c0;
+            xr[e] = one ? (qreal)0 : kR;   xi[e] = one ? (qreal)0 : kI;
+            xr[e11] = one ? kR : (qreal)0; xi[e11] = one ? kI : (qreal)0;
+            xr[e10] = 0; xi[e10] = 0;
+            xr[e01] = 0; xi[e01] = 0;
+            continue;
+        }
+        xr[e10] = c0 * xr[e10]; xi[e10] = c0 * xi[e10];
+        xr[e01] = c0 * xr[e01]; xi[e01] = c0 * xi[e01];
+        if (KIND == kFDepolarise) {
+            const qreal avR = (xr[e] + xr[e11]) / 2, avI = (xi[e] + xi[e11]) / 2;
+            xr[e] = c2 * xr[e] + c1 * avR;     xi[e] = c2 * xi[e] + c1 * avI;
+            xr[e11] = c2 * xr[e11] + c1 * avR; xi[e11] = c2 * xi[e11] + c1 * avI;
+        } else if (KIND == kFDamping) {
+            xr[e] = xr[e] + c1 * xr[e11];      xi[e] = xi[e] + c1 * xi[e11];
+            xr[e11] = c2 * xr[e11];            xi[e11] = c2 * xi[e11];
+        }
+    }
+}
+
+enum TileTier : int { kTierGates = 0,   // every state-vector gate
+                      kTierNoise = 1 }; // + density-matrix noise channels and collapse
+
+#define QB_POS3(BASE, ...)                                             \
+    case (BASE) + 0: { constexpr int P = 0; __VA_ARGS__; } break;      \
+    case (BASE) + 1: { constexpr int P = 1; __VA_ARGS__; } break;      \
+    case (BASE) + 2: { constexpr int P = 2; __VA_ARGS__; } break;
+#define QB_NOISE3(KIND)                                                                                             \
+    case kOpNoise + ((KIND) - kFDephase) * 3 + 0: noiseQuads<KIND, 0, 1, kSubBits>(xr, xi, C(0), C(1), C(2)); break; \
+    case kOpNoise + ((KIND) - kFDephase) * 3 + 1: noiseQuads<KIND, 0, 2, kSubBits>(xr, xi, C(0), C(1), C(2)); break; \
+    case kOpNoise + ((KIND) - kFDephase) * 3 + 2: noiseQuads<KIND, 1, 2, kSubBits>(xr, xi, C(0), C(1), C(2)); break;
+
+// One recorded gate on the 8 amplitudes a thread holds in registers: a single jump on the host-made opcode into code
+// for that (kind, register position).  Coefficients come straight from the constant bank (kernel parameters).
+template <int TIER, bool FMA>
+__device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int opcode, unsigned int regMask,
+                                              qreal (&xr)[kSubElems], qreal (&xi)[kSubElems]) {
+    using Matrix = typename std::conditional<FMA, OpMatrixFma, OpMatrix>::type;
+    using Phase = typename std::conditional<FMA, DiagPhaseFma, DiagPhase>::type;
+#define C(i) tl.c[g][i]
+    switch (opcode) {
+        QB_POS3(kOpMatrix, forEachPair<P, kSubBits>(xr, xi, regMask, Matrix{C(0), C(1), C(2), C(3), C(4), C(5), C(6), C(7)}))
+        QB_POS3(kOpHadamard, forEachPair<P, kSubBits>(xr, xi, regMask, OpHadamard{C(0)}))
+        QB_POS3(kOpSwap, forEachPair<P, kSubBits>(xr, xi, regMask, OpSwap{}))
+        QB_POS3(kOpPauliY, forEachPair<P, kSubBits>(xr, xi, regMask, OpPauliY{C(0)}))
+        case kOpPhase: forSelected<kSubBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
+        case kOpFlip: forSelected<kSubBits>(xr, xi, regMask, DiagFlip{}); break;
+        default:
+            if constexpr (TIER == kTierNoise) {
+                switch (opcode) {
+                    QB_NOISE3(kFDephase)
+                    QB_NOISE3(kFDepolarise)
+                    QB_NOISE3(kFDamping)
+                    QB_NOISE3(kFDensCollapse)
+                    default: break;
+                }
+            }
+            break;
+    }
+#undef C
+}
+#undef QB_POS3
+#undef QB_NOISE3
+
+// asynchronous global -> shared copy of one amplitude component (LDGSTS)
+__device__ __forceinline__ void copyAsync(qreal* smemDst, const qreal* src) {
+    const unsigned int d = (unsigned int)__cvta_generic_to_shared(smemDst);
+    if constexpr (sizeof(qreal) == 8)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(src) : "memory");
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src) : "memory");
+}
+
+__device__ __forceinline__ unsigned int insertZero(unsigned int k, int b) {
+    const unsigned int low = k & ((1u << b) - 1u);
+    return ((k >> b) << (b + 1)) | low;
+}
+
+#ifndef QB_TILE_MINB
+#define QB_TILE_MINB 3
+#endif
+
+template <int TIER, bool FMA>
+__global__ void __launch_bounds__(kTileThreads, QB_TILE_MINB) k_tile(qreal* __restrict__ re, qreal* __restrict__ im,
+                                                                   const __grid_constant__ TileLaunch tl) {
+    __shared__ qreal sRe[1 << kTileBits];
+    __shared__ qreal sIm[1 << kTileBits];
+    __shared__ unsigned int sAct[kMaxTileGates / 32];
+    const unsigned int tid = threadIdx.x;
+
+    // tile base: this CTA's amplitude index with the tile bits at 0 (and the slab bits at their fixed value)
+    unsigned long long k = blockIdx.x;
+#pragma unroll
+    for (int j = 0; j < kTileBits + kMaxSlabBits; ++j) {
+        if (j < tl.nIns) {
+            const int b = tl.ins[j];
+            const unsigned long long low = k & ((1ull << b) - 1ull);
+            k = ((k >> b) << (b + 1)) | low;
+        }
+    }
+    const unsigned long long base = k | tl.slabMask;
+    qreal* const gRe = re + base;
+    qreal* const gIm = im + base;
+
+    const unsigned int nElems = 1u << tl.nTile;
+    const int nLow = tl.nLow;
+    const unsigned int lowMask = (1u << nLow) - 1u;
+    // 1. stage the tile: consecutive threads take consecutive amplitudes of a row
+    for (unsigned int i = tid; i < nElems; i += kTileThreads) {
+        const unsigned long long off = tl.rowOff[i >> nLow] + (i & lowMask);
+        const unsigned int p = tilePlace(i);
+        copyAsync(&sRe[p], gRe + off);
+        copyAsync(&sIm[p], gIm + off);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    // 2. which gates does this tile take part in?  (bit g of sAct; whole warps so that the ballot is defined)
+    const int nGates = tl.nGates;
+    for (int g0 = (int)(tid & ~31u); g0 < nGates; g0 += kTileThreads) {
+        const int g = g0 + (int)(tid & 31u);
+        const unsigned long long m = g < nGates ? tl.outerMask[g] : ~0ull;
+        const unsigned int word = __ballot_sync(0xffffffffu, g < nGates && (base & m) == m);
+        if ((tid & 31u) == 0) sAct[g0 >> 5] = word;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+
+    // 3. the sub-groups
+    const unsigned int nBlocks = nElems >> kSubBits;
+    for (int s = 0; s < tl.nSub; ++s) {
+        const int r0 = tl.sub[s].rb[0], r1 = tl.sub[s].rb[1], r2 = tl.sub[s].rb[2];
+        const int gFirst = tl.sub[s].first, gEnd = gFirst + tl.sub[s].count;
+        for (unsigned int b = tid; b < nBlocks; b += kTileThreads) {
+            const unsigned int idx = insertZero(insertZero(insertZero(b, r0), r1), r2);  // register bits at 0
+            const unsigned int p0 = tilePlace(idx);
+            qreal xr[kSubElems], xi[kSubElems];
+#pragma unroll
+            for (int e = 0; e < kSubElems; ++e) {
+                const unsigned int p = p0 ^ tl.sub[s].place[e];
+                xr[e] = sRe[p];
+                xi[e] = sIm[p];
+            }
+            for (int g = gFirst; g < gEnd; ++g) {
+                if (!((sAct[g >> 5] >> (g & 31)) & 1u)) continue;
+                const unsigned int tm = tl.ctl[g].tileMask;
+                if ((idx & tm) != tm) continue;
+                applyTileGate<TIER, FMA>(tl, g, tl.ctl[g].opcode, tl.ctl[g].regMask, xr, xi);
+            }
+#pragma unroll
+            for (int e = 0; e < kSubElems; ++e) {
+                const unsigned int p = p0 ^ tl.sub[s].place[e];
+                sRe[p] = xr[e];
+                sIm[p] = xi[e];
+            }
+        }
+        __syncthreads();
+    }
+
+    // 4. write the tile back
+    for (unsigned int i = tid; i < nElems; i += kTileThreads) {
+        const unsigned long long off = tl.rowOff[i >> nLow] + (i & lowMask);
+        const unsigned int p = tilePlace(i);
+        gRe[off] = sRe[p];
+        gIm[off] = sIm[p];
+    }
+}
+
+}  // namespace qb

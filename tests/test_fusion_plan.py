@@ -1,7 +1,9 @@
-"""CPU-only check of the gate-fusion scheduler (qb_fuse.h through qb200_debugFuse): groups preserve program order,
-never need more than four dense target qubits, and the per-gate descriptors (target register bit, register mask,
-outer mask) select exactly the amplitudes the unfused gate selects.  The fused kernel's indexing is replayed in
-numpy and compared with applying the gates one by one."""
+"""CPU-only check of the gate-fusion planner (qb_fuse.h through the test hook qb200_debugTilePlan): passes preserve
+program order, a pass's dense targets plus the four lowest index bits never need more than eleven tile bits, a
+sub-group never more than three register bits, and the per-gate descriptors (opcode, register mask, tile mask, outer
+mask) select exactly the amplitudes the unfused gate selects.  The tile kernel's indexing (CTA index -> tile base by bit
+insertion, tile index -> amplitude index by deposit, thread block -> register elements) is replayed in numpy and
+compared with applying the gates one by one."""
 import ctypes
 import os
 import random
@@ -11,7 +13,8 @@ import pytest
 
 from quest_b200 import capi
 
-K_MATRIX, K_HAD, K_SWAP, K_Y, K_PHASE, K_FLIP = range(6)
+K_MATRIX, K_HAD, K_SWAP, K_Y, K_PHASE, K_FLIP, K_DEPHASE, K_DEPOL, K_DAMP = range(9)
+TILE_BITS, TILE_LOW, SUB_BITS, MAX_GATES = 11, 4, 3, 192
 
 
 def _lib():
@@ -19,42 +22,40 @@ def _lib():
         from quest_b200 import build
         build.build_product(2)
     lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
-    lib.qb200_debugFuse.restype = ctypes.c_int
+    lib.qb200_debugTilePlan.restype = ctypes.c_int
     return lib
 
 
-def fuse(lib, local_bits, ops):
+def plan(lib, local_bits, ops):
     n = len(ops)
     kinds = (ctypes.c_int * n)(*[o[0] for o in ops])
     targets = (ctypes.c_int * n)(*[o[1] for o in ops])
+    targets2 = (ctypes.c_int * n)(*[o[3] if len(o) > 3 else -1 for o in ops])
     masks = (ctypes.c_ulonglong * n)(*[o[2] for o in ops])
-    groups = (ctypes.c_int * (7 * n))()
+    passes = (ctypes.c_int * ((4 + TILE_BITS) * n))()
+    subs = (ctypes.c_int * (6 * n))()
     desc = (ctypes.c_ulonglong * (4 * n))()
-    ng = lib.qb200_debugFuse(local_bits, n, kinds, targets, masks, groups, desc)
-    gl = [dict(first=groups[7 * i], count=groups[7 * i + 1], bits=list(groups[7 * i + 2:7 * i + 6]), ndense=groups[7 * i + 6])
-          for i in range(ng)]
-    dl = [dict(kind=desc[4 * i] & 0xFF, opcode=(desc[4 * i] >> 8) & 0xFF, tier=desc[4 * i] >> 16, pos=desc[4 * i + 1], reg=desc[4 * i + 2],
-               outer=desc[4 * i + 3]) for i in range(n)]
-    return gl, dl
+    n_subs = ctypes.c_int()
+    np_ = lib.qb200_debugTilePlan(local_bits, n, kinds, targets, targets2, masks, passes, subs, desc, ctypes.byref(n_subs))
+    W = 4 + TILE_BITS
+    pl = [dict(first=passes[W * i], count=passes[W * i + 1], ntile=passes[W * i + 2], nsub=passes[W * i + 3],
+               bits=[b for b in passes[W * i + 4:W * i + W] if b >= 0], subs=[]) for i in range(np_)]
+    for j in range(n_subs.value):
+        pl[subs[6 * j]]["subs"].append(dict(first=subs[6 * j + 1], count=subs[6 * j + 2], rb=list(subs[6 * j + 3:6 * j + 6])))
+    dl = [dict(opcode=desc[4 * i], reg=desc[4 * i + 1], tile=desc[4 * i + 2], outer=desc[4 * i + 3]) for i in range(n)]
+    return pl, dl
 
 
 def decode_opcode(opcode):
-    """What k_fused's single table jump selects (qb_fuse.h FusedOpcode): (kind, target position, register mask)."""
-    if opcode < 4:
-        return K_MATRIX, opcode, 0            # uncontrolled among the fused qubits
-    if opcode < 8:
-        return K_MATRIX, opcode - 4, None     # mask taken from the descriptor at run time
-    if opcode < 12:
-        return K_HAD, opcode - 8, 0
+    """What k_tile's single table jump selects (qb_fuse.h TileOpcode): (kind, register position, second position)."""
     if opcode < 16:
-        return K_SWAP, opcode - 12, None
-    if opcode < 20:
-        return K_Y, opcode - 16, None
-    assert opcode >= 32
-    if opcode < 48:
-        return K_PHASE, None, opcode - 32
-    assert opcode < 64
-    return K_FLIP, None, opcode - 48
+        return (K_MATRIX, K_HAD, K_SWAP, K_Y)[opcode // 4], opcode % 4, None
+    if opcode == 16:
+        return K_PHASE, None, None
+    if opcode == 17:
+        return K_FLIP, None, None
+    kind, slot = divmod(opcode - 20, 3)
+    return K_DEPHASE + kind, (0, 0, 1)[slot], (1, 2, 2)[slot]
 
 
 def unitary(rng):
@@ -64,11 +65,16 @@ def unitary(rng):
 
 
 def apply_unfused(state, op, u):
-    kind, target, mask = op
+    kind, target, mask = op[:3]
     idx = np.arange(state.size)
     if kind in (K_PHASE, K_FLIP):
         sel = (idx & mask) == mask
         state[sel] *= (np.exp(0.3j) if kind == K_PHASE else -1)
+        return
+    if kind >= K_DEPHASE:  # stand-in for a noise channel: scale the two coherence blocks of the (target, target2) structure
+        t2 = op[3]
+        a, b = (idx >> target) & 1, (idx >> t2) & 1
+        state[a != b] *= 0.9
         return
     sel = ((idx & mask) == mask) & ((idx >> target) & 1 == 0)
     up = idx[sel]
@@ -77,77 +83,150 @@ def apply_unfused(state, op, u):
     state[up], state[lo] = u[0, 0] * a + u[0, 1] * b, u[1, 0] * a + u[1, 1] * b
 
 
-def apply_fused_group(state, local_bits, grp, descs, mats):
-    """numpy twin of k_fused: thread = outer index (fused qubits at 0), registers = 16 amplitudes."""
-    bits = grp["bits"]
-    outer = np.arange(state.size >> 4, dtype=np.int64)
-    for b in bits:  # ascending insertion of zeros
-        low = outer & ((1 << b) - 1)
-        outer = ((outer >> b) << (b + 1)) | low
-    off = np.array([sum(((e >> j) & 1) << bits[j] for j in range(4)) for e in range(16)], dtype=np.int64)
-    reg = state[outer[:, None] + off[None, :]]  # [threads, 16]
-    for d, u in zip(descs, mats):
-        active = (outer & d["outer"]) == d["outer"]
-        kind, p, mask = decode_opcode(d["opcode"])  # the kernel sees only the opcode and the run-time register mask
-        assert kind == d["kind"]
-        # core tier: matrix without a control among the fused qubits, hadamard, swap, phase; everything else needs tier 1
-        assert d["tier"] == (0 if kind in (K_HAD, K_SWAP, K_PHASE) or (kind == K_MATRIX and d["reg"] == 0) else 1)
-        if mask is None:
-            mask = d["reg"]
-        assert mask == d["reg"] and (p is None or p == d["pos"])
-        for e in range(16):
-            if (e & mask) != mask:
-                continue
-            if kind in (K_PHASE, K_FLIP):
-                reg[active, e] *= (np.exp(0.3j) if kind == K_PHASE else -1)
-            else:
-                if (e >> p) & 1:
+def insert_zeros(k, positions):
+    for b in sorted(positions):
+        low = k & ((1 << b) - 1)
+        k = ((k >> b) << (b + 1)) | low
+    return k
+
+
+def apply_pass(state, ops, p, descs, mats):
+    """numpy twin of k_tile: CTA = tile base (tile bits at 0), tile = 2^ntile amplitudes, thread = block of 8 elements."""
+    bits, T = p["bits"], p["ntile"]
+    bases = insert_zeros(np.arange(state.size >> T, dtype=np.int64), bits)
+    dep = np.array([sum(((i >> j) & 1) << bits[j] for j in range(T)) for i in range(1 << T)], dtype=np.int64)
+    assert all(bits[j] == j for j in range(min(TILE_LOW, T)))  # rows of the tile are contiguous in memory
+    tile = state[bases[:, None] + dep[None, :]]  # [CTAs, 2^T]
+    for sg in p["subs"]:
+        rb = sg["rb"]
+        assert rb == sorted(rb) and all(0 <= r < T for r in rb)
+        blocks = insert_zeros(np.arange((1 << T) >> SUB_BITS, dtype=np.int64), rb)
+        off = np.array([sum(((e >> j) & 1) << rb[j] for j in range(SUB_BITS)) for e in range(1 << SUB_BITS)], dtype=np.int64)
+        for k in range(sg["first"], sg["first"] + sg["count"]):
+            d, u = descs[k], mats[k]
+            kind, pos, pos2 = decode_opcode(d["opcode"])
+            assert kind == ops[k][0]
+            cta_on = (bases & d["outer"]) == d["outer"]
+            thr_on = (blocks & d["tile"]) == d["tile"]
+            assert d["tile"] & sum(1 << r for r in rb) == 0
+            cc, tt = np.nonzero(cta_on)[0][:, None], blocks[thr_on][None, :]
+            for e in range(1 << SUB_BITS):
+                if (e & d["reg"]) != d["reg"]:
                     continue
-                f = e | (1 << p)
-                a, b = reg[active, e].copy(), reg[active, f].copy()
-                reg[active, e], reg[active, f] = u[0, 0] * a + u[0, 1] * b, u[1, 0] * a + u[1, 1] * b
-    state[outer[:, None] + off[None, :]] = reg
+                if kind in (K_PHASE, K_FLIP):
+                    tile[cc, tt + off[e]] *= (np.exp(0.3j) if kind == K_PHASE else -1)
+                elif kind >= K_DEPHASE:
+                    if ((e >> pos) & 1) != ((e >> pos2) & 1):
+                        tile[cc, tt + off[e]] *= 0.9
+                else:
+                    if (e >> pos) & 1:
+                        continue
+                    f = e | (1 << pos)
+                    a, b = tile[cc, tt + off[e]].copy(), tile[cc, tt + off[f]].copy()
+                    tile[cc, tt + off[e]], tile[cc, tt + off[f]] = u[0, 0] * a + u[0, 1] * b, u[1, 0] * a + u[1, 1] * b
+    state[bases[:, None] + dep[None, :]] = tile
 
 
-@pytest.mark.parametrize("local_bits,seed", [(4, 1), (5, 2), (7, 3), (10, 4), (12, 5)])
-def test_fused_groups_reproduce_gate_by_gate(local_bits, seed):
-    lib = _lib()
-    rng = random.Random(seed)
-    nrng = np.random.default_rng(seed)
-    n_ops = 120
-    ops, mats = [], []
+def random_ops(rng, local_bits, n_ops, noise=False):
+    ops = []
     for _ in range(n_ops):
-        kind = rng.choice([K_MATRIX, K_MATRIX, K_HAD, K_SWAP, K_Y, K_PHASE, K_PHASE, K_FLIP])
+        kind = rng.choice([K_MATRIX, K_MATRIX, K_HAD, K_SWAP, K_Y, K_PHASE, K_PHASE, K_FLIP] + ([K_DEPHASE, K_DEPOL, K_DAMP] if noise else []))
         t = rng.randrange(local_bits)
         others = [q for q in range(local_bits) if q != t]
         if kind in (K_PHASE, K_FLIP):
             qs = rng.sample(range(local_bits), rng.randint(1, min(4, local_bits)))
             ops.append((kind, -1, sum(1 << q for q in qs)))
+        elif kind >= K_DEPHASE:
+            ops.append((kind, t, 0, rng.choice(others)))
         else:
-            cs = rng.sample(others, rng.choice([0, 0, 1, 2])) if others and kind != K_HAD else []  # no controlled hadamard in the API
+            cs = rng.sample(others, rng.choice([0, 0, 1, 2])) if kind != K_HAD else []  # no controlled hadamard in the API
             ops.append((kind, t, sum(1 << c for c in cs)))
-        mats.append(unitary(nrng))
-    groups, descs = fuse(lib, local_bits, ops)
-    # structure: contiguous cover in order; at most four dense targets per group, all of them among the fused bits
-    assert groups[0]["first"] == 0 and sum(g["count"] for g in groups) == n_ops
-    for a, b in zip(groups, groups[1:]):
+    return ops
+
+
+def dense_bits(op):
+    if op[0] in (K_PHASE, K_FLIP):
+        return set()
+    return {op[1]} | ({op[3]} if len(op) > 3 else set())
+
+
+@pytest.mark.parametrize("local_bits,seed,noise", [(3, 1, False), (4, 2, False), (5, 3, True), (7, 4, False), (10, 5, True),
+                                                   (12, 6, False), (14, 7, True), (16, 8, False)])
+def test_planned_passes_reproduce_gate_by_gate(local_bits, seed, noise):
+    lib = _lib()
+    rng = random.Random(seed)
+    nrng = np.random.default_rng(seed)
+    n_ops = 150
+    ops = random_ops(rng, local_bits, n_ops, noise)
+    mats = [unitary(nrng) for _ in ops]
+    passes, descs = plan(lib, local_bits, ops)
+    T = min(TILE_BITS, local_bits)
+    low = set(range(min(TILE_LOW, T)))
+    # structure: contiguous cover in order; dense targets + low run fit the tile; sub-groups cover the pass in order
+    assert passes[0]["first"] == 0 and sum(p["count"] for p in passes) == n_ops
+    for a, b in zip(passes, passes[1:]):
         assert b["first"] == a["first"] + a["count"]
-    for g in groups:
-        dense_targets = {ops[i][1] for i in range(g["first"], g["first"] + g["count"]) if ops[i][0] < K_PHASE}
-        assert len(dense_targets) <= 4 and dense_targets <= set(g["bits"])
-        assert g["bits"] == sorted(set(g["bits"])) and all(0 <= b < local_bits for b in g["bits"])
-    # greedy maximality: a group ends only because the next dense gate needs a fifth qubit, or it is full (96 gates)
-    for g, nxt in zip(groups, groups[1:]):
-        if g["count"] == 96:
+    for p in passes:
+        dense = set().union(*[dense_bits(ops[i]) for i in range(p["first"], p["first"] + p["count"])])
+        assert p["ntile"] == T and len(p["bits"]) == T and p["bits"] == sorted(set(p["bits"]))
+        assert (dense | low) <= set(p["bits"]) and all(0 <= b < local_bits for b in p["bits"])
+        assert p["subs"][0]["first"] == p["first"] and sum(s["count"] for s in p["subs"]) == p["count"]
+        for s in p["subs"]:
+            sd = set().union(*[dense_bits(ops[i]) for i in range(s["first"], s["first"] + s["count"])])
+            assert len(sd) <= SUB_BITS and {p["bits"].index(b) for b in sd} <= set(s["rb"])
+    # greedy maximality: a pass ends only because the next dense gate does not fit the tile, or it is full
+    for p, nxt in zip(passes, passes[1:]):
+        if p["count"] == MAX_GATES or len(p["subs"]) == 64:
             continue
-        dense_targets = {ops[i][1] for i in range(g["first"], g["first"] + g["count"]) if ops[i][0] < K_PHASE}
-        assert len(dense_targets) == 4 and ops[nxt["first"]][0] < K_PHASE and ops[nxt["first"]][1] not in dense_targets
+        dense = set().union(*[dense_bits(ops[i]) for i in range(p["first"], p["first"] + p["count"])])
+        assert len(dense | low | dense_bits(ops[nxt["first"]])) > T
     state = nrng.standard_normal(1 << local_bits) + 1j * nrng.standard_normal(1 << local_bits)
     want = state.copy()
     for op, u in zip(ops, mats):
         apply_unfused(want, op, u)
     got = state.copy()
-    for g in groups:
-        sl = slice(g["first"], g["first"] + g["count"])
-        apply_fused_group(got, local_bits, g, descs[sl], mats[sl])
+    for p in passes:
+        apply_pass(got, ops, p, descs, mats)
     np.testing.assert_allclose(got, want, atol=1e-12)
+
+
+def test_sweep_step_needs_four_passes_at_30_qubits():
+    """The benchmark's step (configs[1]: 120 gates, every target 0..29) is four passes over HBM."""
+    lib = _lib()
+    ops = []
+    for t in range(30):
+        ops += [(K_HAD, t, 0), (K_MATRIX, t, 0), (K_SWAP, t, 1 << ((t + 1) % 30)),
+                (K_PHASE, -1, (1 << t) | (1 << ((t + 1) % 30)) | (1 << ((t + 2) % 30)))]
+    passes, _ = plan(lib, 30, ops)
+    assert len(passes) == 4, [p["count"] for p in passes]
+    assert [p["count"] for p in passes][0] == 44  # targets 0..10
+
+
+def test_shared_memory_placement_is_a_conflict_light_bijection():
+    """qb::tilePlace (mirrored here): a bijection of the tile, linear over GF(2), and for every choice of three register
+    bits the 16 threads of a half-warp (which differ in the four lowest non-register bits) hit each bank at most twice."""
+    import itertools
+
+    def place(i):
+        h = i >> 4
+        return i ^ ((h ^ (h << 1) ^ (h << 3)) & 15)
+
+    n = 1 << TILE_BITS
+    assert sorted(place(i) for i in range(n)) == list(range(n))
+    rng = random.Random(0)
+    for _ in range(200):
+        a, b = rng.randrange(n), rng.randrange(n)
+        assert place(a ^ b) == place(a) ^ place(b)
+    worst = 0
+    for reg in itertools.combinations(range(TILE_BITS), SUB_BITS):
+        free = [b for b in range(TILE_BITS) if b not in reg]
+        for half in (0, 1):
+            for e in range(1 << SUB_BITS):
+                hits = {}
+                for lane in range(16):
+                    idx = sum(((lane >> j) & 1) << free[j] for j in range(4)) | (half << free[4])
+                    idx |= sum(((e >> j) & 1) << reg[j] for j in range(SUB_BITS))
+                    bank = place(idx) & 15
+                    hits[bank] = hits.get(bank, 0) + 1
+                worst = max(worst, max(hits.values()))
+    assert worst <= 2

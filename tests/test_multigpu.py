@@ -16,8 +16,6 @@ MODES = {
     "default": {},
     "exchange_pipeline_forced_on_small_shards": {"QUEST_B200_OVERLAP_MIN_BITS": "8"},
     "exchanges_back_to_back": {"QUEST_B200_OVERLAP": "0"},
-    "distributed_passes": {"QUEST_B200_DISTRIBUTED": "1"},
-    "distributed_passes_with_lookahead": {"QUEST_B200_DISTRIBUTED": "2"},
 }
 
 
@@ -35,8 +33,6 @@ def test_sharded_parity(mode):
     if n < 2:
         pytest.skip("needs at least two GPUs")
     world = 8 if n >= 8 else (4 if n >= 4 else 2)
-    if "QUEST_B200_DISTRIBUTED" in MODES[mode]:
-        world = 2  # the opt-in distributed passes are validated on GPU for one shard-selecting qubit only
     env = dict(os.environ, **MODES[mode])
     port = 29600 + sorted(MODES).index(mode)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",

@@ -328,64 +328,6 @@ def test_slab_exchanges_cover_the_exchange_exactly_once(local_bits, vec, local_s
         assert np.array_equal(seen, want_seen)
 
 
-# ---- distributed fused pass (qb::planDistributed) ---------------------------------------------------------------
-
-def _dist_plan(lib, local_bits, chunk, bits):
-    out = (ctypes.c_int * 15)()
-    ok = lib.qb200_debugDistributed(local_bits, chunk, (ctypes.c_int * 4)(*bits), out)
-    assert ok == 1
-    n_local, n_shard, me, n_slab = out[0], out[1], out[2], out[3]
-    return dict(n_local=n_local, n_shard=n_shard, me=me, slab_bits=list(out[4:4 + n_slab]), members=list(out[7:7 + (1 << n_shard)]))
-
-
-@pytest.mark.parametrize("world,local_bits,bits", [(2, 8, [1, 4, 7, 8]), (4, 7, [0, 3, 7, 8]), (4, 8, [2, 5, 6, 9]),
-                                                   (8, 7, [3, 7, 8, 9]), (8, 9, [0, 1, 4, 11]), (8, 8, [5, 8, 9, 10])])
-def test_distributed_pass_plan_partitions_the_work_and_applies_the_gate(world, local_bits, bits):
-    """Every rank plans the same group; the members' slabs partition the outer indices of every shard of the group; a
-    gate on a shard-selecting fused qubit executed block by block - element e in shard members[e >> nLocalFused] -
-    equals the same gate on the unsharded state."""
-    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
-    lib.qb200_debugDistributed.restype = ctypes.c_int
-    nq = local_bits + world.bit_length() - 1
-    rng = np.random.default_rng(sum(bits) + world)
-    full = rng.standard_normal(1 << nq) + 1j * rng.standard_normal(1 << nq)
-    shards = [full[r << local_bits:(r + 1) << local_bits].copy() for r in range(world)]
-    plans = [_dist_plan(lib, local_bits, r, bits) for r in range(world)]
-    u = rand_u(np.random.default_rng(5))
-    target_pos = 3  # the highest fused qubit: always shard-selecting in these cases
-    touched = [np.zeros(1 << local_bits, dtype=np.int32) for _ in range(world)]
-    for r, p in enumerate(plans):
-        assert p["n_local"] + p["n_shard"] == 4 and p["members"][p["me"]] == r
-        for m in p["members"]:  # every member plans the same group and the same slab bits
-            assert plans[m]["members"] == p["members"] and plans[m]["slab_bits"] == p["slab_bits"]
-        assert len({plans[m]["me"] for m in p["members"]}) == len(p["members"])
-        fused_local = bits[:p["n_local"]]
-        assert all(b < local_bits and b not in fused_local for b in p["slab_bits"]) and len(p["slab_bits"]) == p["n_shard"]
-        held_out = sorted(fused_local + p["slab_bits"])
-        slab_val = sum(((p["me"] >> j) & 1) << p["slab_bits"][j] for j in range(p["n_shard"]))
-        for k in range((1 << local_bits) >> len(held_out)):
-            base = k
-            for b in held_out:  # the kernel's index expansion
-                base = ((base >> b) << (b + 1)) | (base & ((1 << b) - 1))
-            base |= slab_val
-            block = []
-            for e in range(16):
-                off = sum(1 << bits[j] for j in range(p["n_local"]) if (e >> j) & 1)
-                shard = p["members"][e >> p["n_local"]]
-                block.append((shard, base + off))
-                touched[shard][base + off] += 1
-            for e in range(16):
-                if (e >> target_pos) & 1:
-                    continue
-                (s0, i0), (s1, i1) = block[e], block[e | (1 << target_pos)]
-                a, b = shards[s0][i0], shards[s1][i1]
-                shards[s0][i0], shards[s1][i1] = u[0, 0] * a + u[0, 1] * b, u[1, 0] * a + u[1, 1] * b
-    for t in touched:
-        assert np.all(t == 1)  # every amplitude of every shard belongs to exactly one block of exactly one member
-    want = dense_reference(full, nq, bits[target_pos], 0, u)
-    np.testing.assert_allclose(np.concatenate(shards), want, atol=1e-12)
-
-
 def test_swap_in_prefers_high_slots_and_falls_back_to_low_ones():
     """A shard-selecting qubit is exchanged with a slot >= 10 of a large shard (long contiguous runs over NVLink); only
     when every such slot is pinned by the gate itself (or hosts a guest) does the search drop to the low slots."""
@@ -410,82 +352,3 @@ def test_swap_in_prefers_high_slots_and_falls_back_to_low_ones():
     assert first_victim >= 10 and events[1][0] == 14 and events[1][1] not in (10, 11, 12)
     assert sorted(phys) == list(range(nq))    # still a permutation
 
-
-# ---- walking a queue of logical gates (qb::planWalk: distributed mode, with and without look-ahead) -----------------
-
-def _walk(lib, nq, local_bits, ops, lookahead):
-    n = len(ops)
-    out = (ctypes.c_int * (11 * n))()
-    ns = lib.qb200_debugWalk(nq, local_bits, n, (ctypes.c_int * n)(*[o[0] for o in ops]), (ctypes.c_int * n)(*[o[1] for o in ops]),
-                             (ctypes.c_int * n)(*[-1] * n), (ctypes.c_ulonglong * n)(*[o[2] for o in ops]), int(lookahead), out)
-    steps = []
-    for k in range(ns):
-        o = out[11 * k:11 * (k + 1)]
-        steps.append(dict(first=o[0], count=o[1], swaps=[(o[3 + 2 * j], o[4 + 2 * j]) for j in range(o[2])]))
-    return steps
-
-
-@pytest.mark.parametrize("world,seed,lookahead", [(2, 11, False), (2, 12, True), (4, 13, True), (8, 14, True), (8, 15, False)])
-def test_walk_of_a_logical_queue_reproduces_the_circuit(world, seed, lookahead):
-    """The steps cover the queue in order with at most four dense qubits each; replaying them - slot exchanges as bit
-    swaps, then the group's gates at the bit positions of the layout that then holds (shard-selecting positions
-    included: that is what a distributed pass executes) - gives the circuit's result once the layout is undone.
-    With look-ahead a qubit is exchanged exactly when a later gate uses it again; without, never."""
-    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
-    lib.qb200_debugWalk.restype = ctypes.c_int
-    K_MATRIX = 0
-    rng = random.Random(seed)
-    nq = 10
-    L = nq - (world.bit_length() - 1)
-    ops, mats = [], []
-    for _ in range(90):
-        t = rng.randrange(nq) if rng.random() < 0.6 else rng.randrange(L, nq)
-        cs = rng.sample([q for q in range(nq) if q != t], rng.choice([0, 0, 1, 2]))
-        ops.append((K_MATRIX, t, sum(1 << c for c in cs)))
-        mats.append(rand_u(rng))
-    steps = _walk(lib, nq, L, ops, lookahead)
-    assert steps[0]["first"] == 0 and sum(s["count"] for s in steps) == len(ops)
-    state = circuits.random_state(1 << nq, seed)
-    want = state.copy()
-    for op, u in zip(ops, mats):
-        want = dense_reference(want, nq, op[1], op[2], u)
-    cur = state.copy()
-    layout = list(range(nq))  # logical -> bit position
-    pos = 0
-    n_swaps = 0
-    for s in steps:
-        assert s["first"] == pos
-        group = range(s["first"], s["first"] + s["count"])
-        dense = {ops[i][1] for i in group}
-        assert 1 <= len(dense) <= 4
-        later = {ops[i][1] for i in range(s["first"] + s["count"], len(ops))}
-        brought_in = set()
-        for g, l in s["swaps"]:
-            assert g >= L > l
-            brought_in.add(layout.index(g))
-            cur = _swap_bits(cur, g, l)
-            a, b = layout.index(g), layout.index(l)
-            layout[a], layout[b] = l, g
-            n_swaps += 1
-        if lookahead:
-            # exactly the dense qubits that were shard-selecting before this step AND are used again later came in
-            assert brought_in <= dense and all(q in later for q in brought_in)
-            for q in dense:
-                if layout[q] >= L:
-                    assert q not in later
-        else:
-            assert not s["swaps"]
-        for i in group:
-            _, t, m = ops[i]
-            pm = sum(1 << layout[c] for c in range(nq) if (m >> c) & 1)
-            cur = dense_reference(cur, nq, layout[t], pm, mats[i])
-        pos += s["count"]
-    # undo the layout: bring every logical qubit back to its own bit position
-    for q in range(nq):
-        if layout[q] != q:
-            other = layout.index(q)
-            cur = _swap_bits(cur, layout[q], q)
-            layout[other], layout[q] = layout[q], q
-    np.testing.assert_allclose(cur, want, atol=1e-12)
-    if lookahead:
-        assert n_swaps > 0

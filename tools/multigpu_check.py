@@ -130,11 +130,9 @@ def main():
                   f"states_ok={st_ok} -> {'PASS' if good else 'FAIL'}", flush=True)
     lib.lib.qb200_getOverlappedExchangeCount.restype = ctypes.c_ulonglong
     lib.lib.qb200_getSlotExchangeCount.restype = ctypes.c_ulonglong
-    lib.lib.qb200_getDistributedPassCount.restype = ctypes.c_ulonglong
     if rank == 0:
         print(f"slot exchanges: {lib.lib.qb200_getSlotExchangeCount()}, of which pipelined with the preceding fused pass: "
-              f"{lib.lib.qb200_getOverlappedExchangeCount()}; distributed fused passes: {lib.lib.qb200_getDistributedPassCount()}",
-              flush=True)
+              f"{lib.lib.qb200_getOverlappedExchangeCount()}", flush=True)
     flag = torch.tensor([1 if ok else 0])
     dist.broadcast(flag, 0)
     lib.destroyQuESTEnv(env)
