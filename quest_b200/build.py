@@ -28,9 +28,15 @@ def _newer(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_product(prec: int = 2, force: bool = False, verbose: bool = False) -> str:
+def build_product(prec: int = 2, force: bool = False, verbose: bool = False, defines=(), variant: str = "") -> str:
+    """`defines` / `variant`: an experimental build with extra -D flags goes to lib/variants/lib<variant>.so (used by
+    tools/ab_variants.sh through QUEST_B200_LIB); the product itself is always built without any."""
     os.makedirs(LIBDIR, exist_ok=True)
     out = os.path.join(LIBDIR, "libQuEST.so" if prec == 2 else "libQuEST_f32.so")
+    if variant:
+        os.makedirs(os.path.join(LIBDIR, "variants"), exist_ok=True)
+        out = os.path.join(LIBDIR, "variants", f"lib{variant}.so")
+        force = True
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(ROOT, "include", f) for f in os.listdir(os.path.join(ROOT, "include"))]
     if not force and not _newer(out, deps):
         return out
@@ -38,6 +44,7 @@ def build_product(prec: int = 2, force: bool = False, verbose: bool = False) -> 
            "-Xcompiler", "-fPIC,-fvisibility=default,-Wall,-Wno-unused-function",
            "-Xlinker", "-Bsymbolic", f"-DQuEST_PREC={prec}",
            "-I" + os.path.join(ROOT, "include"), "-I" + CSRC]
+    cmd += [f"-D{d}" for d in defines]
     if verbose:
         cmd += ["-Xptxas", "-v"]
     cmd += [os.path.join(CSRC, f) for f in CU_SOURCES + CXX_SOURCES]  # .cu through nvcc, .cpp straight to g++
@@ -48,6 +55,10 @@ def build_product(prec: int = 2, force: bool = False, verbose: bool = False) -> 
 
 
 if __name__ == "__main__":
+    if "--variant" in sys.argv:  # python build.py --variant NAME -DFOO=1 -DBAR=2
+        name = sys.argv[sys.argv.index("--variant") + 1]
+        build_product(2, verbose="-v" in sys.argv, defines=[a[2:] for a in sys.argv if a.startswith("-D")], variant=name)
+        sys.exit(0)
     build_product(2, force="--force" in sys.argv, verbose="-v" in sys.argv)
     if "--f32" in sys.argv:
         build_product(1, force="--force" in sys.argv)

@@ -245,6 +245,8 @@ def load(path: str) -> QuESTLibrary:
 def load_product(prec: int = 2) -> QuESTLibrary:
     """The CUDA library.  Raises if it has not been built; there is no CPU stand-in."""
     path = PRODUCT_LIB if prec == 2 else PRODUCT_LIB_F32
+    if prec == 2 and os.environ.get("QUEST_B200_LIB"):  # kernel A/B experiments (tools/ab_variants.sh): another build of the product
+        path = os.environ["QUEST_B200_LIB"]
     if not os.path.isfile(path):
         raise RuntimeError(
             f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "

@@ -331,7 +331,7 @@ int preparePass(const std::vector<PendingOp>& ops, const TilePass& p) {
         for (int k = sg.first; k < sg.first + sg.count; ++k) {
             const TileGate tg = describe(ops[k], p, sg);
             const int g = k - p.first;
-            tl.ctl[g] = TileGateCtl{tg.opcode, tg.regMask, tg.tileMask, 0};
+            tl.ctl[g] = TileGateCtl{(unsigned short)tg.tileMask, (unsigned char)tg.opcode, (unsigned char)tg.regMask, 0};
             tl.outerMask[g] = tg.outerMask;
             std::memcpy(tl.c[g], ops[k].c, sizeof ops[k].c);
             tier |= tierOf(tg.opcode);
@@ -866,6 +866,11 @@ QuESTEnv createQuESTEnv(void) {
     CUDA_OK(cudaMalloc(&g.dWidePartials, (size_t)kProbAll * g.wideBlocks * sizeof(double)));
     CUDA_OK(cudaMalloc(&g.dWide, kProbAll * sizeof(double)));
     CUDA_OK(cudaHostAlloc(&g.hWide, kProbAll * sizeof(double), cudaHostAllocDefault));
+    // the fused pass keeps 32 KiB of shared memory per CTA and wants 3 CTAs per SM: ask for the large carve-out
+    CUDA_OK(cudaFuncSetAttribute(k_tile<kTierGates, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CUDA_OK(cudaFuncSetAttribute(k_tile<kTierGates, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CUDA_OK(cudaFuncSetAttribute(k_tile<kTierNoise, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CUDA_OK(cudaFuncSetAttribute(k_tile<kTierNoise, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     if (const char* s = std::getenv("QUEST_B200_PROB_CACHE")) g.probCache = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_FUSE")) g.fuse = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_FMA")) g.contract = std::atoi(s) != 0;
@@ -1464,9 +1469,11 @@ void qb200_setKernelTiming(int enabled) {
 void qb200_getFusedKernelTime(double* totalMs, unsigned long long* launches) {
     CUDA_OK(cudaStreamSynchronize(g.stream));
     double sum = 0;
+    const bool show = std::getenv("QUEST_B200_PRINT_PASS_TIMES") != nullptr;  // diagnostics: every pass's own device time
     for (auto& ev : g.fusedEvents) {
         float ms = 0;
         CUDA_OK(cudaEventElapsedTime(&ms, ev.first, ev.second));
+        if (show) std::printf("[pass %.2f ms] ", ms);
         sum += ms;
         cudaEventDestroy(ev.first);
         cudaEventDestroy(ev.second);

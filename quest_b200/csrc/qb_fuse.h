@@ -38,6 +38,7 @@ constexpr int kTileLow = 4;              // the lowest index bits are always til
 constexpr int kSubBits = 3;              // qubits resolved in registers per sub-group (2^3 amplitudes per thread)
 constexpr int kMaxTileGates = 192;       // gates per pass: descriptors travel as kernel parameters (constant bank)
 constexpr int kMaxTileSubs = 64;         // sub-groups per pass
+constexpr int kMaxSubGates = 64;         // gates per sub-group: their per-CTA activity is one 64-bit word
 constexpr int kMaxSlabBits = 3;          // a launch may be confined to the amplitudes with given values on up to 3 bits
 
 enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, kFPhase = 4, kFFlip = 5,
@@ -105,7 +106,7 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
         while (i < n && p.count < kMaxTileGates) {
             const unsigned long long need = denseBitsOf(ops[i]);
             if (__builtin_popcountll(p.denseMask | need | lowMask) > T) break;
-            if (__builtin_popcountll(subDense | need) > R) {  // the gate opens a new sub-group
+            if (__builtin_popcountll(subDense | need) > R || cur.count == kMaxSubGates) {  // the gate opens a new sub-group
                 if ((int)p.subs.size() + 1 == kMaxTileSubs) break;
                 p.subs.push_back(cur);
                 subMasks.push_back(subDense);
@@ -172,17 +173,16 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
 // ---- device dispatch ---------------------------------------------------------------------------------------
 // The kernel resolves a gate with ONE table jump: kind and target position among the sub-group's register bits
 // (dense gates) or position pair (noise) are folded into a dense opcode on the host.
-enum TileOpcode : int {
+enum TileOpcode : int {   // dense numbering: the kernel's switch compiles to one jump table
     kOpMatrix = 0,      // +pos (0..2)
-    kOpHadamard = 4,    // +pos
-    kOpSwap = 8,        // +pos
-    kOpPauliY = 12,     // +pos
-    kOpPhase = 16,
-    kOpFlip = 17,
-    kOpNoise = 20,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
-    kOpCount = 32
+    kOpHadamard = 3,    // +pos
+    kOpSwap = 6,        // +pos
+    kOpPauliY = 9,      // +pos
+    kOpPhase = 12,
+    kOpFlip = 13,
+    kOpNoise = 14,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
+    kOpCount = 26
 };
-
 // (p, q), p < q < 3  ->  0..2
 inline int pairSlot(int p, int q) { return p + q - 1; }
 

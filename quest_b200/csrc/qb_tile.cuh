@@ -23,6 +23,10 @@
 
 namespace qb {
 
+#ifndef QB_SWAP_IMPL
+#define QB_SWAP_IMPL forEachPair  // forPairsByMask: one body per control mask - measured worse (register moves at the joins)
+#endif
+
 constexpr int kTileThreads = 256;
 constexpr int kSubElems = 1 << kSubBits;
 
@@ -32,12 +36,13 @@ struct TileSubDesc {
     unsigned int place[kSubElems];     // tilePlace() of register element e's offset from the thread's base tile index
 };
 
-struct TileGateCtl {
-    int opcode;
-    unsigned int regMask;
-    unsigned int tileMask;
+struct TileGateCtl {                   // 8 bytes: one constant-bank load per gate
+    unsigned short tileMask;           // selecting bits among the tile bits that are not register bits (tile-index space)
+    unsigned char opcode;
+    unsigned char regMask;
     unsigned int pad_;
 };
+static_assert(kTileBits <= 16, "tileMask is 16 bits wide");
 
 struct TileLaunch {
     int nTile;                         // tile bits of this pass (<= kTileBits)
@@ -53,6 +58,41 @@ struct TileLaunch {
     qreal c[kMaxTileGates][8];         // coefficients (meaning per kind: qb_fuse.h PendingOp::c)
 };
 
+// OpMatrix with the four outputs built up side by side: every product that reads an old value is issued before the
+// last partial sum of that value's replacement, so the new values can be allocated to the registers of the old ones and
+// the gate bodies need no register moves where control flow rejoins after the dispatch.  Each output is still
+// ((a*x - b*y) + c*z) - d*w, evaluated left to right: the same IEEE bits as OpMatrix / the reference's expressions.
+struct TileMatrix {
+    qreal r00, i00, r01, i01, r10, i10, r11, i11;
+    __device__ __forceinline__ void operator()(qreal& uR, qreal& uI, qreal& lR, qreal& lI) const {
+        qreal a = r00 * uR, b = r00 * uI, c = r10 * uR, d = r10 * uI;
+        a = a - i00 * uI; b = b + i00 * uR; c = c - i10 * uI; d = d + i10 * uR;
+        a = a + r01 * lR; b = b + r01 * lI; c = c + r11 * lR; d = d + r11 * lI;
+        const qreal t0 = i01 * lI, t1 = i01 * lR, t2 = i11 * lI, t3 = i11 * lR;
+        uR = a - t0; uI = b + t1; lR = c - t2; lI = d + t3;
+    }
+};
+struct TileMatrixFma {
+    qreal r00, i00, r01, i01, r10, i10, r11, i11;
+    __device__ __forceinline__ void operator()(qreal& uR, qreal& uI, qreal& lR, qreal& lI) const {
+        qreal a = r00 * uR, b = r00 * uI, c = r10 * uR, d = r10 * uI;
+        a = fma(-i00, uI, a); b = fma(i00, uR, b); c = fma(-i10, uI, c); d = fma(i10, uR, d);
+        a = fma(r01, lR, a); b = fma(r01, lI, b); c = fma(r11, lR, c); d = fma(r11, lI, d);
+        const qreal nuR = fma(-i01, lI, a), nuI = fma(i01, lR, b), nlR = fma(-i11, lI, c), nlI = fma(i11, lR, d);
+        uR = nuR; uI = nuI; lR = nlR; lI = nlI;
+    }
+};
+
+// no control among the register bits: straight-line arithmetic on all pairs
+template <int P, int R, class PairFn>
+__device__ __forceinline__ void forEveryPair(qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e) {
+        if ((e >> P) & 1) continue;
+        fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
+    }
+}
+
 template <int P, int R, class PairFn>
 __device__ __forceinline__ void forEachPair(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
 #pragma unroll
@@ -62,12 +102,52 @@ __device__ __forceinline__ void forEachPair(qreal (&xr)[1 << R], qreal (&xi)[1 <
     }
 }
 
-// Diagonal gates touch only the register elements whose register bits contain regMask.
-template <int R, class ElemFn>
-__device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, ElemFn fn) {
+// Diagonal gates touch only the register elements whose register bits contain the mask: compile-time masks (the caller
+// switches on the 8 possible values), so exactly the selected elements are computed.
+template <int MASK, int R, class ElemFn>
+__device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 << R], ElemFn fn) {
 #pragma unroll
     for (int e = 0; e < (1 << R); ++e)
-        if ((e & regMask) == regMask) fn(xr[e], xi[e]);
+        if ((e & MASK) == MASK) fn(xr[e], xi[e]);
+}
+// Pair operations whose control mask is switched on (swap: a handful of register moves per pair, which the compiler
+// would otherwise predicate - executing all of them for every gate).  MASK never contains bit P.
+template <int P, int MASK, int R, class PairFn>
+__device__ __forceinline__ void forMaskedPairs(qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e) {
+        if ((e >> P) & 1) continue;
+        if ((e & MASK) == MASK) fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
+    }
+}
+template <int P, int R, class PairFn>
+__device__ __forceinline__ void forPairsByMask(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
+    static_assert(R == 3, "eight register masks");
+    switch (regMask) {
+        case 0: forMaskedPairs<P, 0, R>(xr, xi, fn); break;
+        case 1: forMaskedPairs<P, 1 & ~(1 << P), R>(xr, xi, fn); break;
+        case 2: forMaskedPairs<P, 2 & ~(1 << P), R>(xr, xi, fn); break;
+        case 3: forMaskedPairs<P, 3 & ~(1 << P), R>(xr, xi, fn); break;
+        case 4: forMaskedPairs<P, 4 & ~(1 << P), R>(xr, xi, fn); break;
+        case 5: forMaskedPairs<P, 5 & ~(1 << P), R>(xr, xi, fn); break;
+        case 6: forMaskedPairs<P, 6 & ~(1 << P), R>(xr, xi, fn); break;
+        default: forMaskedPairs<P, 7 & ~(1 << P), R>(xr, xi, fn); break;
+    }
+}
+
+template <int R, class ElemFn>
+__device__ __forceinline__ void forSelectedByMask(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, ElemFn fn) {
+    static_assert(R == 3, "eight register masks");
+    switch (regMask) {
+        case 0: forSelected<0, R>(xr, xi, fn); break;
+        case 1: forSelected<1, R>(xr, xi, fn); break;
+        case 2: forSelected<2, R>(xr, xi, fn); break;
+        case 3: forSelected<3, R>(xr, xi, fn); break;
+        case 4: forSelected<4, R>(xr, xi, fn); break;
+        case 5: forSelected<5, R>(xr, xi, fn); break;
+        case 6: forSelected<6, R>(xr, xi, fn); break;
+        default: forSelected<7, R>(xr, xi, fn); break;
+    }
 }
 
 // One-qubit noise channel on the (row bit P, column bit Q) block structure, P < Q register bits.  Same arithmetic as
@@ -118,16 +198,20 @@ enum TileTier : int { kTierGates = 0,   // every state-vector gate
 template <int TIER, bool FMA>
 __device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int opcode, unsigned int regMask,
                                               qreal (&xr)[kSubElems], qreal (&xi)[kSubElems]) {
-    using Matrix = typename std::conditional<FMA, OpMatrixFma, OpMatrix>::type;
+    using Matrix = typename std::conditional<FMA, TileMatrixFma, TileMatrix>::type;
     using Phase = typename std::conditional<FMA, DiagPhaseFma, DiagPhase>::type;
 #define C(i) tl.c[g][i]
     switch (opcode) {
-        QB_POS3(kOpMatrix, forEachPair<P, kSubBits>(xr, xi, regMask, Matrix{C(0), C(1), C(2), C(3), C(4), C(5), C(6), C(7)}))
-        QB_POS3(kOpHadamard, forEachPair<P, kSubBits>(xr, xi, regMask, OpHadamard{C(0)}))
-        QB_POS3(kOpSwap, forEachPair<P, kSubBits>(xr, xi, regMask, OpSwap{}))
+        QB_POS3(kOpMatrix, {
+            const Matrix m{C(0), C(1), C(2), C(3), C(4), C(5), C(6), C(7)};
+            if (regMask == 0) forEveryPair<P, kSubBits>(xr, xi, m);
+            else forEachPair<P, kSubBits>(xr, xi, regMask, m);
+        })
+        QB_POS3(kOpHadamard, forEveryPair<P, kSubBits>(xr, xi, OpHadamard{C(0)}))  // the API has no controlled hadamard
+        QB_POS3(kOpSwap, QB_SWAP_IMPL<P, kSubBits>(xr, xi, regMask, OpSwap{}))
         QB_POS3(kOpPauliY, forEachPair<P, kSubBits>(xr, xi, regMask, OpPauliY{C(0)}))
-        case kOpPhase: forSelected<kSubBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
-        case kOpFlip: forSelected<kSubBits>(xr, xi, regMask, DiagFlip{}); break;
+        case kOpPhase: forSelectedByMask<kSubBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
+        case kOpFlip: forSelectedByMask<kSubBits>(xr, xi, regMask, DiagFlip{}); break;
         default:
             if constexpr (TIER == kTierNoise) {
                 switch (opcode) {
@@ -135,8 +219,10 @@ __device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int o
                     QB_NOISE3(kFDepolarise)
                     QB_NOISE3(kFDamping)
                     QB_NOISE3(kFDensCollapse)
-                    default: break;
+                    default: __builtin_unreachable();
                 }
+            } else {
+                __builtin_unreachable();  // the host never sends a noise opcode to this tier (qb::tierOf)
             }
             break;
     }
@@ -166,9 +252,9 @@ __device__ __forceinline__ unsigned int insertZero(unsigned int k, int b) {
 template <int TIER, bool FMA>
 __global__ void __launch_bounds__(kTileThreads, QB_TILE_MINB) k_tile(qreal* __restrict__ re, qreal* __restrict__ im,
                                                                    const __grid_constant__ TileLaunch tl) {
-    __shared__ qreal sRe[1 << kTileBits];
-    __shared__ qreal sIm[1 << kTileBits];
-    __shared__ unsigned int sAct[kMaxTileGates / 32];
+    constexpr unsigned int kTileElems = 1u << kTileBits;
+    __shared__ qreal sAmp[2 * kTileElems];  // real parts, then imaginary parts: one address register serves both
+    __shared__ unsigned int sAct[kMaxTileGates / 32 + 2];
     const unsigned int tid = threadIdx.x;
 
     // tile base: this CTA's amplitude index with the tile bits at 0 (and the slab bits at their fixed value)
@@ -182,23 +268,30 @@ __global__ void __launch_bounds__(kTileThreads, QB_TILE_MINB) k_tile(qreal* __re
         }
     }
     const unsigned long long base = k | tl.slabMask;
-    qreal* const gRe = re + base;
-    qreal* const gIm = im + base;
 
+    // 1. stage the tile: consecutive threads take consecutive amplitudes of a row.  Thread t copies tile indices
+    // t, t + 256, t + 512, ...: both the amplitude offset and the shared-memory placement are linear in the index, so
+    // index t + 256 j costs one add / one xor on top of what index t needs (rowOff is indexed by tile index >> nLow).
     const unsigned int nElems = 1u << tl.nTile;
     const int nLow = tl.nLow;
-    const unsigned int lowMask = (1u << nLow) - 1u;
-    // 1. stage the tile: consecutive threads take consecutive amplitudes of a row
-    for (unsigned int i = tid; i < nElems; i += kTileThreads) {
-        const unsigned long long off = tl.rowOff[i >> nLow] + (i & lowMask);
-        const unsigned int p = tilePlace(i);
-        copyAsync(&sRe[p], gRe + off);
-        copyAsync(&sIm[p], gIm + off);
+    const unsigned int p0 = tilePlace(tid);
+    qreal* const gRe = re + base + tl.rowOff[tid >> nLow] + (tid & ((1u << nLow) - 1u));
+    qreal* const gIm = im + (gRe - re);
+    if (tid < nElems) {
+#pragma unroll
+        for (unsigned int j = 0; j < kTileElems / kTileThreads; ++j) {
+            if (j * kTileThreads < nElems) {
+                const unsigned long long off = tl.rowOff[(j * kTileThreads) >> nLow];
+                const unsigned int p = p0 ^ tilePlace(j * kTileThreads);  // compile-time constant per j
+                copyAsync(&sAmp[p], gRe + off);
+                copyAsync(&sAmp[kTileElems + p], gIm + off);
+            }
+        }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     // 2. which gates does this tile take part in?  (bit g of sAct; whole warps so that the ballot is defined)
     const int nGates = tl.nGates;
-    for (int g0 = (int)(tid & ~31u); g0 < nGates; g0 += kTileThreads) {
+    for (int g0 = (int)(tid & ~31u); g0 < kMaxTileGates + 64; g0 += kTileThreads) {
         const int g = g0 + (int)(tid & 31u);
         const unsigned long long m = g < nGates ? tl.outerMask[g] : ~0ull;
         const unsigned int word = __ballot_sync(0xffffffffu, g < nGates && (base & m) == m);
@@ -211,39 +304,53 @@ __global__ void __launch_bounds__(kTileThreads, QB_TILE_MINB) k_tile(qreal* __re
     const unsigned int nBlocks = nElems >> kSubBits;
     for (int s = 0; s < tl.nSub; ++s) {
         const int r0 = tl.sub[s].rb[0], r1 = tl.sub[s].rb[1], r2 = tl.sub[s].rb[2];
-        const int gFirst = tl.sub[s].first, gEnd = gFirst + tl.sub[s].count;
+        const int gFirst = tl.sub[s].first;
+        // activity of the sub-group's (at most 64) gates for this CTA, bit j = gate gFirst + j
+        unsigned long long act;
+        {
+            const int w = gFirst >> 5, sh = gFirst & 31;
+            const unsigned long long lo = sAct[w] | ((unsigned long long)sAct[w + 1] << 32);
+            act = (lo >> sh) | (sh ? ((unsigned long long)sAct[w + 2] << (64 - sh)) : 0ull);
+            const int cnt = tl.sub[s].count;
+            if (cnt < 64) act &= (1ull << cnt) - 1ull;
+        }
         for (unsigned int b = tid; b < nBlocks; b += kTileThreads) {
             const unsigned int idx = insertZero(insertZero(insertZero(b, r0), r1), r2);  // register bits at 0
-            const unsigned int p0 = tilePlace(idx);
+            const unsigned int pb = tilePlace(idx);
             qreal xr[kSubElems], xi[kSubElems];
 #pragma unroll
             for (int e = 0; e < kSubElems; ++e) {
-                const unsigned int p = p0 ^ tl.sub[s].place[e];
-                xr[e] = sRe[p];
-                xi[e] = sIm[p];
+                const qreal* at = &sAmp[pb ^ tl.sub[s].place[e]];
+                xr[e] = at[0];
+                xi[e] = at[kTileElems];
             }
-            for (int g = gFirst; g < gEnd; ++g) {
-                if (!((sAct[g >> 5] >> (g & 31)) & 1u)) continue;
-                const unsigned int tm = tl.ctl[g].tileMask;
-                if ((idx & tm) != tm) continue;
-                applyTileGate<TIER, FMA>(tl, g, tl.ctl[g].opcode, tl.ctl[g].regMask, xr, xi);
+            for (unsigned long long todo = act; todo; todo &= todo - 1ull) {
+                const int g = gFirst + __ffsll((long long)todo) - 1;
+                const TileGateCtl ctl = tl.ctl[g];
+                if ((idx & ctl.tileMask) != ctl.tileMask) continue;
+                applyTileGate<TIER, FMA>(tl, g, ctl.opcode, ctl.regMask, xr, xi);
             }
 #pragma unroll
-            for (int e = 0; e < kSubElems; ++e) {
-                const unsigned int p = p0 ^ tl.sub[s].place[e];
-                sRe[p] = xr[e];
-                sIm[p] = xi[e];
+            for (int e = 0; e < kSubElems; ++e) {  // (addresses recomputed: keeping them alive costs registers the gates need)
+                qreal* at = &sAmp[pb ^ tl.sub[s].place[e]];
+                at[0] = xr[e];
+                at[kTileElems] = xi[e];
             }
         }
         __syncthreads();
     }
 
     // 4. write the tile back
-    for (unsigned int i = tid; i < nElems; i += kTileThreads) {
-        const unsigned long long off = tl.rowOff[i >> nLow] + (i & lowMask);
-        const unsigned int p = tilePlace(i);
-        gRe[off] = sRe[p];
-        gIm[off] = sIm[p];
+    if (tid < nElems) {
+#pragma unroll
+        for (unsigned int j = 0; j < kTileElems / kTileThreads; ++j) {
+            if (j * kTileThreads < nElems) {
+                const unsigned long long off = tl.rowOff[(j * kTileThreads) >> nLow];
+                const unsigned int p = p0 ^ tilePlace(j * kTileThreads);
+                gRe[off] = sAmp[p];
+                gIm[off] = sAmp[kTileElems + p];
+            }
+        }
     }
 }
 

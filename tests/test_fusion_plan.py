@@ -48,13 +48,13 @@ def plan(lib, local_bits, ops):
 
 def decode_opcode(opcode):
     """What k_tile's single table jump selects (qb_fuse.h TileOpcode): (kind, register position, second position)."""
-    if opcode < 16:
-        return (K_MATRIX, K_HAD, K_SWAP, K_Y)[opcode // 4], opcode % 4, None
-    if opcode == 16:
+    if opcode < 12:
+        return (K_MATRIX, K_HAD, K_SWAP, K_Y)[opcode // 3], opcode % 3, None
+    if opcode == 12:
         return K_PHASE, None, None
-    if opcode == 17:
+    if opcode == 13:
         return K_FLIP, None, None
-    kind, slot = divmod(opcode - 20, 3)
+    kind, slot = divmod(opcode - 14, 3)
     return K_DEPHASE + kind, (0, 0, 1)[slot], (1, 2, 2)[slot]
 
 

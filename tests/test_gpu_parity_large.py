@@ -145,7 +145,12 @@ def test_noise_channels_on_a_14_qubit_density_matrix(product, product_env, refer
     product.lib.qb200_setFusion(fusion)
     try:
         got, want = _run_both(product, reference, gq, cq, ops)
-        np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-13)
+        # The reference adds the 2^28 squares of calcPurity sequentially per OpenMP thread (QuEST_cpu.c:854-880): 2^24
+        # terms per thread leave it up to ~2e-9 off (measured 2.4e-11), so the scalars are held to that bound against the
+        # reference and the product's purity to 1e-12 against a pairwise (numpy) sum over its own amplitudes; the
+        # amplitudes themselves must still agree bit for bit.
+        np.testing.assert_allclose(got, want, rtol=2e-9, atol=1e-13)
+        np.testing.assert_allclose(got[0], harness.sum_squares_chunked(product, gq), rtol=1e-12)
         _finish(product, product_env, reference, reference_env, gq, cq, bit_exact=True)
     finally:
         product.lib.qb200_setFusion(1)
