@@ -321,17 +321,16 @@ int preparePass(const std::vector<PendingOp>& ops, const TilePass& p) {
         TileSubDesc& d = tl.sub[s];
         d.first = sg.first - p.first;
         d.count = sg.count;
-        for (int j = 0; j < kSubBits; ++j) d.rb[j] = sg.rb[j];
-        for (int e = 0; e < kSubElems; ++e) {
-            unsigned int off = 0;
-            for (int j = 0; j < kSubBits; ++j)
-                if ((e >> j) & 1) off |= 1u << sg.rb[j];
-            d.place[e] = tilePlace(off);
-        }
+        int pos[kRegBits];  // element bit j -> tile-index position: the register bits, then the spectator bit
+        for (int j = 0; j < kSubBits; ++j) pos[j] = sg.rb[j];
+        pos[kSubBits] = sg.spect;
+        for (int j = 0; j < kRegBits; ++j) d.ins[j] = pos[j];
+        std::sort(d.ins, d.ins + kRegBits);
+        for (int j = 0; j < kRegBits; ++j) d.placeBit[j] = tilePlace(1u << pos[j]) * (unsigned int)sizeof(qreal);
         for (int k = sg.first; k < sg.first + sg.count; ++k) {
             const TileGate tg = describe(ops[k], p, sg);
             const int g = k - p.first;
-            tl.ctl[g] = TileGateCtl{(unsigned short)tg.tileMask, (unsigned char)tg.opcode, (unsigned char)tg.regMask, 0};
+            tl.ctl[g] = TileGateCtl{(unsigned short)tg.tileMask, (unsigned char)tg.opcode, (unsigned char)tg.regMask};
             tl.outerMask[g] = tg.outerMask;
             std::memcpy(tl.c[g], ops[k].c, sizeof ops[k].c);
             tier |= tierOf(tg.opcode);
@@ -344,19 +343,38 @@ int preparePass(const std::vector<PendingOp>& ops, const TilePass& p) {
             if ((r >> (j - tl.nLow)) & 1) o |= 1ull << p.tileBits[j];
         tl.rowOff[r] = o;
     }
+    for (int j = 0; j < kTileCopies; ++j) {
+        const unsigned int i = (unsigned int)j * kTileThreads;
+        tl.stepOff[j] = i < (1u << p.nTile) ? tl.rowOff[i >> tl.nLow] + (i & ((1u << tl.nLow) - 1u)) : 0;
+    }
     return tier;
 }
 
 // One launch of k_tile over the whole shard (sp == nullptr) or over slab `slab` of it.
 void launchPrepared(QuregRec* r, const TilePass& p, int tier, const SlabPlan* sp, int slab) {
-    int n = 0;
-    for (int j = 0; j < p.nTile; ++j) tl.ins[n++] = p.tileBits[j];
+    // the index bits that are neither tile bits nor slab bits, as contiguous runs fed from the CTA index
+    u64 held = 0;
+    for (int j = 0; j < p.nTile; ++j) held |= 1ull << p.tileBits[j];
     if (sp)
-        for (int j = 0; j < sp->nBits; ++j) tl.ins[n++] = sp->bits[j];
-    std::sort(tl.ins, tl.ins + n);
-    tl.nIns = n;
+        for (int j = 0; j < sp->nBits; ++j) held |= 1ull << sp->bits[j];
+    int nRuns = 0, src = 0;
+    for (int b = 0; b < r->localBits;) {
+        if ((held >> b) & 1) {
+            ++b;
+            continue;
+        }
+        int e = b;
+        while (e < r->localBits && !((held >> e) & 1)) ++e;
+        tl.runSrc[nRuns] = (unsigned char)src;
+        tl.runDst[nRuns] = (unsigned char)b;
+        tl.runLen[nRuns] = (unsigned char)(e - b);
+        src += e - b;
+        ++nRuns;
+        b = e;
+    }
+    tl.nRuns = nRuns;
     tl.slabMask = sp ? sp->valueMask(slab) : 0;
-    const unsigned int nb = (unsigned int)((u64)r->n >> n);
+    const unsigned int nb = (unsigned int)((u64)r->n >> __builtin_popcountll(held));
     if (tier == kTierNoise && g.contract)
         k_tile<kTierNoise, true><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
     else if (tier == kTierNoise)
@@ -639,7 +657,7 @@ void submit(const Qureg& q, PendingOp op) {
     }
     // registers whose device pointers were handed out run every gate at once: whoever holds the raw pointers sees the
     // amplitudes the API calls so far produce (stream-ordered), and nothing queued can overwrite what they write
-    const bool recording = g.fuse && !r->exposed && r->localBits >= kSubBits;
+    const bool recording = g.fuse && !r->exposed && r->localBits >= kRegBits;
     if (recording) {  // before any rank-dependent decision: every rank counts every gate call
         if (r->callsSinceFlush >= kQueueCap) flush(q);
         ++r->callsSinceFlush;
@@ -1565,7 +1583,7 @@ int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int l
 // Host pass-planning logic of the fusion queue, exposed for CPU-only tests (no CUDA call): plans the given gate list
 // exactly as flush() would for a shard of 2^localBits amplitudes.  Gates: kind (qb_fuse.h FusedKind), target, second target
 // (-1 if none), mask.  passesOut, per pass: first, count, nTile, nSub, tileBits[kTileBits] (= 4 + 11 ints); subsOut, per
-// sub-group in pass order: pass index, first, count, rb[3] (6 ints); descOut, per gate: opcode, regMask, tileMask, outerMask
+// sub-group in pass order: pass index, first, count, rb[3], spectator (7 ints); descOut, per gate: opcode, regMask, tileMask, outerMask
 // (4 words).  Returns the number of passes; *nSubsOut receives the number of sub-groups.
 int qb200_debugTilePlan(int localBits, int nOps, const int* kinds, const int* targets, const int* targets2,
                         const unsigned long long* masks, int* passesOut, int* subsOut, unsigned long long* descOut,
@@ -1586,9 +1604,10 @@ int qb200_debugTilePlan(int localBits, int nOps, const int* kinds, const int* ta
         o[0] = p.first; o[1] = p.count; o[2] = p.nTile; o[3] = (int)p.subs.size();
         for (int j = 0; j < kTileBits; ++j) o[4 + j] = j < p.nTile ? p.tileBits[j] : -1;
         for (const TileSub& sg : p.subs) {
-            int* so = subsOut + 6 * nSubs++;
+            int* so = subsOut + 7 * nSubs++;
             so[0] = (int)pi; so[1] = sg.first; so[2] = sg.count;
             for (int j = 0; j < kSubBits; ++j) so[3 + j] = sg.rb[j];
+            so[6] = sg.spect;
             for (int k = sg.first; k < sg.first + sg.count; ++k) {
                 const TileGate tg = describe(ops[k], p, sg);
                 unsigned long long* d = descOut + 4 * k;

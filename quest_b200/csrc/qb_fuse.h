@@ -35,10 +35,13 @@ namespace qb {
 #endif
 constexpr int kTileBits = QB_TILE_BITS;  // amplitudes staged per CTA: 2^kTileBits (2 x 16 KiB of shared memory in double)
 constexpr int kTileLow = 4;              // the lowest index bits are always tile bits: 2^4 doubles = one 128-byte line
-constexpr int kSubBits = 3;              // qubits resolved in registers per sub-group (2^3 amplitudes per thread)
+constexpr int kSubBits = 3;              // dense-target qubits resolved in registers per sub-group ...
+constexpr int kSpectBits = 1;            // ... plus one SPECTATOR tile bit no gate of the sub-group touches: a thread holds
+                                         // 2^(3+1) = 16 amplitudes and every dispatched gate body serves two 8-blocks
+constexpr int kMaxTouched = 8;           // a gate touching more index bits than this (target + controls) runs on its own
 constexpr int kMaxTileGates = 192;       // gates per pass: descriptors travel as kernel parameters (constant bank)
 constexpr int kMaxTileSubs = 64;         // sub-groups per pass
-constexpr int kMaxSubGates = 64;         // gates per sub-group: their per-CTA activity is one 64-bit word
+constexpr int kMaxSubGates = 32;         // gates per sub-group: their per-CTA activity is one 32-bit word
 constexpr int kMaxSlabBits = 3;          // a launch may be confined to the amplitudes with given values on up to 3 bits
 
 enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, kFPhase = 4, kFFlip = 5,
@@ -73,7 +76,8 @@ inline unsigned long long denseBitsOf(const PendingOp& op) {
 struct TileSub {
     int first, count;              // ops [first, first+count) of the queue
     int rb[kSubBits];              // register bits, ascending, as positions in TILE-INDEX space (bit j of a tile index
-                                   // is amplitude-index bit tileBits[j]); -1 = unused (registers of fewer than 3 qubits)
+                                   // is amplitude-index bit tileBits[j])
+    int spect;                     // spectator bit (tile-index space): no gate of the sub-group has it as target or in its mask
 };
 
 struct TilePass {
@@ -100,20 +104,33 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
         p.count = 0;
         p.nTile = T;
         p.denseMask = 0;
-        unsigned long long subDense = 0;
-        TileSub cur{i, 0, {0, 0, 0}};
+        unsigned long long subDense = 0, subTouched = 0;
+        TileSub cur{i, 0, {0, 0, 0}, 0};
         std::vector<unsigned long long> subMasks;  // dense bits of each closed sub-group (amplitude-index space)
         while (i < n && p.count < kMaxTileGates) {
             const unsigned long long need = denseBitsOf(ops[i]);
+            const unsigned long long touched = need | ops[i].mask;
+            if (__builtin_popcountll(touched) > std::min(kMaxTouched, T - 1)) {  // many-control gate: a pass of its own (single-gate kernel)
+                if (p.count) break;
+                ++cur.count;
+                ++p.count;
+                ++i;
+                break;
+            }
             if (__builtin_popcountll(p.denseMask | need | lowMask) > T) break;
-            if (__builtin_popcountll(subDense | need) > R || cur.count == kMaxSubGates) {  // the gate opens a new sub-group
+            // a sub-group ends when its dense targets exceed the register bits, when it is full, or when its gates
+            // would touch so many index bits that no tile bit is left over as the spectator
+            if (__builtin_popcountll(subDense | need) > R || cur.count == kMaxSubGates ||
+                __builtin_popcountll(subTouched | touched) > T - 1) {
                 if ((int)p.subs.size() + 1 == kMaxTileSubs) break;
                 p.subs.push_back(cur);
                 subMasks.push_back(subDense);
-                cur = TileSub{i, 0, {0, 0, 0}};
+                cur = TileSub{i, 0, {0, 0, 0}, 0};
                 subDense = 0;
+                subTouched = 0;
             }
             subDense |= need;
+            subTouched |= touched;
             p.denseMask |= need;
             ++cur.count;
             ++p.count;
@@ -164,6 +181,16 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
             for (int tp = 0; tp < T; ++tp)
                 if ((reg >> tp) & 1) sg.rb[q++] = tp;
             for (; q < kSubBits; ++q) sg.rb[q] = -1;
+            // spectator: the highest tile bit that is neither a register bit nor mentioned by any gate of the sub-group
+            unsigned int busy = reg;
+            for (int k = sg.first; k < sg.first + sg.count; ++k)
+                for (unsigned long long m = ops[k].mask; m; m &= m - 1) {
+                    const int tp = tilePosOf[__builtin_ctzll(m)];
+                    if (tp >= 0) busy |= 1u << tp;
+                }
+            sg.spect = -1;
+            for (int tp = T - 1; tp >= 0 && sg.spect < 0; --tp)
+                if (!((busy >> tp) & 1)) sg.spect = tp;
         }
         out.push_back(p);
     }

@@ -23,35 +23,40 @@
 
 namespace qb {
 
-#ifndef QB_SWAP_IMPL
-#define QB_SWAP_IMPL forEachPair  // forPairsByMask: one body per control mask - measured worse (register moves at the joins)
-#endif
-
-constexpr int kTileThreads = 256;
-constexpr int kSubElems = 1 << kSubBits;
+constexpr int kRegBits = kSubBits + kSpectBits;        // index bits a thread holds in registers
+constexpr int kSubElems = 1 << kRegBits;                // 16 amplitudes per thread
+constexpr int kTileThreads = 1 << (kTileBits - kRegBits);  // one register block per thread: 128 threads per CTA
+constexpr int kTileCopies = (1 << kTileBits) / kTileThreads;  // amplitudes per thread when staging the tile
 
 struct TileSubDesc {
-    int first, count;                  // gates [first, first + count) of the launch
-    int rb[kSubBits];                  // register bits (tile-index space, ascending)
-    unsigned int place[kSubElems];     // tilePlace() of register element e's offset from the thread's base tile index
+    int first, count;                  // gates [first, first + count) of the launch (count <= kMaxSubGates)
+    int ins[kRegBits];                 // register bits + spectator bit (tile-index space), ascending: held at 0 in a thread's base index
+    unsigned int placeBit[kRegBits];   // BYTE offset in shared memory, as an XOR term, of bit j of the register element index
+                                       // (bits 0..2 = the register bits in ascending order, bit 3 = the spectator bit):
+                                       // sizeof(qreal) * tilePlace(1 << position); placement is linear, so element e sits at
+                                       // the XOR of the terms of its set bits with the thread's base placement
 };
 
-struct TileGateCtl {                   // 8 bytes: one constant-bank load per gate
+struct TileGateCtl {                   // 4 bytes: one constant-bank load per gate
     unsigned short tileMask;           // selecting bits among the tile bits that are not register bits (tile-index space)
     unsigned char opcode;
     unsigned char regMask;
-    unsigned int pad_;
 };
 static_assert(kTileBits <= 16, "tileMask is 16 bits wide");
+
+constexpr int kMaxRuns = kTileBits + kMaxSlabBits + 1;
 
 struct TileLaunch {
     int nTile;                         // tile bits of this pass (<= kTileBits)
     int nLow;                          // min(kTileLow, nTile): tile-index bits [0, nLow) are amplitude-index bits [0, nLow)
     int nSub, nGates;
-    int nIns;                          // tile bits + slab bits: positions held out of the CTA index ...
-    int ins[kTileBits + kMaxSlabBits]; // ... ascending
+    // CTA index -> tile base: the index bits that are neither tile bits nor slab bits form nRuns contiguous runs; run i
+    // takes runLen[i] bits of the CTA index (from bit runSrc[i]) to amplitude-index bit runDst[i]
+    int nRuns;
+    unsigned char runSrc[kMaxRuns], runDst[kMaxRuns], runLen[kMaxRuns];
     unsigned long long slabMask;       // value of the slab bits for this launch (0 for a whole-shard pass)
     unsigned long long rowOff[1 << (kTileBits - kTileLow)];  // amplitude offset of tile index (r << nLow) from the tile base
+    unsigned long long stepOff[kTileCopies];                 // amplitude offset of tile index j * kTileThreads
     TileSubDesc sub[kMaxTileSubs];
     TileGateCtl ctl[kMaxTileGates];
     unsigned long long outerMask[kMaxTileGates];  // control/selecting bits outside the tile
@@ -110,34 +115,9 @@ __device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 <
     for (int e = 0; e < (1 << R); ++e)
         if ((e & MASK) == MASK) fn(xr[e], xi[e]);
 }
-// Pair operations whose control mask is switched on (swap: a handful of register moves per pair, which the compiler
-// would otherwise predicate - executing all of them for every gate).  MASK never contains bit P.
-template <int P, int MASK, int R, class PairFn>
-__device__ __forceinline__ void forMaskedPairs(qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
-#pragma unroll
-    for (int e = 0; e < (1 << R); ++e) {
-        if ((e >> P) & 1) continue;
-        if ((e & MASK) == MASK) fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
-    }
-}
-template <int P, int R, class PairFn>
-__device__ __forceinline__ void forPairsByMask(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
-    static_assert(R == 3, "eight register masks");
-    switch (regMask) {
-        case 0: forMaskedPairs<P, 0, R>(xr, xi, fn); break;
-        case 1: forMaskedPairs<P, 1 & ~(1 << P), R>(xr, xi, fn); break;
-        case 2: forMaskedPairs<P, 2 & ~(1 << P), R>(xr, xi, fn); break;
-        case 3: forMaskedPairs<P, 3 & ~(1 << P), R>(xr, xi, fn); break;
-        case 4: forMaskedPairs<P, 4 & ~(1 << P), R>(xr, xi, fn); break;
-        case 5: forMaskedPairs<P, 5 & ~(1 << P), R>(xr, xi, fn); break;
-        case 6: forMaskedPairs<P, 6 & ~(1 << P), R>(xr, xi, fn); break;
-        default: forMaskedPairs<P, 7 & ~(1 << P), R>(xr, xi, fn); break;
-    }
-}
-
 template <int R, class ElemFn>
 __device__ __forceinline__ void forSelectedByMask(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, ElemFn fn) {
-    static_assert(R == 3, "eight register masks");
+    static_assert(kSubBits == 3, "eight register masks: the spectator bit is never part of a mask");
     switch (regMask) {
         case 0: forSelected<0, R>(xr, xi, fn); break;
         case 1: forSelected<1, R>(xr, xi, fn); break;
@@ -189,9 +169,9 @@ enum TileTier : int { kTierGates = 0,   // every state-vector gate
     case (BASE) + 1: { constexpr int P = 1; __VA_ARGS__; } break;      \
     case (BASE) + 2: { constexpr int P = 2; __VA_ARGS__; } break;
 #define QB_NOISE3(KIND)                                                                                             \
-    case kOpNoise + ((KIND) - kFDephase) * 3 + 0: noiseQuads<KIND, 0, 1, kSubBits>(xr, xi, C(0), C(1), C(2)); break; \
-    case kOpNoise + ((KIND) - kFDephase) * 3 + 1: noiseQuads<KIND, 0, 2, kSubBits>(xr, xi, C(0), C(1), C(2)); break; \
-    case kOpNoise + ((KIND) - kFDephase) * 3 + 2: noiseQuads<KIND, 1, 2, kSubBits>(xr, xi, C(0), C(1), C(2)); break;
+    case kOpNoise + ((KIND) - kFDephase) * 3 + 0: noiseQuads<KIND, 0, 1, kRegBits>(xr, xi, C(0), C(1), C(2)); break; \
+    case kOpNoise + ((KIND) - kFDephase) * 3 + 1: noiseQuads<KIND, 0, 2, kRegBits>(xr, xi, C(0), C(1), C(2)); break; \
+    case kOpNoise + ((KIND) - kFDephase) * 3 + 2: noiseQuads<KIND, 1, 2, kRegBits>(xr, xi, C(0), C(1), C(2)); break;
 
 // One recorded gate on the 8 amplitudes a thread holds in registers: a single jump on the host-made opcode into code
 // for that (kind, register position).  Coefficients come straight from the constant bank (kernel parameters).
@@ -204,14 +184,14 @@ __device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int o
     switch (opcode) {
         QB_POS3(kOpMatrix, {
             const Matrix m{C(0), C(1), C(2), C(3), C(4), C(5), C(6), C(7)};
-            if (regMask == 0) forEveryPair<P, kSubBits>(xr, xi, m);
-            else forEachPair<P, kSubBits>(xr, xi, regMask, m);
+            if (regMask == 0) forEveryPair<P, kRegBits>(xr, xi, m);
+            else forEachPair<P, kRegBits>(xr, xi, regMask, m);
         })
-        QB_POS3(kOpHadamard, forEveryPair<P, kSubBits>(xr, xi, OpHadamard{C(0)}))  // the API has no controlled hadamard
-        QB_POS3(kOpSwap, QB_SWAP_IMPL<P, kSubBits>(xr, xi, regMask, OpSwap{}))
-        QB_POS3(kOpPauliY, forEachPair<P, kSubBits>(xr, xi, regMask, OpPauliY{C(0)}))
-        case kOpPhase: forSelectedByMask<kSubBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
-        case kOpFlip: forSelectedByMask<kSubBits>(xr, xi, regMask, DiagFlip{}); break;
+        QB_POS3(kOpHadamard, forEveryPair<P, kRegBits>(xr, xi, OpHadamard{C(0)}))  // the API has no controlled hadamard
+        QB_POS3(kOpSwap, forEachPair<P, kRegBits>(xr, xi, regMask, OpSwap{}))
+        QB_POS3(kOpPauliY, forEachPair<P, kRegBits>(xr, xi, regMask, OpPauliY{C(0)}))
+        case kOpPhase: forSelectedByMask<kRegBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
+        case kOpFlip: forSelectedByMask<kRegBits>(xr, xi, regMask, DiagFlip{}); break;
         default:
             if constexpr (TIER == kTierNoise) {
                 switch (opcode) {
@@ -240,38 +220,36 @@ __device__ __forceinline__ void copyAsync(qreal* smemDst, const qreal* src) {
         asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src) : "memory");
 }
 
+__host__ __device__ constexpr int lowestSetBit(int e) { return (e & 1) ? 0 : (e & 2) ? 1 : (e & 4) ? 2 : 3; }
+
 __device__ __forceinline__ unsigned int insertZero(unsigned int k, int b) {
     const unsigned int low = k & ((1u << b) - 1u);
     return ((k >> b) << (b + 1)) | low;
 }
 
 #ifndef QB_TILE_MINB
-#define QB_TILE_MINB 3
+#define QB_TILE_MINB 4
 #endif
 
 template <int TIER, bool FMA>
 __global__ void __launch_bounds__(kTileThreads, QB_TILE_MINB) k_tile(qreal* __restrict__ re, qreal* __restrict__ im,
                                                                    const __grid_constant__ TileLaunch tl) {
     constexpr unsigned int kTileElems = 1u << kTileBits;
-    __shared__ qreal sAmp[2 * kTileElems];  // real parts, then imaginary parts: one address register serves both
-    __shared__ unsigned int sAct[kMaxTileGates / 32 + 2];
+    __shared__ qreal sAmp[2 * kTileElems];          // real parts, then imaginary parts: one address register serves both
+    __shared__ unsigned int sSubAct[kMaxTileSubs];  // per sub-group: which of its gates this tile takes part in
     const unsigned int tid = threadIdx.x;
 
     // tile base: this CTA's amplitude index with the tile bits at 0 (and the slab bits at their fixed value)
-    unsigned long long k = blockIdx.x;
-#pragma unroll
-    for (int j = 0; j < kTileBits + kMaxSlabBits; ++j) {
-        if (j < tl.nIns) {
-            const int b = tl.ins[j];
-            const unsigned long long low = k & ((1ull << b) - 1ull);
-            k = ((k >> b) << (b + 1)) | low;
-        }
+    unsigned long long base = tl.slabMask;
+    {
+        const unsigned long long k = blockIdx.x;
+        for (int i = 0; i < tl.nRuns; ++i)
+            base |= ((k >> tl.runSrc[i]) & ((1ull << tl.runLen[i]) - 1ull)) << tl.runDst[i];
     }
-    const unsigned long long base = k | tl.slabMask;
 
     // 1. stage the tile: consecutive threads take consecutive amplitudes of a row.  Thread t copies tile indices
-    // t, t + 256, t + 512, ...: both the amplitude offset and the shared-memory placement are linear in the index, so
-    // index t + 256 j costs one add / one xor on top of what index t needs (rowOff is indexed by tile index >> nLow).
+    // t, t + 128, t + 256, ...: both the amplitude offset and the shared-memory placement are linear in the index, so
+    // index t + 128 j costs one add / one xor (with constants) on top of what index t needs.
     const unsigned int nElems = 1u << tl.nTile;
     const int nLow = tl.nLow;
     const unsigned int p0 = tilePlace(tid);
@@ -279,62 +257,74 @@ __global__ void __launch_bounds__(kTileThreads, QB_TILE_MINB) k_tile(qreal* __re
     qreal* const gIm = im + (gRe - re);
     if (tid < nElems) {
 #pragma unroll
-        for (unsigned int j = 0; j < kTileElems / kTileThreads; ++j) {
+        for (unsigned int j = 0; j < kTileCopies; ++j) {
             if (j * kTileThreads < nElems) {
-                const unsigned long long off = tl.rowOff[(j * kTileThreads) >> nLow];
                 const unsigned int p = p0 ^ tilePlace(j * kTileThreads);  // compile-time constant per j
-                copyAsync(&sAmp[p], gRe + off);
-                copyAsync(&sAmp[kTileElems + p], gIm + off);
+                copyAsync(&sAmp[p], gRe + tl.stepOff[j]);
+                copyAsync(&sAmp[kTileElems + p], gIm + tl.stepOff[j]);
             }
         }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
-    // 2. which gates does this tile take part in?  (bit g of sAct; whole warps so that the ballot is defined)
-    const int nGates = tl.nGates;
-    for (int g0 = (int)(tid & ~31u); g0 < kMaxTileGates + 64; g0 += kTileThreads) {
-        const int g = g0 + (int)(tid & 31u);
-        const unsigned long long m = g < nGates ? tl.outerMask[g] : ~0ull;
-        const unsigned int word = __ballot_sync(0xffffffffu, g < nGates && (base & m) == m);
-        if ((tid & 31u) == 0) sAct[g0 >> 5] = word;
+    // 2. which gates does this tile take part in?  One 32-bit word per sub-group (bit j = its j-th gate): controls and
+    // phase-mask bits outside the tile are the same for every amplitude of the tile.  Warp w serves sub-groups w, w+4, ...
+    for (int s = (int)(tid >> 5); s < tl.nSub; s += kTileThreads / 32) {
+        const int j = (int)(tid & 31u);
+        const bool mine = j < tl.sub[s].count;
+        const unsigned long long m = mine ? tl.outerMask[tl.sub[s].first + j] : ~0ull;
+        const unsigned int word = __ballot_sync(0xffffffffu, mine && (base & m) == m);
+        if (j == 0) sSubAct[s] = word;
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
     // 3. the sub-groups
-    const unsigned int nBlocks = nElems >> kSubBits;
+    const unsigned int nBlocks = nElems >> kRegBits;
     for (int s = 0; s < tl.nSub; ++s) {
-        const int r0 = tl.sub[s].rb[0], r1 = tl.sub[s].rb[1], r2 = tl.sub[s].rb[2];
-        const int gFirst = tl.sub[s].first;
-        // activity of the sub-group's (at most 64) gates for this CTA, bit j = gate gFirst + j
-        unsigned long long act;
-        {
-            const int w = gFirst >> 5, sh = gFirst & 31;
-            const unsigned long long lo = sAct[w] | ((unsigned long long)sAct[w + 1] << 32);
-            act = (lo >> sh) | (sh ? ((unsigned long long)sAct[w + 2] << (64 - sh)) : 0ull);
-            const int cnt = tl.sub[s].count;
-            if (cnt < 64) act &= (1ull << cnt) - 1ull;
-        }
-        for (unsigned int b = tid; b < nBlocks; b += kTileThreads) {
-            const unsigned int idx = insertZero(insertZero(insertZero(b, r0), r1), r2);  // register bits at 0
-            const unsigned int pb = tilePlace(idx);
+        const TileSubDesc& sg = tl.sub[s];
+        const int gFirst = sg.first;
+        const unsigned int act = sSubAct[s];
+        if (tid < nBlocks && act != 0u) {
+            // this thread's block: the register and spectator bits of its base tile index are 0
+            const unsigned int idx = insertZero(insertZero(insertZero(insertZero(tid, sg.ins[0]), sg.ins[1]), sg.ins[2]), sg.ins[3]);
+            const unsigned int pb = tilePlace(idx) * (unsigned int)sizeof(qreal);
+            char* const sBase = reinterpret_cast<char*>(sAmp);
+            constexpr unsigned int kImag = kTileElems * sizeof(qreal);
             qreal xr[kSubElems], xi[kSubElems];
+            {
+                unsigned int q[kSubElems];
+                q[0] = pb;
 #pragma unroll
-            for (int e = 0; e < kSubElems; ++e) {
-                const qreal* at = &sAmp[pb ^ tl.sub[s].place[e]];
-                xr[e] = at[0];
-                xi[e] = at[kTileElems];
-            }
-            for (unsigned long long todo = act; todo; todo &= todo - 1ull) {
-                const int g = gFirst + __ffsll((long long)todo) - 1;
-                const TileGateCtl ctl = tl.ctl[g];
-                if ((idx & ctl.tileMask) != ctl.tileMask) continue;
-                applyTileGate<TIER, FMA>(tl, g, ctl.opcode, ctl.regMask, xr, xi);
-            }
+                for (int e = 1; e < kSubElems; ++e) q[e] = q[e & (e - 1)] ^ sg.placeBit[lowestSetBit(e)];
 #pragma unroll
-            for (int e = 0; e < kSubElems; ++e) {  // (addresses recomputed: keeping them alive costs registers the gates need)
-                qreal* at = &sAmp[pb ^ tl.sub[s].place[e]];
-                at[0] = xr[e];
-                at[kTileElems] = xi[e];
+                for (int e = 0; e < kSubElems; ++e) {
+                    xr[e] = *reinterpret_cast<const qreal*>(sBase + q[e]);
+                    xi[e] = *reinterpret_cast<const qreal*>(sBase + q[e] + kImag);
+                }
+            }
+            // gate loop: the control word of the next gate is fetched while the current gate computes
+            unsigned int todo = act;
+            int g = gFirst + __ffs((int)todo) - 1;
+            TileGateCtl ctl = tl.ctl[g];
+            while (true) {
+                todo &= todo - 1u;
+                const int gNext = todo ? gFirst + __ffs((int)todo) - 1 : g;
+                const TileGateCtl next = tl.ctl[gNext];
+                if ((idx & ctl.tileMask) == ctl.tileMask) applyTileGate<TIER, FMA>(tl, g, ctl.opcode, ctl.regMask, xr, xi);
+                if (!todo) break;
+                g = gNext;
+                ctl = next;
+            }
+            {  // (addresses recomputed: keeping them alive costs registers the gates need)
+                unsigned int q[kSubElems];
+                q[0] = pb;
+#pragma unroll
+                for (int e = 1; e < kSubElems; ++e) q[e] = q[e & (e - 1)] ^ sg.placeBit[lowestSetBit(e)];
+#pragma unroll
+                for (int e = 0; e < kSubElems; ++e) {
+                    *reinterpret_cast<qreal*>(sBase + q[e]) = xr[e];
+                    *reinterpret_cast<qreal*>(sBase + q[e] + kImag) = xi[e];
+                }
             }
         }
         __syncthreads();
@@ -343,12 +333,11 @@ __global__ void __launch_bounds__(kTileThreads, QB_TILE_MINB) k_tile(qreal* __re
     // 4. write the tile back
     if (tid < nElems) {
 #pragma unroll
-        for (unsigned int j = 0; j < kTileElems / kTileThreads; ++j) {
+        for (unsigned int j = 0; j < kTileCopies; ++j) {
             if (j * kTileThreads < nElems) {
-                const unsigned long long off = tl.rowOff[(j * kTileThreads) >> nLow];
                 const unsigned int p = p0 ^ tilePlace(j * kTileThreads);
-                gRe[off] = sAmp[p];
-                gIm[off] = sAmp[kTileElems + p];
+                gRe[tl.stepOff[j]] = sAmp[p];
+                gIm[tl.stepOff[j]] = sAmp[kTileElems + p];
             }
         }
     }

@@ -14,7 +14,7 @@ import pytest
 from quest_b200 import capi
 
 K_MATRIX, K_HAD, K_SWAP, K_Y, K_PHASE, K_FLIP, K_DEPHASE, K_DEPOL, K_DAMP = range(9)
-TILE_BITS, TILE_LOW, SUB_BITS, MAX_GATES = 11, 4, 3, 192
+TILE_BITS, TILE_LOW, SUB_BITS, MAX_GATES, MAX_SUB_GATES = 11, 4, 3, 192, 32
 
 
 def _lib():
@@ -33,7 +33,7 @@ def plan(lib, local_bits, ops):
     targets2 = (ctypes.c_int * n)(*[o[3] if len(o) > 3 else -1 for o in ops])
     masks = (ctypes.c_ulonglong * n)(*[o[2] for o in ops])
     passes = (ctypes.c_int * ((4 + TILE_BITS) * n))()
-    subs = (ctypes.c_int * (6 * n))()
+    subs = (ctypes.c_int * (7 * n))()
     desc = (ctypes.c_ulonglong * (4 * n))()
     n_subs = ctypes.c_int()
     np_ = lib.qb200_debugTilePlan(local_bits, n, kinds, targets, targets2, masks, passes, subs, desc, ctypes.byref(n_subs))
@@ -41,7 +41,8 @@ def plan(lib, local_bits, ops):
     pl = [dict(first=passes[W * i], count=passes[W * i + 1], ntile=passes[W * i + 2], nsub=passes[W * i + 3],
                bits=[b for b in passes[W * i + 4:W * i + W] if b >= 0], subs=[]) for i in range(np_)]
     for j in range(n_subs.value):
-        pl[subs[6 * j]]["subs"].append(dict(first=subs[6 * j + 1], count=subs[6 * j + 2], rb=list(subs[6 * j + 3:6 * j + 6])))
+        pl[subs[7 * j]]["subs"].append(dict(first=subs[7 * j + 1], count=subs[7 * j + 2], rb=list(subs[7 * j + 3:7 * j + 6]),
+                                            spect=subs[7 * j + 6]))
     dl = [dict(opcode=desc[4 * i], reg=desc[4 * i + 1], tile=desc[4 * i + 2], outer=desc[4 * i + 3]) for i in range(n)]
     return pl, dl
 
@@ -98,9 +99,15 @@ def apply_pass(state, ops, p, descs, mats):
     assert all(bits[j] == j for j in range(min(TILE_LOW, T)))  # rows of the tile are contiguous in memory
     tile = state[bases[:, None] + dep[None, :]]  # [CTAs, 2^T]
     for sg in p["subs"]:
-        rb = sg["rb"]
-        assert rb == sorted(rb) and all(0 <= r < T for r in rb)
-        blocks = insert_zeros(np.arange((1 << T) >> SUB_BITS, dtype=np.int64), rb)
+        rb, spect = sg["rb"], sg["spect"]
+        assert rb == sorted(rb) and all(0 <= r < T for r in rb) and 0 <= spect < T and spect not in rb
+        assert sg["count"] <= MAX_SUB_GATES
+        # a thread holds the 16 elements spanned by the register bits and the spectator bit; no gate of the sub-group may
+        # mention the spectator bit (both 8-element halves run exactly the same gates)
+        for k in range(sg["first"], sg["first"] + sg["count"]):
+            assert not (descs[k]["tile"] >> spect) & 1
+        blocks = insert_zeros(np.arange((1 << T) >> (SUB_BITS + 1), dtype=np.int64), rb + [spect])
+        blocks = np.concatenate([blocks, blocks | (1 << spect)])  # the two halves, as two 8-element blocks
         off = np.array([sum(((e >> j) & 1) << rb[j] for j in range(SUB_BITS)) for e in range(1 << SUB_BITS)], dtype=np.int64)
         for k in range(sg["first"], sg["first"] + sg["count"]):
             d, u = descs[k], mats[k]
@@ -150,7 +157,7 @@ def dense_bits(op):
     return {op[1]} | ({op[3]} if len(op) > 3 else set())
 
 
-@pytest.mark.parametrize("local_bits,seed,noise", [(3, 1, False), (4, 2, False), (5, 3, True), (7, 4, False), (10, 5, True),
+@pytest.mark.parametrize("local_bits,seed,noise", [(4, 1, False), (4, 2, False), (5, 3, True), (7, 4, False), (10, 5, True),
                                                    (12, 6, False), (14, 7, True), (16, 8, False)])
 def test_planned_passes_reproduce_gate_by_gate(local_bits, seed, noise):
     lib = _lib()
@@ -178,6 +185,10 @@ def test_planned_passes_reproduce_gate_by_gate(local_bits, seed, noise):
     for p, nxt in zip(passes, passes[1:]):
         if p["count"] == MAX_GATES or len(p["subs"]) == 64:
             continue
+        # a gate that touches more index bits than min(8, T - 1) leaves no spectator bit: it is a pass of its own
+        loner = lambda op: len(dense_bits(op)) + bin(op[2]).count("1") > min(8, T - 1)
+        if loner(ops[nxt["first"]]) or (p["count"] == 1 and loner(ops[p["first"]])):
+            continue
         dense = set().union(*[dense_bits(ops[i]) for i in range(p["first"], p["first"] + p["count"])])
         assert len(dense | low | dense_bits(ops[nxt["first"]])) > T
     state = nrng.standard_normal(1 << local_bits) + 1j * nrng.standard_normal(1 << local_bits)
@@ -186,7 +197,10 @@ def test_planned_passes_reproduce_gate_by_gate(local_bits, seed, noise):
         apply_unfused(want, op, u)
     got = state.copy()
     for p in passes:
-        apply_pass(got, ops, p, descs, mats)
+        if p["count"] == 1:  # flush() runs one-gate passes through the single-gate kernels
+            apply_unfused(got, ops[p["first"]], mats[p["first"]])
+        else:
+            apply_pass(got, ops, p, descs, mats)
     np.testing.assert_allclose(got, want, atol=1e-12)
 
 
