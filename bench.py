@@ -531,22 +531,44 @@ def main():
             step()
             return lib.calcTotalProb(q)
 
-        e2e_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            prob = e2e_step()
-        barrier()
-        dt = time.perf_counter() - t0
-        if world > 1:
-            tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            dt = float(tt.item())
-        assert abs(prob - 1.0) < 1e-9, prob
+        def timed_e2e():
+            e2e_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                prob = e2e_step()
+            barrier()
+            dt = time.perf_counter() - t0
+            if world > 1:
+                tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                dt = float(tt.item())
+            assert abs(prob - 1.0) < 1e-9, prob
+            return dt
+
+        # reference semantics first: setAmps complete on return (the GPU idles during the PCIe transfer) ...
+        dt_blocking = timed_e2e()
+        # ... then the library's deferred upload (quest_b200.h: qb200_setDeferredUpload): the same setAmps call returns once
+        # the copies are enqueued and the first passes follow the upload slab by slab; one GPU only
+        lib.lib.qb200_setDeferredUpload.argtypes = [ctypes.c_int]
+        lib.lib.qb200_getPassesUnderUploadCount.restype = ctypes.c_ulonglong
+        deferred = world == 1
+        dt = dt_blocking
+        under = 0
+        if deferred:
+            lib.lib.qb200_setDeferredUpload(1)
+            u0 = lib.lib.qb200_getPassesUnderUploadCount()
+            dt = timed_e2e()
+            under = int(lib.lib.qb200_getPassesUnderUploadCount() - u0)
+            lib.lib.qb200_setDeferredUpload(0)
         e2e = {"value": world * gates / dt, "unit": "gates/s", "h2d_bytes_per_step": 16 * n_local * world,
                "d2h_bytes_per_step": 8 * world, "ms_per_step": 1e3 * dt / args.steps,
                "what": "setAmps(shard from pinned host) + the step's gate calls + calcTotalProb per step, host wall "
-                       "clock, max over ranks"}
+                       "clock, max over ranks" + ("; qb200_setDeferredUpload(1): the upload is cut into 8 slabs and the "
+                       "leading passes follow it slab by slab" if deferred else ""),
+               "passes_under_upload_per_step": under / (args.steps + 1) if deferred else 0,
+               "blocking_setAmps": {"value": world * gates / dt_blocking, "ms_per_step": 1e3 * dt_blocking / args.steps,
+                                    "what": "the same with setAmps complete on return (reference semantics)"}}
         del re, im
     lib.destroyQureg(q, env)
 

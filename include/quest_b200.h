@@ -58,6 +58,19 @@ unsigned long long qb200_getOverlappedExchangeCount(void);
  * (two plain cudaMemcpy). */
 unsigned long long qb200_getPipelinedTransferCount(void);
 
+/* Deferred uploads (off by default; single-GPU registers).  The reference's setAmps / initStateFromAmps are complete on
+ * return (QuEST_gpu.cu:34-44: two blocking cudaMemcpy), which leaves the GPU idle for the whole PCIe transfer - 0.3 s for
+ * a 30-qubit state.  With qb200_setDeferredUpload(1) a call that overwrites the WHOLE register from PINNED host memory
+ * returns as soon as the copies are enqueued (eight slabs on a copy stream); gate calls made afterwards are recorded as
+ * usual, and when they are executed the leading passes follow the upload slab by slab, so the transfer and the
+ * arithmetic overlap.  The price: the caller must not modify or free the host arrays before the next synchronising
+ * call (any value-returning call such as calcTotalProb / getAmp / measure, or syncQuESTEnv).  Transfers that do not
+ * qualify (pageable memory, partial ranges, small or sharded registers) are copied the blocking way as before.
+ * The counters report how many uploads were deferred and how many passes ran underneath one. */
+void qb200_setDeferredUpload(int enabled);
+unsigned long long qb200_getDeferredUploadCount(void);
+unsigned long long qb200_getPassesUnderUploadCount(void);
+
 /* Arithmetic of the fused pass.  0 (default): every product and sum is rounded separately, exactly as the reference's
  * CPU build does (gcc without FMA), so amplitudes are bit-identical to it.  1 (or QUEST_B200_FMA=1): products feeding
  * a sum may be contracted into fused multiply-adds - fewer fp64 instructions per gate, results within an ulp or two

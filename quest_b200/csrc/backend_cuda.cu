@@ -87,6 +87,12 @@ struct Engine {
     void* pendingReg = nullptr;     // register whose last exchange the engine stream has not waited for yet ...
     SlabPlan pendingPlan{0, {0, 0, 0}};  // ... and how it was cut
     unsigned long long overlapped = 0;
+    // deferred uploads (qb200_setDeferredUpload): a whole-register setAmps from pinned memory is cut into slabs on the
+    // copy stream and returns at once; the first passes recorded afterwards follow it slab by slab
+    bool deferUpload = false;
+    cudaStream_t copy = nullptr;
+    cudaEvent_t upEv[8] = {};
+    unsigned long long deferredUploads = 0, passesUnderUpload = 0;
     bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fusedEvents;
 } g;
@@ -108,6 +114,8 @@ struct QuregRec {
     int probQueries = 0;
     double probZero[64];
     QubitMap map;                  // where each logical qubit lives (qb_plan.h); identity unless sharded
+    bool uploading = false;        // a deferred upload of this register is in flight on the copy stream, cut along ...
+    SlabPlan uploadPlan{0, {0, 0, 0}};  // ... these bits; slab s is in place once g.upEv[s] has happened
 };
 
 std::vector<QuregRec*> liveRegisters;  // for syncQuESTEnv / qb200_setFusion: every queue must be drainable
@@ -459,10 +467,48 @@ void exchangeSlots(const Qureg& q, SlotSwap sw);
 
 // Execute everything recorded for this register: single gates through their own kernel, runs of gates through
 // k_tile (one HBM pass per planned pass, qb_fuse.h).
+// The engine stream catches up with a deferred upload of this register (everything enqueued afterwards sees the data).
+void settleUpload(QuregRec* r) {
+    if (!r->uploading) return;
+    for (int s = 0; s < (1 << r->uploadPlan.nBits); ++s) CUDA_OK(cudaStreamWaitEvent(g.stream, g.upEv[s], 0));
+    r->uploading = false;
+}
+
+// Recorded gates behind a deferred upload: the leading passes that do not touch the slab bits run slab by slab, each
+// slab as soon as its part of the state has arrived over PCIe - the upload and those passes overlap.
+void flushBehindUpload(const Qureg& q) {
+    QuregRec* r = rec(q);
+    std::vector<PendingOp> ops;
+    ops.swap(r->queue);
+    const SlabPlan sp = r->uploadPlan;
+    const std::vector<TilePass> passes = planPasses(ops, r->localBits, bitsOf(sp));
+    size_t nFollow = 0;
+    while (nFollow < passes.size() && passes[nFollow].count > 1 && !(bitsOf(passes[nFollow]) & bitsOf(sp))) ++nFollow;
+    for (int s = 0; s < (1 << sp.nBits); ++s) {
+        CUDA_OK(cudaStreamWaitEvent(g.stream, g.upEv[s], 0));
+        for (size_t i = 0; i < nFollow; ++i) {
+            const int tier = preparePass(ops, passes[i]);
+            launchPrepared(r, passes[i], tier, &sp, s);
+        }
+    }
+    r->uploading = false;
+    for (size_t i = 0; i < nFollow; ++i) {
+        ++g.fusedLaunches;
+        ++g.passesUnderUpload;
+        g.fusedGates += passes[i].count;
+    }
+    for (size_t i = nFollow; i < passes.size(); ++i) runPass(q, ops, passes[i]);
+}
+
 void flush(const Qureg& q) {
     QuregRec* r = rec(q);
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
+    if (r->uploading) {
+        if (r->queue.empty()) settleUpload(r);
+        else flushBehindUpload(q);
+        return;
+    }
     const bool pending = g.pendingReg == r;
     if (r->queue.empty()) {
         if (pending) settle();
@@ -487,7 +533,7 @@ void flush(const Qureg& q) {
 
 void flushAll() {
     for (QuregRec* r : liveRegisters) {
-        if (r->queue.empty()) continue;
+        if (r->queue.empty() && !r->uploading) continue;
         Qureg q;
         std::memset(&q, 0, sizeof q);
         q.pairStateVec.real = reinterpret_cast<qreal*>(r);
@@ -622,6 +668,7 @@ inline QuregRec* canon(const Qureg& q) {
 inline QuregRec* fresh(const Qureg& q) {
     QuregRec* r = rec(q);
     if (g.pendingReg == r) settle();
+    settleUpload(r);
     dirty(r);
     r->queue.clear();
     r->callsSinceFlush = 0;
@@ -666,6 +713,7 @@ void submit(const Qureg& q, PendingOp op) {
             if (op.target2 >= 0 && op.target2 < r->localBits) r->denseSinceFlush |= 1ull << op.target2;
         }
     }
+    if (!recording) settleUpload(r);
     if (!qb::localiseControls(r->localBits, q.chunkId, op.mask)) return;
     if (isNoise(op.kind) && (op.target >= r->localBits || op.target2 >= r->localBits))
         comm::unsupported("one-qubit noise on a qubit that selects the shard (with QUEST_B200_REMAP=0)");
@@ -827,6 +875,42 @@ double probOfZero(const Qureg& q, int tLogical) {
     return s;
 }
 
+bool isPinnedHost(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+// Deferred upload (opt-in, qb200_setDeferredUpload): the whole shard, from pinned host memory, goes out as 8 slabs (cut
+// along the three highest index bits) on the copy stream and the call returns at once; slab s is announced by g.upEv[s].
+// The caller must leave the host arrays alone until the next call that synchronises (any value-returning call,
+// syncQuESTEnv).  Returns false when the transfer does not qualify (the caller then copies the usual, blocking way).
+bool uploadDeferred(QuregRec* r, idx_t lo, idx_t hi, const qreal* reals, const qreal* imags) {
+    if (!g.deferUpload || g.world > 1 || lo != 0 || hi != r->n || r->localBits < 24) return false;
+    if (!isPinnedHost(reals) || !isPinnedHost(imags)) return false;
+    if (!g.copy) {
+        CUDA_OK(cudaStreamCreateWithFlags(&g.copy, cudaStreamNonBlocking));
+        for (cudaEvent_t& e : g.upEv) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    // the copy stream must not overtake what the engine stream still does to this register
+    cudaEvent_t now = g.upEv[7];
+    CUDA_OK(cudaEventRecord(now, g.stream));
+    CUDA_OK(cudaStreamWaitEvent(g.copy, now, 0));
+    r->uploadPlan = SlabPlan{3, {r->localBits - 3, r->localBits - 2, r->localBits - 1}};
+    const idx_t slab = r->n >> 3;
+    for (int s = 0; s < 8; ++s) {
+        CUDA_OK(cudaMemcpyAsync(r->re + s * slab, reals + s * slab, slab * sizeof(qreal), cudaMemcpyHostToDevice, g.copy));
+        CUDA_OK(cudaMemcpyAsync(r->im + s * slab, imags + s * slab, slab * sizeof(qreal), cudaMemcpyHostToDevice, g.copy));
+        CUDA_OK(cudaEventRecord(g.upEv[s], g.copy));
+    }
+    r->uploading = true;
+    ++g.deferredUploads;
+    return true;
+}
+
 double densDiagSum(const Qureg& q, int bit) {
     QuregRec* r = canon(q);
     const u64 dim = 1ull << q.numQubitsRepresented;
@@ -933,6 +1017,11 @@ void destroyQuESTEnv(QuESTEnv env) {
         for (cudaEvent_t e : g.xDone) cudaEventDestroy(e);
         cudaEventDestroy(g.commDone);
     }
+    if (g.copy) {
+        CUDA_OK(cudaStreamSynchronize(g.copy));
+        cudaStreamDestroy(g.copy);
+        for (cudaEvent_t e : g.upEv) cudaEventDestroy(e);
+    }
     if (g.world > 1) comm::shutdown();
     io::release();
     cudaFree(g.dPartials);
@@ -1030,6 +1119,7 @@ void statevec_destroyQureg(Qureg qureg, QuESTEnv env) {
     if (!r) return;
     r->queue.clear();  // gates never observed need not run
     if (g.pendingReg == r) settle();
+    settleUpload(r);
     liveRegisters.erase(std::remove(liveRegisters.begin(), liveRegisters.end(), r), liveRegisters.end());
     CUDA_OK(cudaStreamSynchronize(g.stream));
     if (g.world > 1) comm::unregisterShard(qureg);
@@ -1046,11 +1136,20 @@ void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, i
     idx_t lo = std::max<idx_t>(startInd - off, 0), hi = std::min<idx_t>(startInd - off + numAmps, r->n);
     if (hi > lo) {
         const idx_t src = lo + off - startInd;
+        if (uploadDeferred(r, lo, hi, reals + src, imags + src)) return;
         io::upload(r->re + lo, reals + src, (hi - lo) * sizeof(qreal), g.stream);
         io::upload(r->im + lo, imags + src, (hi - lo) * sizeof(qreal), g.stream);
     }
     CUDA_OK(cudaStreamSynchronize(g.stream));
 }
+
+void qb200_setDeferredUpload(int enabled) {
+    requireEngine();
+    flushAll();
+    g.deferUpload = enabled != 0;
+}
+unsigned long long qb200_getDeferredUploadCount(void) { return g.deferredUploads; }
+unsigned long long qb200_getPassesUnderUploadCount(void) { return g.passesUnderUpload; }
 
 void qb200_copyAmpsToHost(Qureg qureg, idx_t start, idx_t n, qreal* reals, qreal* imags) {
     QuregRec* r = canon(qureg);
