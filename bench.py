@@ -146,7 +146,7 @@ def sampled_step_ops(nq, step):
     return [full[4 * t + (t + step) % 4] for t in range(nq)]
 
 
-def run_reference_arm(args, rank, world):
+def run_reference_arm(args, rank, world, emit):
     if rank != 0:
         return
     cores = use_all_host_cores()
@@ -184,7 +184,7 @@ def run_reference_arm(args, rank, world):
         "cpu_baseline": {"value": value, "unit": "gates/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "gates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def parity_leg(lib, env, rank, world, nq, torch, dist):
@@ -218,8 +218,8 @@ def parity_leg(lib, env, rank, world, nq, torch, dist):
 
     chunk = 1 << 24
 
-    def compare():
-        """max |diff| / max |amp| over the whole register and whether every double is bit-identical."""
+    def compare(scale=1.0):
+        """max |got - scale * want| / max |want| over the whole register and whether every double is bit-identical."""
         worst, biggest, same = 0.0, 0.0, True
         if world == 1:
             re = np.empty(min(chunk, n_local), dtype=np.float64)
@@ -230,7 +230,7 @@ def parity_leg(lib, env, rank, world, nq, torch, dist):
                 for got, want_ptr in ((re, cq.stateVec.real), (im, cq.stateVec.imag)):
                     want = np.ctypeslib.as_array(want_ptr, shape=(n_local,))[at:at + n]
                     same = same and np.array_equal(got[:n], want)
-                    worst = max(worst, float(np.abs(got[:n] - want).max()))
+                    worst = max(worst, float(np.abs(got[:n] - scale * want).max()))
                     biggest = max(biggest, float(np.abs(want).max()))
             return worst / biggest, same
         shard = lib.get_state(q)  # this rank's shard, identity layout restored
@@ -245,38 +245,51 @@ def parity_leg(lib, env, rank, world, nq, torch, dist):
             got = t.cpu().numpy().view(np.complex128)
             sl = slice(r * n_local, (r + 1) * n_local)
             same = same and np.array_equal(got.real, want_re[sl]) and np.array_equal(got.imag, want_im[sl])
-            worst = max(worst, float(np.abs(got.real - want_re[sl]).max()), float(np.abs(got.imag - want_im[sl]).max()))
+            worst = max(worst, float(np.abs(got.real - scale * want_re[sl]).max()), float(np.abs(got.imag - scale * want_im[sl]).max()))
             biggest = max(biggest, float(np.abs(want_re[sl]).max()), float(np.abs(want_im[sl]).max()))
         return worst / biggest, same
 
     rel1, same1 = compare()
     got_tail = circuits.run_circuit(lib, q, tail, seed=77)
     want_tail = circuits.run_circuit(cpu, cq, tail, seed=77) if rank == 0 else None
-    rel2, same2 = compare()
+    # After a collapse each library has renormalised with ITS OWN outcome probability.  The reference adds |amp|^2
+    # sequentially per OpenMP thread (QuEST_cpu.c:2880-2887), which at 2^28+ amplitudes leaves it up to ~1e-10 off, and
+    # four collapses compound that.  Both final states are therefore the same direction with slightly different norms,
+    # and the norms are known accurately (the product's device tree sum; the reference's Kahan sum,
+    # QuEST_cpu_local.c:123-151).  The bar after the measurements: identical outcomes; the product's own norm 1 to 1e-12;
+    # amplitudes within 1e-12 once the reference state is rescaled by sqrt(total_quest_b200 / total_cpu); and that
+    # factor, like the outcome probability, within the 2e-9 bound on the reference's sequential sums.
+    scale = 1.0
+    if world > 1:
+        t = torch.tensor([want_tail[-1] if rank == 0 else 0.0], dtype=torch.float64, device="cuda")
+        dist.broadcast(t, 0)
+        want_total = float(t.item())
+    else:
+        want_total = want_tail[-1]
+    scale = math.sqrt(got_tail[-1] / want_total)
+    rel2, same2 = compare(scale)
     lib.destroyQureg(q, env)
     if rank != 0:
         return None, None
     cpu.destroyQureg(cq, cenv)
     outcomes_equal = [int(x) for x in got_tail[:3]] == [int(x) for x in want_tail[:3]]
     scalars_rel = max(abs(a - b) / max(abs(b), 1e-300) for a, b in zip(got_tail[3:], want_tail[3:]))
-    # After a collapse each library has renormalised with ITS OWN outcome probability.  The reference adds |amp|^2
-    # sequentially per OpenMP thread (QuEST_cpu.c:2880-2887), which at 2^28+ amplitudes can leave it 1e-10 off; its
-    # Kahan-summed calcTotalProb (QuEST_cpu_local.c:123-151) then reports that defect as |total - 1|.  The bar after
-    # measurements is 1e-12 beyond the two libraries' own normalisation defects; before them it is 1e-12 flat.
-    defect = abs(got_tail[-1] - 1.0) + abs(want_tail[-1] - 1.0)
-    tol2 = 1e-12 + 4 * defect
-    ok = rel1 <= 1e-12 and rel2 <= tol2 and outcomes_equal and scalars_rel <= tol2
+    ref_bound = 2e-9
+    ok = (rel1 <= 1e-12 and rel2 <= 1e-12 and outcomes_equal and abs(got_tail[-1] - 1.0) <= 1e-12
+          and abs(scale - 1.0) <= ref_bound and scalars_rel <= ref_bound)
     parity = {"qubits": nq, "n_gpus": world, "against": "oracle/_ref (the reference's own CPU/OpenMP build)" if kind == "reference"
               else "oracle/ (CPU restatement)", "gates": nq + len(ops), "amplitudes_compared": n_local * world,
               "max_rel_diff": rel1, "bit_identical": bool(same1),
               "measurement_outcomes": [int(x) for x in got_tail[:3]], "outcomes_equal": outcomes_equal,
               "collapse_prob_and_total_prob_rel_diff": scalars_rel,
               "max_rel_diff_after_measurements": rel2, "bit_identical_after_measurements": bool(same2),
-              "tolerance": 1e-12, "tolerance_after_measurements": tol2,
+              "tolerance": 1e-12, "reference_rescaled_by": scale, "bound_on_reference_sequential_sums": ref_bound,
               "total_prob_after": {"quest_b200": got_tail[-1], "cpu": want_tail[-1]}, "ok": bool(ok),
               "what": "initPlusState + rotateY on every qubit + one full configs[1] sweep step, every amplitude compared "
                       "(max |diff| / max |amp|); then measure x3 + collapseToOutcome under seedQuEST({77,155}) and every "
-                      "amplitude again"}
+                      "amplitude again, the reference state rescaled by sqrt(total_prob quest_b200 / cpu): each library "
+                      "renormalises with its own outcome probabilities and the reference's sequential sums are only good "
+                      "to ~1e-10 at this size, the product's norm stays 1 to 1e-15"}
     return parity, cpu_info
 
 
@@ -300,8 +313,18 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     # keep stdout to the one JSON line: NCCL writes its version banner / debug lines to stdout unless told otherwise
     os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # stdout carries the ONE JSON line and nothing else: whatever libraries print (NCCL banners, C-level printf) goes to
+    # stderr for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
+
     if args.impl == "reference":
-        run_reference_arm(args, rank, world)
+        run_reference_arm(args, rank, world, emit)
         return
 
     import torch
@@ -643,7 +666,7 @@ def main():
             line["circuit_34q"] = circuit34
         if circuit33:
             line["circuit_33q"] = circuit33
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     lib.destroyQuESTEnv(env)
