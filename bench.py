@@ -408,6 +408,9 @@ def main():
     for _ in range(warmup):
         step()
     barrier()
+    lib.lib.qb200_getSlotExchangeCount.restype = ctypes.c_ulonglong
+    lib.lib.qb200_getOverlappedExchangeCount.restype = ctypes.c_ulonglong
+    x0, xo0 = lib.lib.qb200_getSlotExchangeCount(), lib.lib.qb200_getOverlappedExchangeCount()
     sampler = ClockSampler(device)
     sampler.start()
     lib.lib.qb200_setKernelTiming(1)
@@ -430,6 +433,8 @@ def main():
     fl1, fg1 = ctypes.c_ulonglong(), ctypes.c_ulonglong()
     lib.lib.qb200_getFusionStats(ctypes.byref(fl1), ctypes.byref(fg1))
     clocks = sampler.stop()
+    exchanges = {"exchanges_per_step": (lib.lib.qb200_getSlotExchangeCount() - x0) / args.steps,
+                 "pipelined_per_step": (lib.lib.qb200_getOverlappedExchangeCount() - xo0) / args.steps}
     if world > 1:
         t = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -660,6 +665,11 @@ def main():
         }
         if contracted:
             line["contracted_arithmetic"] = contracted
+        if world > 1:
+            # time of a step that is not spent inside a fused pass on rank 0: exchange time the passes did not hide (plus
+            # single-gate launches and gaps); one qubit-slot exchange alone takes nvlink.slot_exchange.ms
+            exchanges["exchange_ms_exposed"] = total_ms / args.steps - fused_ms.value / args.steps
+            line["exchanges"] = exchanges
         if nvlink:
             line["nvlink"] = nvlink
         if circuit34:

@@ -109,6 +109,7 @@ struct QuregRec {
     u64 denseSinceFlush = 0;
     // calcProbOfOutcome: the second query on an unchanged state computes P(qubit = 0) for every qubit in one pass;
     // later queries are answered from here until the state changes (dirty()).
+    bool logical = false;  // sharded registers, default mode: the queue holds LOGICAL qubits and full control masks
     bool probValid = false;
     bool exposed = false;  // device pointers were handed out (qb200_getDevicePointers): the state can change unseen
     int probQueries = 0;
@@ -317,18 +318,19 @@ void runOpNow(const Qureg& q, const PendingOp& op) {
 
 TileLaunch tl;  // ~21 KB: passed by value as the kernel parameter block
 
-// Fill the parameter block for one planned pass (qb_fuse.h); returns the kernel tier it needs.
-int preparePass(const std::vector<PendingOp>& ops, const TilePass& p) {
+// Fill the parameter block for one planned pass (qb_fuse.h); returns the kernel tier it needs.  `alive` (sharded
+// registers): gates this rank takes no part in (a control on a shard-selecting qubit is not satisfied here) are planned
+// like the others - every rank cuts the queue the same way - but do not reach the kernel.
+int preparePass(const std::vector<PendingOp>& ops, const TilePass& p, const std::vector<char>* alive = nullptr) {
     int tier = 0;
     tl.nTile = p.nTile;
     tl.nLow = std::min(kTileLow, p.nTile);
     tl.nSub = (int)p.subs.size();
-    tl.nGates = p.count;
+    int g = 0;
     for (int s = 0; s < tl.nSub; ++s) {
         const TileSub& sg = p.subs[s];
         TileSubDesc& d = tl.sub[s];
-        d.first = sg.first - p.first;
-        d.count = sg.count;
+        d.first = g;
         int pos[kRegBits];  // element bit j -> tile-index position: the register bits, then the spectator bit
         for (int j = 0; j < kSubBits; ++j) pos[j] = sg.rb[j];
         pos[kSubBits] = sg.spect;
@@ -336,14 +338,17 @@ int preparePass(const std::vector<PendingOp>& ops, const TilePass& p) {
         std::sort(d.ins, d.ins + kRegBits);
         for (int j = 0; j < kRegBits; ++j) d.placeBit[j] = tilePlace(1u << pos[j]) * (unsigned int)sizeof(qreal);
         for (int k = sg.first; k < sg.first + sg.count; ++k) {
+            if (alive && !(*alive)[k]) continue;
             const TileGate tg = describe(ops[k], p, sg);
-            const int g = k - p.first;
             tl.ctl[g] = TileGateCtl{(unsigned short)tg.tileMask, (unsigned char)tg.opcode, (unsigned char)tg.regMask};
             tl.outerMask[g] = tg.outerMask;
             std::memcpy(tl.c[g], ops[k].c, sizeof ops[k].c);
             tier |= tierOf(tg.opcode);
+            ++g;
         }
+        d.count = g - d.first;
     }
+    tl.nGates = g;
     // amplitude offset of every row of the tile: tile-index bits [nLow, nTile) deposited at their index positions
     for (unsigned int r = 0; r < (1u << (p.nTile - tl.nLow)); ++r) {
         u64 o = 0;
@@ -380,6 +385,7 @@ void launchPrepared(QuregRec* r, const TilePass& p, int tier, const SlabPlan* sp
         ++nRuns;
         b = e;
     }
+    if (tl.nGates == 0) return;  // nothing for this rank in this pass
     tl.nRuns = nRuns;
     tl.slabMask = sp ? sp->valueMask(slab) : 0;
     const unsigned int nb = (unsigned int)((u64)r->n >> __builtin_popcountll(held));
@@ -409,12 +415,12 @@ struct FusedTimer {  // qb200_setKernelTiming: one event pair per fused pass (a 
     }
 };
 
-void runPass(const Qureg& q, const std::vector<PendingOp>& ops, const TilePass& p) {
+void runPass(const Qureg& q, const std::vector<PendingOp>& ops, const TilePass& p, const std::vector<char>* alive = nullptr) {
     if (p.count == 1) {
-        runOpNow(q, ops[p.first]);
+        if (!alive || (*alive)[p.first]) runOpNow(q, ops[p.first]);
         return;
     }
-    const int tier = preparePass(ops, p);
+    const int tier = preparePass(ops, p, alive);
     FusedTimer t;
     t.start();
     launchPrepared(rec(q), p, tier, nullptr, 0);
@@ -445,8 +451,8 @@ inline u64 bitsOf(const TilePass& p) {
 // One fused pass cut along `sp`: slab s starts once `waitFor[s]` has happened (the exchange before it delivered that
 // slab) and `record[s]` marks its end (the exchange after it may take that slab).
 void runPassInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const TilePass& p, const SlabPlan& sp,
-                    const cudaEvent_t* waitFor, const cudaEvent_t* record) {
-    const int tier = preparePass(ops, p);
+                    const cudaEvent_t* waitFor, const cudaEvent_t* record, const std::vector<char>* alive = nullptr) {
+    const int tier = preparePass(ops, p, alive);
     FusedTimer t;
     bool started = false;
     for (int s = 0; s < (1 << sp.nBits); ++s) {
@@ -464,6 +470,7 @@ void runPassInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const Til
 }
 
 void exchangeSlots(const Qureg& q, SlotSwap sw);
+void flushSharded(const Qureg& q);
 
 // Execute everything recorded for this register: single gates through their own kernel, runs of gates through
 // k_tile (one HBM pass per planned pass, qb_fuse.h).
@@ -507,6 +514,10 @@ void flush(const Qureg& q) {
     if (r->uploading) {
         if (r->queue.empty()) settleUpload(r);
         else flushBehindUpload(q);
+        return;
+    }
+    if (r->logical) {
+        flushSharded(q);
         return;
     }
     const bool pending = g.pendingReg == r;
@@ -582,68 +593,173 @@ void exchangeSlots(const Qureg& q, SlotSwap sw) {
     ++g.slotSwaps;
 }
 
-// flush(q) followed by exchangeSlots(q, sw), pipelined.  The exchange and the fused passes on either side of it are
-// cut into slabs (qb::planSlabs): on the communication stream slab s of the exchange starts as soon as the pass before
-// it has finished slab s on both GPUs of the pair (event + handshake) and moves over NVLink while that pass computes
-// slab s+1; the call returns without waiting, and the first pass recorded afterwards follows the exchange slab by
-// slab in the same way (flush).  Passes are bound by fp64 issue, the exchange by NVLink, so they overlap.
-void flushThenExchange(const Qureg& q, SlotSwap sw) {
+// ---- sharded registers, default mode: plan the whole recorded queue, then execute ---------------------------------
+// The queue holds logical gates - the same list on every rank.  qb::planWalk cuts it into segments whose dense targets
+// are local and the slot exchanges between them (victims by furthest next use).  Every segment is planned into passes on
+// the FULL gate list (so that all ranks cut alike); gates this rank takes no part in are dropped only when a pass is
+// handed to the kernel.  An exchange is cut into slabs along index bits that neither it nor the passes next to it hold,
+// and pipelined on the communication stream: slab s moves over NVLink once the pass before it has finished slab s on
+// both GPUs of the pair, while that pass computes slab s+1; the pass after it follows slab by slab in the same way.
+struct ShardSegment {
+    std::vector<PendingOp> ops;    // bit positions under the layout of the segment, controls localised for this rank
+    std::vector<char> alive;
+    std::vector<TilePass> passes;
+    u64 firstBits = 0, lastBits = 0;  // tile bits of the first / last pass
+};
+
+void planSegment(ShardSegment& seg, const std::vector<PendingOp>& full, int localBits, u64 avoid) {
+    seg.passes = planPasses(full, localBits, avoid);
+    seg.firstBits = bitsOf(seg.passes.front());
+    seg.lastBits = bitsOf(seg.passes.back());
+}
+
+void flushSharded(const Qureg& q) {
     QuregRec* r = rec(q);
-    // Both GPUs of the pair must cut along the same bits and issue the same handshakes, whatever their own queues hold:
-    // everything below that shapes the protocol derives from rank-independent state.
-    const u64 busy = r->denseSinceFlush | (1ull << sw.localSlot);
-    const int spare = r->localBits - __builtin_popcountll((busy | ((1ull << kTileLow) - 1ull)) & ((1ull << r->localBits) - 1)) - kTileBits;
-    SlabPlan sp{0, {0, 0, 0}};
-    const bool eligible = g.overlap && g.comm && r->callsSinceFlush > 0 && r->localBits >= g.overlapMinBits;
-    bool chained = false;  // the previous exchange of this register is still in flight and is cut the same way
-    if (eligible && g.pendingReg == r && !(bitsOf(g.pendingPlan) & busy) && spare >= g.pendingPlan.nBits) {
-        sp = g.pendingPlan;
-        chained = true;
-    } else if (eligible && spare > 0) {
-        sp = planSlabs(r->localBits, busy, std::min(kMaxSlabBits, spare), std::min(16, g.overlapMinBits / 2 + 2));
-    }
-    if (sp.nBits == 0) {
-        flush(q);
-        exchangeSlots(q, sw);
-        return;
-    }
-    if (!chained) settle();
-    std::vector<PendingOp> ops;
-    ops.swap(r->queue);
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
-    const std::vector<TilePass> groups = planPasses(ops, r->localBits, bitsOf(sp));
-    const int nSlabs = 1 << sp.nBits;
-    bool signalled = false;  // the last pass recorded slabEv[] itself
-    for (size_t i = 0; i < groups.size(); ++i) {
-        const bool isFirst = i == 0, isLast = i + 1 == groups.size();
-        const bool fusedPass = groups[i].count > 1;
-        const bool follow = chained && isFirst && fusedPass;  // dense targets never sit on slab bits: see `busy`
-        if (chained && isFirst && !follow) settle();
-        if (fusedPass && (follow || isLast)) {
-            runPassInSlabs(q, ops, groups[i], sp, follow ? g.xDone : nullptr, isLast ? g.slabEv : nullptr);
-            signalled = signalled || isLast;
-        } else {
-            runPass(q, ops, groups[i]);
+    r->logical = false;
+    if (r->queue.empty()) {
+        if (g.pendingReg == r) settle();
+        return;
+    }
+    std::vector<PendingOp> logicalOps;
+    logicalOps.swap(r->queue);
+    std::vector<WalkOp> walk(logicalOps.size());
+    for (size_t i = 0; i < logicalOps.size(); ++i) {
+        const PendingOp& op = logicalOps[i];
+        walk[i] = WalkOp{isDiagonal(op.kind) ? -1 : op.target, isDiagonal(op.kind) ? -1 : op.target2, op.mask};
+    }
+    QubitMap after = r->map;
+    const std::vector<WalkStep> steps = planWalk(after, walk);
+
+    // 1. every segment in bit positions under its own layout (rank-independent: full control masks), dry-planned
+    QubitMap cur = r->map;
+    std::vector<ShardSegment> segs(steps.size());
+    std::vector<std::vector<PendingOp>> full(steps.size());
+    for (size_t k = 0; k < steps.size(); ++k) {
+        if (steps[k].isExchange) {
+            cur.applySwap(steps[k].sw.globalSlot, steps[k].sw.localSlot);
+            continue;
+        }
+        for (int i = steps[k].first; i < steps[k].first + steps[k].count; ++i) {
+            PendingOp op = logicalOps[i];
+            if (!isDiagonal(op.kind)) {
+                op.target = cur.phys[op.target];
+                if (op.target2 >= 0) op.target2 = cur.phys[op.target2];
+            }
+            op.mask = cur.physMask(op.mask);
+            full[k].push_back(op);
+        }
+        planSegment(segs[k], full[k], r->localBits, 0);
+    }
+    // 2. slab plan of every exchange: the highest local bits held neither by the exchange nor by the passes around it
+    const bool pipeline = g.overlap && g.comm && r->localBits >= g.overlapMinBits;
+    std::vector<SlabPlan> plan(steps.size(), SlabPlan{0, {0, 0, 0}});
+    std::vector<u64> avoid(steps.size(), 0);
+    for (size_t k = 0; k < steps.size(); ++k) {
+        if (!steps[k].isExchange || !pipeline) continue;
+        const bool hasBefore = k > 0 && !steps[k - 1].isExchange, hasAfter = k + 1 < steps.size() && !steps[k + 1].isExchange;
+        u64 busy = (1ull << steps[k].sw.localSlot) | ((1ull << kTileLow) - 1ull);
+        if (hasBefore) busy |= segs[k - 1].lastBits;
+        if (hasAfter) busy |= segs[k + 1].firstBits;
+        if (!hasBefore && !hasAfter) continue;
+        // a pass that sits alone between two exchanges is cut once: reuse the previous exchange's plan if it still fits
+        SlabPlan sp{0, {0, 0, 0}};
+        if (k >= 2 && steps[k - 2].isExchange && plan[k - 2].nBits && segs[k - 1].passes.size() == 1 && !(bitsOf(plan[k - 2]) & busy))
+            sp = plan[k - 2];
+        else
+            sp = planSlabs(r->localBits, busy, kMaxSlabBits, std::min(16, g.overlapMinBits / 2 + 2));
+        plan[k] = sp;
+        if (hasBefore) avoid[k - 1] |= bitsOf(sp);
+        if (hasAfter) avoid[k + 1] |= bitsOf(sp);
+    }
+    // 3. final plans (padding keeps clear of the slab bits; dense targets are unchanged), this rank's view of the gates
+    for (size_t k = 0; k < steps.size(); ++k) {
+        if (steps[k].isExchange) continue;
+        if (avoid[k]) planSegment(segs[k], full[k], r->localBits, avoid[k]);
+        segs[k].ops = full[k];
+        segs[k].alive.assign(full[k].size(), 1);
+        for (size_t i = 0; i < full[k].size(); ++i)
+            if (!qb::localiseControls(r->localBits, q.chunkId, segs[k].ops[i].mask)) segs[k].alive[i] = 0;
+    }
+    // 4. execute
+    bool signalled = false;             // the pass just run has recorded slabEv[] for the exchange that follows it
+    bool inFlight = g.pendingReg == r;  // an exchange whose slabs the engine stream has not waited for yet ...
+    SlabPlan inFlightPlan = g.pendingPlan;  // ... cut this way
+    if (inFlight) {  // left over from an earlier call: not planned here
+        settle();
+        inFlight = false;
+    }
+    for (size_t k = 0; k < steps.size(); ++k) {
+        if (steps[k].isExchange) {
+            const SlotSwap sw = steps[k].sw;
+            const SlabPlan& sp = plan[k];
+            if (sp.nBits == 0) {
+                if (inFlight) {
+                    settle();
+                    inFlight = false;
+                }
+                exchangeSlots(q, sw);
+                continue;
+            }
+            const int nSlabs = 1 << sp.nBits;
+            // Unless the pass before it recorded slabEv[] slab by slab, everything the engine stream holds so far has to
+            // finish first.  (An exchange straight after another one simply queues up behind it on the communication
+            // stream; an exchange after a segment finds no exchange in flight: the segment's first pass has waited.)
+            if (!signalled)
+                for (int sl = 0; sl < nSlabs; ++sl) CUDA_OK(cudaEventRecord(g.slabEv[sl], g.stream));
+            signalled = false;
+            const comm::Partner peer = comm::partnerOf(q, sw.globalSlot - r->localBits);
+            for (int sl = 0; sl < nSlabs; ++sl) {
+                CUDA_OK(cudaStreamWaitEvent(g.comm, g.slabEv[sl], 0));
+                comm::pairBarrier(peer.rank, g.comm, 1);  // the partner has finished slab sl too
+                launchSwap(q, sw, &sp, sl, g.comm);
+                comm::pairBarrier(peer.rank, g.comm, 1);  // the partner's remote writes into this slab have landed
+                CUDA_OK(cudaEventRecord(g.xDone[sl], g.comm));
+            }
+            CUDA_OK(cudaEventRecord(g.commDone, g.comm));
+            g.pendingReg = r;
+            g.pendingPlan = sp;
+            inFlight = true;
+            inFlightPlan = sp;
+            r->map.applySwap(sw.globalSlot, sw.localSlot);
+            ++g.slotSwaps;
+            ++g.overlapped;
+            continue;
+        }
+        ShardSegment& seg = segs[k];
+        const bool exchangeNext = k + 1 < steps.size() && steps[k + 1].isExchange && plan[k + 1].nBits > 0;
+        for (size_t i = 0; i < seg.passes.size(); ++i) {
+            const TilePass& p = seg.passes[i];
+            const bool isFirst = i == 0, isLast = i + 1 == seg.passes.size();
+            const bool fused = p.count > 1;
+            const bool follow = inFlight && isFirst && fused && !(bitsOf(p) & bitsOf(inFlightPlan));
+            bool signal = exchangeNext && isLast && fused && !(bitsOf(p) & bitsOf(plan[k + 1]));
+            if (follow && signal && bitsOf(inFlightPlan) != bitsOf(plan[k + 1])) signal = false;  // one cut per pass
+            if (inFlight && isFirst && !follow) {
+                settle();
+                inFlight = false;
+            }
+            if (follow || signal) {
+                runPassInSlabs(q, seg.ops, p, follow ? inFlightPlan : plan[k + 1], follow ? g.xDone : nullptr,
+                               signal ? g.slabEv : nullptr, &seg.alive);
+                if (follow) {  // the last slab waited for the last piece of the exchange
+                    g.pendingReg = nullptr;
+                    inFlight = false;
+                }
+            } else {
+                runPass(q, seg.ops, p, &seg.alive);
+            }
+            if (isLast) signalled = signal;
         }
     }
-    // (with an empty queue a chained exchange simply queues up behind the previous one on the communication stream)
-    if (!signalled)
-        for (int s = 0; s < nSlabs; ++s) CUDA_OK(cudaEventRecord(g.slabEv[s], g.stream));
-    const comm::Partner peer = comm::partnerOf(q, sw.globalSlot - r->localBits);
-    for (int s = 0; s < nSlabs; ++s) {
-        CUDA_OK(cudaStreamWaitEvent(g.comm, g.slabEv[s], 0));
-        comm::pairBarrier(peer.rank, g.comm, 1);  // the partner has finished slab s too
-        launchSwap(q, sw, &sp, s, g.comm);
-        comm::pairBarrier(peer.rank, g.comm, 1);  // the partner's remote writes into this slab have landed
-        CUDA_OK(cudaEventRecord(g.xDone[s], g.comm));
+    if (inFlight) settle();
+    // the use history the walk accumulated (the layout itself was replayed exchange by exchange above)
+    for (int lq = 0; lq < 64; ++lq) {
+        r->map.lastUse[lq] = after.lastUse[lq];
+        r->map.prevUse[lq] = after.prevUse[lq];
     }
-    CUDA_OK(cudaEventRecord(g.commDone, g.comm));
-    g.pendingReg = r;
-    g.pendingPlan = sp;
-    r->map.applySwap(sw.globalSlot, sw.localSlot);
-    ++g.slotSwaps;
-    ++g.overlapped;
+    r->map.tick = after.tick;
 }
 
 // the register's record with no gate pending: every entry point that reads or overwrites amplitudes uses this
@@ -657,7 +773,7 @@ inline QuregRec* canon(const Qureg& q) {
     flush(q);
     QuregRec* r = rec(q);
     if (!r->map.identity()) {
-        SlotSwap sw[64];
+        SlotSwap sw[192];
         const int n = planCanonicalize(r->map, sw);
         for (int i = 0; i < n; ++i) exchangeSlots(q, sw[i]);
     }
@@ -671,6 +787,7 @@ inline QuregRec* fresh(const Qureg& q) {
     settleUpload(r);
     dirty(r);
     r->queue.clear();
+    r->logical = false;
     r->callsSinceFlush = 0;
     r->denseSinceFlush = 0;
     r->map.reset(r->map.nQubits, r->localBits);
@@ -682,6 +799,15 @@ inline QuregRec* fresh(const Qureg& q) {
 void submit(const Qureg& q, PendingOp op) {
     QuregRec* r = rec(q);
     dirty(r);
+    if (g.world > 1 && g.fuse && g.remap && !r->exposed && r->localBits >= kRegBits) {
+        // sharded register, default mode: the gate is recorded as it came - logical qubits, full control mask - so that
+        // every rank holds the same queue; layout decisions are taken when the queue is executed (flushSharded)
+        if (r->callsSinceFlush >= kQueueCap) flush(q);
+        ++r->callsSinceFlush;
+        r->logical = true;
+        r->queue.push_back(op);
+        return;
+    }
     // logical qubits -> current bit positions; a dense target living in a shard-selecting slot is first made local
     if (g.world > 1) {
         if (!isDiagonal(op.kind)) {
@@ -693,7 +819,10 @@ void submit(const Qureg& q, PendingOp op) {
                     u64 keep = op.mask | (1ull << logical[0]);
                     if (logical[1] >= 0) keep |= 1ull << logical[1];
                     const SlotSwap sw = planSwapIn(r->map, t, keep);
-                    if (sw.globalSlot >= 0) flushThenExchange(q, sw);
+                    if (sw.globalSlot >= 0) {
+                        flush(q);
+                        exchangeSlots(q, sw);
+                    }
                 }
                 r->map.touch(t);
             }
@@ -1650,11 +1779,63 @@ int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, c
         eventsOut[3 * i + 2] = m.phys[targets[i]];
     }
     for (int q = 0; q < nQubits; ++q) physOut[q] = m.phys[q];
-    SlotSwap back[64];
+    SlotSwap back[192];
     const int n = planCanonicalize(m, back);
     for (int i = 0; i < n; ++i) {
         canonOut[2 * i] = back[i].globalSlot;
         canonOut[2 * i + 1] = back[i].localSlot;
+    }
+    return n;
+}
+
+// Host walk of a recorded queue of logical gates (qb::planWalk), exposed for CPU-only tests (no CUDA call).  The layout
+// and use history travel in and out through mapState (phys[64], lastUse[64], prevUse[64], tick = 193 words), so that a
+// test can replay several flushes in a row.  stepsOut: 3 ints per step - exchange: (1, globalSlot, localSlot); segment:
+// (0, first, count).  Returns the number of steps.
+int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* targets, const int* targets2,
+                    const unsigned long long* masks, unsigned long long* mapState, int* stepsOut) {
+    QubitMap m;
+    m.reset(nQubits, localBits);
+    if (mapState[192]) {
+        for (int q = 0; q < 64; ++q) {
+            m.phys[q] = (int)mapState[q];
+            m.logicalAt[m.phys[q]] = q;
+            m.lastUse[q] = mapState[64 + q];
+            m.prevUse[q] = mapState[128 + q];
+        }
+        m.tick = mapState[192];
+    }
+    std::vector<WalkOp> ops(nOps);
+    for (int i = 0; i < nOps; ++i) ops[i] = WalkOp{targets[i], targets2[i], masks[i]};
+    const std::vector<WalkStep> steps = planWalk(m, ops);
+    for (size_t k = 0; k < steps.size(); ++k) {
+        stepsOut[3 * k] = steps[k].isExchange;
+        stepsOut[3 * k + 1] = steps[k].isExchange ? steps[k].sw.globalSlot : steps[k].first;
+        stepsOut[3 * k + 2] = steps[k].isExchange ? steps[k].sw.localSlot : steps[k].count;
+    }
+    for (int q = 0; q < 64; ++q) {
+        mapState[q] = (unsigned long long)m.phys[q];
+        mapState[64 + q] = m.lastUse[q];
+        mapState[128 + q] = m.prevUse[q];
+    }
+    mapState[192] = m.tick;
+    return (int)steps.size();
+}
+
+// Host canonicalisation logic (qb::planCanonicalize) for ANY layout, exposed for CPU-only tests (no CUDA call):
+// phys[nQubits] = logical -> bit position; out = pairs (globalSlot, localSlot); returns the number of exchanges.
+int qb200_debugCanon(int nQubits, int localBits, const int* phys, int* out) {
+    QubitMap m;
+    m.reset(nQubits, localBits);
+    for (int q = 0; q < nQubits; ++q) {
+        m.phys[q] = phys[q];
+        m.logicalAt[phys[q]] = q;
+    }
+    SlotSwap back[192];
+    const int n = planCanonicalize(m, back);
+    for (int i = 0; i < n; ++i) {
+        out[2 * i] = back[i].globalSlot;
+        out[2 * i + 1] = back[i].localSlot;
     }
     return n;
 }

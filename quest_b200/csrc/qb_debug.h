@@ -21,6 +21,14 @@ void qb200_debugPlanGate(int localBits, int chunkId, int target, unsigned long l
 int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, const unsigned long long* masks,
                      int* eventsOut, int* physOut, int* canonOut);
 
+/* How a recorded queue of logical gates on a sharded register is cut into local segments and slot exchanges, with the
+ * layout and use history carried from one call to the next. */
+int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* targets, const int* targets2,
+                    const unsigned long long* masks, unsigned long long* mapState, int* stepsOut);
+
+/* The exchanges that restore the identity layout from any layout. */
+int qb200_debugCanon(int nQubits, int localBits, const int* phys, int* out);
+
 /* The slab bits chosen for pipelining a fused pass with a slot exchange, and every k_swapPeer launch plan of that
  * exchange. */
 int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int lowestAllowed, int vec, int localSlot,

@@ -157,6 +157,7 @@ struct QubitMap {
     int phys[64];                   // logical qubit -> bit position in the amplitude index
     int logicalAt[64];              // bit position -> logical qubit
     unsigned long long lastUse[64]; // logical qubit -> tick of its last use as a dense target
+    unsigned long long prevUse[64]; // ... and of the use before that (0 = none): their distance predicts the next use
     unsigned long long tick = 0;
 
     void reset(int n, int local) {
@@ -165,7 +166,7 @@ struct QubitMap {
         tick = 0;
         for (int q = 0; q < 64; ++q) {
             phys[q] = logicalAt[q] = q;
-            lastUse[q] = 0;
+            lastUse[q] = prevUse[q] = 0;
         }
     }
     bool identity() const {
@@ -188,7 +189,16 @@ struct QubitMap {
             if ((logicalIndex >> q) & 1) p |= 1ull << phys[q];
         return p;
     }
-    void touch(int logicalQubit) { lastUse[logicalQubit] = ++tick; }
+    void touch(int logicalQubit) {
+        prevUse[logicalQubit] = lastUse[logicalQubit];
+        lastUse[logicalQubit] = ++tick;
+    }
+    // When will this qubit be a dense target again?  Its last two uses predict the next one (a qubit swept every N gates
+    // comes back N gates after its last use; a qubit used once has no prediction).
+    unsigned long long predictedNextUse(int logicalQubit) const {
+        if (!prevUse[logicalQubit]) return ~0ull;
+        return lastUse[logicalQubit] + (lastUse[logicalQubit] - prevUse[logicalQubit]);
+    }
     void applySwap(int g, int l) {  // exchange the occupants of bit positions g and l
         const int a = logicalAt[g], b = logicalAt[l];
         logicalAt[g] = b;
@@ -289,12 +299,132 @@ inline SwapLaunch planSlotSwap(int localBits, int vec, int l, bool amUpper, cons
     return out;
 }
 
-// The transpositions that restore the identity layout (each is its own inverse).
-inline int planCanonicalize(const QubitMap& m, SlotSwap* out /* >= 64 */) {
+// Global<->local slot exchanges that restore the identity layout, for ANY placement the exchanges have produced.
+// Phase 1 sends every shard-selecting qubit home (one exchange if it sits in a local slot, two if it sits in another
+// shard-selecting slot); phase 2 resolves what is left - a permutation of the local qubits among the local slots - cycle
+// by cycle through the first shard-selecting slot as a buffer (k + 1 exchanges for a cycle of k slots).  In the common
+// case, a few disjoint global<->local transpositions, this is one exchange per transposition.
+inline int planCanonicalize(const QubitMap& m0, SlotSwap* out /* >= 192 */) {
+    QubitMap m = m0;
     int n = 0;
-    for (int g = m.localBits; g < m.nQubits; ++g)
-        if (m.logicalAt[g] != g) out[n++] = SlotSwap{g, m.logicalAt[g]};  // occupant's home is the local slot
+    auto swap = [&](int g, int l) {
+        out[n++] = SlotSwap{g, l};
+        m.applySwap(g, l);
+    };
+    for (int h = m.localBits; h < m.nQubits; ++h) {
+        if (m.logicalAt[h] == h) continue;
+        int at = m.phys[h];  // where the native of slot h sits
+        if (at >= m.localBits) {  // in another shard-selecting slot: bring it into a local slot first
+            swap(at, m.localBits - 1);
+            at = m.localBits - 1;
+        }
+        swap(h, at);
+    }
+    if (m.nQubits > m.localBits) {
+        const int g0 = m.localBits;
+        for (int l = 0; l < m.localBits; ++l) {
+            if (m.logicalAt[l] == l) continue;
+            swap(g0, l);  // slot l now holds the native of g0, the buffer holds a displaced local qubit
+            while (m.logicalAt[g0] != g0) swap(g0, m.logicalAt[g0]);  // ... which goes home, handing the buffer the next one
+        }
+    }
     return n;
+}
+
+// ---- walking a recorded queue of LOGICAL gates (sharded registers, default mode) ---------------------------------------
+// The queue (the same on every rank) is cut into SEGMENTS of gates whose dense targets are all local under the layout
+// of that moment, separated by slot exchanges that bring the next needed shard-selecting qubit in.  The victim of an
+// exchange is the local qubit whose next use as a dense target lies furthest away: known from the rest of the queue
+// where it is used again, predicted from its last two uses where it is not (a qubit swept every N gates comes back N
+// gates after its last use), least recently used where there is no history.  Pure bookkeeping: the executor replays the
+// steps on the GPUs.
+struct WalkStep {
+    int isExchange;
+    int first, count;  // segment: gates [first, first + count) of the queue
+    SlotSwap sw;       // exchange
+};
+
+inline int chooseVictimSlot(const QubitMap& m, const unsigned long long* nextUse /* per logical qubit, ~0 = none */,
+                            unsigned long long keepLogical) {
+    int best = -1, bestClass = -1;
+    unsigned long long bestKey = 0;
+    const int preferred = m.localBits > 12 ? 10 : 2;  // low slots move short runs over NVLink (see planSwapIn)
+    for (int lowest = preferred; best < 0 && lowest >= 0; lowest = lowest ? 0 : -1)
+        for (int x = lowest; x < m.localBits; ++x) {
+            const int lq = m.logicalAt[x];
+            if ((keepLogical >> lq) & 1) continue;
+            int cls;
+            unsigned long long key;
+            if (nextUse[lq] != ~0ull) {                 // used again in this queue: the later the better
+                cls = 0;
+                key = nextUse[lq];
+            } else if (m.lastUse[lq] == 0) {            // never a dense target so far
+                cls = 3;
+                key = (unsigned long long)x;
+            } else if (m.prevUse[lq] == 0) {            // used once: no prediction, least recently used first
+                cls = 1;
+                key = ~m.lastUse[lq];
+            } else {                                    // predicted from its last two uses: the later the better
+                cls = 2;
+                key = m.predictedNextUse(lq);
+            }
+            if (cls > bestClass || (cls == bestClass && key > bestKey)) {
+                best = x;
+                bestClass = cls;
+                bestKey = key;
+            }
+        }
+    return best;
+}
+
+struct WalkOp {  // what the walk needs to know about a recorded gate (logical qubits)
+    int target, target2;          // dense targets (-1 = none; both -1 for a diagonal gate)
+    unsigned long long mask;
+};
+
+// `map` is advanced to the layout (and use history) after the whole queue.  A gate whose dense target cannot be made
+// local (every local qubit is pinned by the gate itself) ends up in a segment of its own with that target still in a
+// shard-selecting slot: the executor runs it as a cross-shard pass.
+inline std::vector<WalkStep> planWalk(QubitMap& map, const std::vector<WalkOp>& ops) {
+    std::vector<WalkStep> steps;
+    const int n = (int)ops.size();
+    // next dense use of every logical qubit at or after position i, filled backwards
+    std::vector<unsigned long long> next((size_t)(n + 1) * 64, ~0ull);
+    for (int i = n - 1; i >= 0; --i) {
+        for (int q = 0; q < 64; ++q) next[(size_t)i * 64 + q] = next[(size_t)(i + 1) * 64 + q];
+        if (ops[i].target >= 0) next[(size_t)i * 64 + ops[i].target] = (unsigned long long)i;
+        if (ops[i].target2 >= 0) next[(size_t)i * 64 + ops[i].target2] = (unsigned long long)i;
+    }
+    int segStart = 0;
+    for (int i = 0; i < n; ++i) {
+        const int t[2] = {ops[i].target, ops[i].target2};
+        unsigned long long keep = ops[i].mask;
+        for (int k = 0; k < 2; ++k)
+            if (t[k] >= 0) keep |= 1ull << t[k];
+        bool cross = false;
+        for (int k = 0; k < 2; ++k) {
+            if (t[k] < 0 || map.phys[t[k]] < map.localBits) continue;
+            const int slot = map.localBits >= 3 ? chooseVictimSlot(map, &next[(size_t)(i + 1) * 64], keep) : -1;
+            if (slot < 0) {
+                cross = true;
+                continue;
+            }
+            if (i > segStart) steps.push_back(WalkStep{0, segStart, i - segStart, SlotSwap{-1, -1}});
+            segStart = i;
+            const SlotSwap sw{map.phys[t[k]], slot};
+            steps.push_back(WalkStep{1, 0, 0, sw});
+            map.applySwap(sw.globalSlot, sw.localSlot);
+        }
+        if (cross) {  // isolate the gate
+            if (i > segStart) steps.push_back(WalkStep{0, segStart, i - segStart, SlotSwap{-1, -1}});
+            steps.push_back(WalkStep{0, i, 1, SlotSwap{-1, -1}});
+            segStart = i + 1;
+        }
+        for (int k = 0; k < 2; ++k)
+            if (t[k] >= 0) map.touch(t[k]);
+    }
+    if (n > segStart) steps.push_back(WalkStep{0, segStart, n - segStart, SlotSwap{-1, -1}});
+    return steps;
 }
 
 }  // namespace qb

@@ -352,3 +352,97 @@ def test_swap_in_prefers_high_slots_and_falls_back_to_low_ones():
     assert first_victim >= 10 and events[1][0] == 14 and events[1][1] not in (10, 11, 12)
     assert sorted(phys) == list(range(nq))    # still a permutation
 
+
+
+# ---- walking a recorded queue of logical gates (qb::planWalk: sharded registers, default mode) -----------------------
+
+def _walk(lib, nq, local_bits, ops, state):
+    """ops: (target, target2, mask); state: the 193-word layout/history block carried between flushes."""
+    n = len(ops)
+    steps = (ctypes.c_int * (3 * (2 * n + 8)))()
+    ns = lib.qb200_debugWalk(nq, local_bits, n, (ctypes.c_int * n)(*[o[0] for o in ops]), (ctypes.c_int * n)(*[o[1] for o in ops]),
+                             (ctypes.c_ulonglong * n)(*[o[2] for o in ops]), state, steps)
+    return [(steps[3 * k], steps[3 * k + 1], steps[3 * k + 2]) for k in range(ns)]
+
+
+@pytest.mark.parametrize("world,seed", [(2, 21), (4, 22), (8, 23)])
+def test_walk_of_a_logical_queue_reproduces_the_circuit(world, seed):
+    """Several flushes in a row: segments cover the queue in order, every dense target is local when its gate runs,
+    exchanges swap one shard-selecting slot with one local slot, and replaying exchanges + translated gates on a full
+    state - followed by the canonicalising exchanges for whatever layout resulted - gives the circuit's result."""
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    lib.qb200_debugWalk.restype = ctypes.c_int
+    lib.qb200_debugCanon.restype = ctypes.c_int
+    rng = random.Random(seed)
+    nq = 11
+    L = nq - (world.bit_length() - 1)
+    state = (ctypes.c_ulonglong * 193)()
+    psi = circuits.random_state(1 << nq, seed)
+    want, cur = psi.copy(), psi.copy()
+    layout = list(range(nq))  # logical -> bit position
+    n_exchanges = n_cross = 0
+    for flush in range(6):
+        ops, mats = [], []
+        for _ in range(rng.randrange(1, 60)):
+            t = rng.randrange(nq) if rng.random() < 0.6 else rng.randrange(L, nq)
+            cs = rng.sample([q for q in range(nq) if q != t], rng.choice([0, 0, 1, 2]))
+            if rng.random() < 0.2:   # diagonal gate: no dense target
+                ops.append((-1, -1, sum(1 << c for c in cs) | (1 << t)))
+            else:
+                ops.append((t, -1, sum(1 << c for c in cs)))
+                n_cross += t >= L
+            mats.append(rand_u(rng))
+        steps = _walk(lib, nq, L, ops, state)
+        covered = 0
+        for is_x, a, b in steps:
+            if is_x:
+                assert a >= L > b >= 0
+                cur = _swap_bits(cur, a, b)
+                ia, ib = layout.index(a), layout.index(b)
+                layout[ia], layout[ib] = b, a
+                n_exchanges += 1
+                continue
+            assert a == covered
+            for i in range(a, a + b):
+                t, _, m = ops[i]
+                pm = sum(1 << layout[c] for c in range(nq) if (m >> c) & 1)
+                if t < 0:
+                    idx = np.arange(1 << nq)
+                    sel = (idx & pm) == pm
+                    cur[sel] *= np.exp(0.3j)
+                    lm = m
+                    want[(idx & lm) == lm] *= np.exp(0.3j)
+                else:
+                    assert layout[t] < L
+                    cur = dense_reference(cur, nq, layout[t], pm, mats[i])
+                    want = dense_reference(want, nq, t, m, mats[i])
+            covered += b
+        assert covered == len(ops)
+        assert [int(state[q]) for q in range(nq)] == layout
+    assert 0 < n_exchanges < n_cross
+    back = (ctypes.c_int * 384)()
+    nb = lib.qb200_debugCanon(nq, L, (ctypes.c_int * nq)(*layout), back)
+    for k in range(nb):
+        assert back[2 * k] >= L > back[2 * k + 1]
+        cur = _swap_bits(cur, back[2 * k], back[2 * k + 1])
+        ia, ib = layout.index(back[2 * k]), layout.index(back[2 * k + 1])
+        layout[ia], layout[ib] = back[2 * k + 1], back[2 * k]
+    assert layout == list(range(nq))
+    np.testing.assert_allclose(cur, want, atol=1e-12)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_cyclic_sweep_costs_one_exchange_per_shard_selecting_qubit_per_step(world):
+    """The benchmark's step sweeps every target in turn.  Evicting the local qubit whose next use is furthest away - the
+    one just swept - costs log2(G) exchanges per step; least-recently-used eviction (round 1) cost twice that."""
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    lib.qb200_debugWalk.restype = ctypes.c_int
+    g = world.bit_length() - 1
+    L, nq = 30, 30 + g
+    ops = []
+    for t in range(nq):
+        ops += [(t, -1, 0), (t, -1, 0), (t, -1, 1 << ((t + 1) % nq)), (-1, -1, (1 << t) | (1 << ((t + 1) % nq)) | (1 << ((t + 2) % nq)))]
+    state = (ctypes.c_ulonglong * 193)()
+    for step in range(6):
+        steps = _walk(lib, nq, L, ops, state)
+        assert sum(1 for s in steps if s[0]) == g
