@@ -94,7 +94,11 @@ struct Engine {
     cudaEvent_t upEv[8] = {};
     unsigned long long deferredUploads = 0, passesUnderUpload = 0;
     bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
-    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fusedEvents;
+    struct TimedLaunch {
+        cudaEvent_t e0, e1;
+        bool opensPass;  // a pass cut into slabs is several launches, each timed after its own wait
+    };
+    std::vector<TimedLaunch> fusedEvents;
 } g;
 
 struct QuregRec {
@@ -400,7 +404,7 @@ void launchPrepared(QuregRec* r, const TilePass& p, int tier, const SlabPlan* sp
     launched();
 }
 
-struct FusedTimer {  // qb200_setKernelTiming: one event pair per fused pass (a pass cut into slabs counts once)
+struct FusedTimer {  // qb200_setKernelTiming: an event pair per fused launch (a pass cut into slabs counts as one pass)
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     void start() {
         if (!g.timeFused) return;
@@ -408,10 +412,10 @@ struct FusedTimer {  // qb200_setKernelTiming: one event pair per fused pass (a 
         CUDA_OK(cudaEventCreate(&e1));
         CUDA_OK(cudaEventRecord(e0, g.stream));
     }
-    void stop() {
+    void stop(bool opensPass = true) {
         if (!g.timeFused) return;
         CUDA_OK(cudaEventRecord(e1, g.stream));
-        g.fusedEvents.emplace_back(e0, e1);
+        g.fusedEvents.push_back(Engine::TimedLaunch{e0, e1, opensPass});
     }
 };
 
@@ -453,18 +457,14 @@ inline u64 bitsOf(const TilePass& p) {
 void runPassInSlabs(const Qureg& q, const std::vector<PendingOp>& ops, const TilePass& p, const SlabPlan& sp,
                     const cudaEvent_t* waitFor, const cudaEvent_t* record, const std::vector<char>* alive = nullptr) {
     const int tier = preparePass(ops, p, alive);
-    FusedTimer t;
-    bool started = false;
     for (int s = 0; s < (1 << sp.nBits); ++s) {
         if (waitFor) CUDA_OK(cudaStreamWaitEvent(g.stream, waitFor[s], 0));
-        if (!started) {  // after the first wait, so that the measured time is the pass and not the exchange before it
-            t.start();
-            started = true;
-        }
+        FusedTimer t;  // after the wait, so that the measured time is the pass and not the exchange before it
+        t.start();
         launchPrepared(rec(q), p, tier, &sp, s);
+        t.stop(s == 0);
         if (record) CUDA_OK(cudaEventRecord(record[s], g.stream));
     }
-    t.stop();
     ++g.fusedLaunches;
     g.fusedGates += p.count;
 }
@@ -1716,16 +1716,18 @@ void qb200_getFusedKernelTime(double* totalMs, unsigned long long* launches) {
     CUDA_OK(cudaStreamSynchronize(g.stream));
     double sum = 0;
     const bool show = std::getenv("QUEST_B200_PRINT_PASS_TIMES") != nullptr;  // diagnostics: every pass's own device time
+    unsigned long long passes = 0;
     for (auto& ev : g.fusedEvents) {
         float ms = 0;
-        CUDA_OK(cudaEventElapsedTime(&ms, ev.first, ev.second));
-        if (show) std::printf("[pass %.2f ms] ", ms);
+        CUDA_OK(cudaEventElapsedTime(&ms, ev.e0, ev.e1));
+        if (show) std::printf(ev.opensPass ? "[pass %.2f ms] " : "[+slab %.2f ms] ", ms);
         sum += ms;
-        cudaEventDestroy(ev.first);
-        cudaEventDestroy(ev.second);
+        passes += ev.opensPass ? 1 : 0;
+        cudaEventDestroy(ev.e0);
+        cudaEventDestroy(ev.e1);
     }
     *totalMs = sum;
-    *launches = g.fusedEvents.size();
+    *launches = passes;
     g.fusedEvents.clear();
 }
 

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cstring>
 #include <initializer_list>
+#include <utility>
 #include <vector>
 
 namespace qb {
@@ -344,12 +345,16 @@ struct WalkStep {
     SlotSwap sw;       // exchange
 };
 
+// `skip`: take the (skip+1)-th best candidate of the best class instead of the best one.  The walk asks for that when
+// exchanges follow each other within a few gates (a run of gates on several shard-selecting qubits): spreading the victims
+// over qubits that were last used at different times spreads the NEXT round of exchanges over the program, where each
+// one can hide behind the passes on both sides of it instead of queueing up behind the previous exchange.
 inline int chooseVictimSlot(const QubitMap& m, const unsigned long long* nextUse /* per logical qubit, ~0 = none */,
-                            unsigned long long keepLogical) {
-    int best = -1, bestClass = -1;
-    unsigned long long bestKey = 0;
+                            unsigned long long keepLogical, int skip = 0) {
     const int preferred = m.localBits > 12 ? 10 : 2;  // low slots move short runs over NVLink (see planSwapIn)
-    for (int lowest = preferred; best < 0 && lowest >= 0; lowest = lowest ? 0 : -1)
+    for (int lowest = preferred; lowest >= 0; lowest = lowest ? 0 : -1) {
+        int bestClass = -1;
+        std::vector<std::pair<unsigned long long, int>> ranked;  // (key, slot) of the best class
         for (int x = lowest; x < m.localBits; ++x) {
             const int lq = m.logicalAt[x];
             if ((keepLogical >> lq) & 1) continue;
@@ -368,13 +373,20 @@ inline int chooseVictimSlot(const QubitMap& m, const unsigned long long* nextUse
                 cls = 2;
                 key = m.predictedNextUse(lq);
             }
-            if (cls > bestClass || (cls == bestClass && key > bestKey)) {
-                best = x;
+            if (cls > bestClass) {
                 bestClass = cls;
-                bestKey = key;
+                ranked.clear();
             }
+            if (cls == bestClass) ranked.push_back({key, x});
         }
-    return best;
+        if (ranked.empty()) continue;
+        std::sort(ranked.begin(), ranked.end(), [](const std::pair<unsigned long long, int>& a, const std::pair<unsigned long long, int>& b) {
+            return a.first != b.first ? a.first > b.first : a.second > b.second;
+        });
+        const int pick = bestClass == 0 ? 0 : std::min(skip, (int)ranked.size() - 1);  // never give up a known-later use
+        return ranked[pick].second;
+    }
+    return -1;
 }
 
 struct WalkOp {  // what the walk needs to know about a recorded gate (logical qubits)
@@ -396,6 +408,8 @@ inline std::vector<WalkStep> planWalk(QubitMap& map, const std::vector<WalkOp>& 
         if (ops[i].target2 >= 0) next[(size_t)i * 64 + ops[i].target2] = (unsigned long long)i;
     }
     int segStart = 0;
+    int lastExchangeAt = -1000000, closeRun = 0;  // exchanges that follow each other within kCloseGates gates
+    constexpr int kCloseGates = 16, kSpread = 7;
     for (int i = 0; i < n; ++i) {
         const int t[2] = {ops[i].target, ops[i].target2};
         unsigned long long keep = ops[i].mask;
@@ -404,13 +418,15 @@ inline std::vector<WalkStep> planWalk(QubitMap& map, const std::vector<WalkOp>& 
         bool cross = false;
         for (int k = 0; k < 2; ++k) {
             if (t[k] < 0 || map.phys[t[k]] < map.localBits) continue;
-            const int slot = map.localBits >= 3 ? chooseVictimSlot(map, &next[(size_t)(i + 1) * 64], keep) : -1;
+            closeRun = (i - lastExchangeAt <= kCloseGates) ? closeRun + 1 : 0;
+            const int slot = map.localBits >= 3 ? chooseVictimSlot(map, &next[(size_t)(i + 1) * 64], keep, closeRun * kSpread) : -1;
             if (slot < 0) {
                 cross = true;
                 continue;
             }
             if (i > segStart) steps.push_back(WalkStep{0, segStart, i - segStart, SlotSwap{-1, -1}});
             segStart = i;
+            lastExchangeAt = i;
             const SlotSwap sw{map.phys[t[k]], slot};
             steps.push_back(WalkStep{1, 0, 0, sw});
             map.applySwap(sw.globalSlot, sw.localSlot);

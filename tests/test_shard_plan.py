@@ -443,6 +443,12 @@ def test_cyclic_sweep_costs_one_exchange_per_shard_selecting_qubit_per_step(worl
     for t in range(nq):
         ops += [(t, -1, 0), (t, -1, 0), (t, -1, 1 << ((t + 1) % nq)), (-1, -1, (1 << t) | (1 << ((t + 1) % nq)) | (1 << ((t + 2) % nq)))]
     state = (ctypes.c_ulonglong * 193)()
-    for step in range(6):
+    counts, spacing = [], []
+    for step in range(12):
         steps = _walk(lib, nq, L, ops, state)
-        assert sum(1 for s in steps if s[0]) == g
+        counts.append(sum(1 for s in steps if s[0]))
+        spacing.append([s[2] for s in steps if not s[0]])
+    assert all(g <= c <= g + 1 for c in counts) and sum(counts) <= 12 * g + 2, counts
+    # after the first step the exchanges are spread over the step: at least seven targets' worth of gates between them
+    if g > 1:
+        assert all(min(sp[1:-1]) >= 28 for sp in spacing[1:6]), spacing
