@@ -79,6 +79,8 @@ struct Engine {
     unsigned long long slotSwaps = 0;
     bool overlap = true;            // QUEST_B200_OVERLAP: pipeline a slot exchange with the fused pass before it
     int swapCtasPerSm = 1;          // QUEST_B200_SWAP_CTAS: footprint of a pipelined exchange
+    int swapThreads = 128;          // QUEST_B200_SWAP_THREADS: ... and the size of its CTAs (measured on 2 GPUs: 64 threads leave NVLink idle,
+                                    // 256 push a pass CTA off every SM; 128 hide the exchange completely behind the passes)
     int overlapMinBits = 24;        // ... for shards of at least 2^24 amplitudes (QUEST_B200_OVERLAP_MIN_BITS: tests)
     cudaStream_t comm = nullptr;    // high-priority stream of the pipelined exchanges (sharded runs only)
     cudaEvent_t slabEv[8] = {};     // engine stream: the pass before an exchange has finished slab s
@@ -572,11 +574,13 @@ void launchSwap(const Qureg& q, SlotSwap sw, const SlabPlan* sp, int slab, cudaS
     qreal* aIm = amUpper ? r->im : peer.im;
     qreal* bRe = amUpper ? peer.re : r->re;
     qreal* bIm = amUpper ? peer.im : r->im;
-    // alone: up to 8 CTAs on every SM; next to a fused pass: g.swapCtasPerSm, the rest of each SM stays with the pass
+    // alone: up to 8 CTAs of 256 threads on every SM; next to a fused pass: g.swapCtasPerSm small CTAs (g.swapThreads
+    // threads: they must fit into the registers four resident pass CTAs leave over, see qb_tile.cuh)
+    const unsigned int threads = sp ? (unsigned int)g.swapThreads : (unsigned int)kBlock;
     const unsigned int cap = (unsigned int)g.numSMs * (sp ? (unsigned int)g.swapCtasPerSm : 8u);
-    const unsigned int grid = std::min(blocksFor(p.nTasks), cap);
+    const unsigned int grid = std::min((unsigned int)((p.nTasks + threads - 1) / threads), cap);
     dispatchV(vec, [&](auto V) {
-        k_swapPeer<decltype(V)::value><<<grid, kBlock, 0, stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
+        k_swapPeer<decltype(V)::value><<<grid, threads, 0, stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
     });
     launched();
 }
@@ -1117,6 +1121,11 @@ QuESTEnv createQuESTEnv(void) {
         comm::init(ln, g.device, g.stream);
         if (const char* s = std::getenv("QUEST_B200_OVERLAP")) g.overlap = std::atoi(s) != 0;
         if (const char* s = std::getenv("QUEST_B200_SWAP_CTAS")) g.swapCtasPerSm = std::max(1, std::min(8, std::atoi(s)));
+        if (const char* s = std::getenv("QUEST_B200_SWAP_THREADS")) g.swapThreads = std::max(32, std::min(256, std::atoi(s) & ~31));
+        // the exchange kernel shares SMs with the fused pass: both must ask for the same shared-memory carve-out
+        CUDA_OK(cudaFuncSetAttribute(k_swapPeer<4>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CUDA_OK(cudaFuncSetAttribute(k_swapPeer<2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CUDA_OK(cudaFuncSetAttribute(k_swapPeer<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         if (const char* s = std::getenv("QUEST_B200_OVERLAP_MIN_BITS")) g.overlapMinBits = std::max(8, std::atoi(s));
         int lowPrio = 0, highPrio = 0;
         CUDA_OK(cudaDeviceGetStreamPriorityRange(&lowPrio, &highPrio));

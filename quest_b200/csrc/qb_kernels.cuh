@@ -151,8 +151,8 @@ template <int VEC>
 __global__ void __launch_bounds__(kBlock) k_swapPeer(qreal* __restrict__ aRe, qreal* __restrict__ aIm,
                                                     qreal* __restrict__ bRe, qreal* __restrict__ bIm,
                                                     unsigned long long nTasks, BitPlan plan, int lvb) {
-    const unsigned long long stride = (unsigned long long)gridDim.x * kBlock;
-    for (unsigned long long k = (unsigned long long)blockIdx.x * kBlock + threadIdx.x; k < nTasks; k += stride) {
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; k < nTasks; k += stride) {
         const unsigned long long vi = expand(k, plan);
         const unsigned long long ib = vi * VEC, ia = ib + ((unsigned long long)VEC << lvb);
         const Vec<qreal, VEC> ar = load<VEC>(aRe + ia), ai = load<VEC>(aIm + ia);

@@ -227,12 +227,16 @@ __device__ __forceinline__ unsigned int insertZero(unsigned int k, int b) {
     return ((k >> b) << (b + 1)) | low;
 }
 
-#ifndef QB_TILE_MINB
-#define QB_TILE_MINB 4
+// Four CTAs of 128 threads per SM.  The register budget is set a little under a quarter of the register file (120, not
+// 128): on a sharded register the qubit-slot exchange (k_swapPeer, one small CTA per SM on the communication stream) has
+// to fit NEXT to four resident pass CTAs - with 128 registers per thread the pass owns the whole file, an exchange CTA
+// can only take the place of a pass CTA, and every pass that overlaps an exchange loses a quarter of its occupancy.
+#ifndef QB_TILE_MAXREG
+#define QB_TILE_MAXREG 120
 #endif
 
 template <int TIER, bool FMA>
-__global__ void __launch_bounds__(kTileThreads, QB_TILE_MINB) k_tile(qreal* __restrict__ re, qreal* __restrict__ im,
+__global__ void __maxnreg__(QB_TILE_MAXREG) k_tile(qreal* __restrict__ re, qreal* __restrict__ im,
                                                                    const __grid_constant__ TileLaunch tl) {
     constexpr unsigned int kTileElems = 1u << kTileBits;
     __shared__ qreal sAmp[2 * kTileElems];          // real parts, then imaginary parts: one address register serves both
