@@ -23,6 +23,10 @@
 
 namespace qb {
 
+#ifndef QB_SWAP_IMPL
+#define QB_SWAP_IMPL forEachPair
+#endif
+
 constexpr int kRegBits = kSubBits + kSpectBits;        // index bits a thread holds in registers
 constexpr int kSubElems = 1 << kRegBits;                // 16 amplitudes per thread
 constexpr int kTileThreads = 1 << (kTileBits - kRegBits);  // one register block per thread: 128 threads per CTA
@@ -115,6 +119,32 @@ __device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 <
     for (int e = 0; e < (1 << R); ++e)
         if ((e & MASK) == MASK) fn(xr[e], xi[e]);
 }
+// Pair operations with the control mask as a compile-time constant (the caller switches on the 8 possible values): a
+// swap is a handful of register moves per pair, which the compiler predicates when the mask is a run-time value -
+// executing the moves of all eight pairs for every controlledNot.  MASK never contains bit P.
+template <int P, int MASK, int R, class PairFn>
+__device__ __forceinline__ void forMaskedPairs(qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
+#pragma unroll
+    for (int e = 0; e < (1 << R); ++e) {
+        if ((e >> P) & 1) continue;
+        if ((e & MASK) == MASK) fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
+    }
+}
+template <int P, int R, class PairFn>
+__device__ __forceinline__ void forPairsByMask(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
+    static_assert(kSubBits == 3, "eight register masks: the spectator bit is never part of a mask");
+    switch (regMask & ~(1u << P)) {
+        case 0: forMaskedPairs<P, 0, R>(xr, xi, fn); break;
+        case 1: forMaskedPairs<P, 1 & ~(1 << P), R>(xr, xi, fn); break;
+        case 2: forMaskedPairs<P, 2 & ~(1 << P), R>(xr, xi, fn); break;
+        case 3: forMaskedPairs<P, 3 & ~(1 << P), R>(xr, xi, fn); break;
+        case 4: forMaskedPairs<P, 4 & ~(1 << P), R>(xr, xi, fn); break;
+        case 5: forMaskedPairs<P, 5 & ~(1 << P), R>(xr, xi, fn); break;
+        case 6: forMaskedPairs<P, 6 & ~(1 << P), R>(xr, xi, fn); break;
+        default: forMaskedPairs<P, 7 & ~(1 << P), R>(xr, xi, fn); break;
+    }
+}
+
 template <int R, class ElemFn>
 __device__ __forceinline__ void forSelectedByMask(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, ElemFn fn) {
     static_assert(kSubBits == 3, "eight register masks: the spectator bit is never part of a mask");
@@ -188,7 +218,7 @@ __device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int o
             else forEachPair<P, kRegBits>(xr, xi, regMask, m);
         })
         QB_POS3(kOpHadamard, forEveryPair<P, kRegBits>(xr, xi, OpHadamard{C(0)}))  // the API has no controlled hadamard
-        QB_POS3(kOpSwap, forEachPair<P, kRegBits>(xr, xi, regMask, OpSwap{}))
+        QB_POS3(kOpSwap, QB_SWAP_IMPL<P, kRegBits>(xr, xi, regMask, OpSwap{}))
         QB_POS3(kOpPauliY, forEachPair<P, kRegBits>(xr, xi, regMask, OpPauliY{C(0)}))
         case kOpPhase: forSelectedByMask<kRegBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
         case kOpFlip: forSelectedByMask<kRegBits>(xr, xi, regMask, DiagFlip{}); break;
