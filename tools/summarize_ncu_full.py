@@ -1,15 +1,18 @@
 #!/usr/bin/env python3
 """Markdown summary of every launch in an `ncu --set full` report: time, DRAM bytes (traffic), DRAM throughput, the busiest
 pipes, occupancy, top stall reasons.   python tools/summarize_ncu_full.py <rep> [algorithmic-bytes-json]
-The optional JSON maps a kernel-name substring to its algorithmic bytes per launch (traffic / algorithmic is printed)."""
+The optional JSON list gives the algorithmic bytes of every launch, in launch order (traffic / algorithmic is printed)."""
 import csv
 import json
 import subprocess
 import sys
 
 rep = sys.argv[1]
-algo = json.load(open(sys.argv[2])) if len(sys.argv) > 2 else {}
-out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+algo = json.loads(sys.argv[2]) if len(sys.argv) > 2 else []   # algorithmic bytes per launch, in launch order
+if rep.endswith(".csv"):   # a raw page exported on the GPU box (`ncu -i rep --page raw --csv`): reports are too big to bring back
+    out = open(rep).read()
+else:
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hdr, units, data = rows[0], rows[1], rows[2:]
 col = {h: i for i, h in enumerate(hdr)}
@@ -44,7 +47,7 @@ for i, r in enumerate(data):
     name = r[col["Kernel Name"]]
     short = name.split("(")[0].replace("void qb::", "").replace("void ", "")
     rd, wr = to_bytes(r, "dram__bytes_read.sum"), to_bytes(r, "dram__bytes_write.sum")
-    a = next((v for k, v in algo.items() if k in name), None)
+    a = algo[i] if i < len(algo) else None
     top = sorted(((val(r, h, 0.0), h[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")]) for h in stalls), reverse=True)[:3]
     print(f"| {i} | `{short}` | {r[col['Grid Size']]} x {r[col['Block Size']]} | {to_ms(r, 'gpu__time_duration.sum'):.3f} | "
           f"{rd / 1e9:.2f} + {wr / 1e9:.2f} = {(rd + wr) / 1e9:.2f} | {((rd + wr) / a):.3f} |" if a else
