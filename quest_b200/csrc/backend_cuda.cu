@@ -74,6 +74,7 @@ struct Engine {
     unsigned long long launches = 0;
     bool fuse = true;               // QUEST_B200_FUSE / qb200_setFusion: record gates and run them in fused passes
     unsigned long long fusedLaunches = 0, fusedGates = 0;
+    bool peephole = true;           // QUEST_B200_PEEPHOLE: hadamard + matrix on the same target share one dispatch
     bool contract = false;          // QUEST_B200_FMA / qb200_setArithmetic: fused pass may contract a*b+c into fma
     bool remap = true;              // QUEST_B200_REMAP: make shard-selecting qubits local by slot exchange
     unsigned long long slotSwaps = 0;
@@ -292,6 +293,15 @@ void runOpNow(const Qureg& q, const PendingOp& op) {
         case kFMatrix:
             cross ? runPairsAcrossShards(q, op.target, op.mask, matrixOf(op)) : runPairsNow(q, op.target, op.mask, matrixOf(op));
             break;
+        case kFHadMatrix: {  // a fused pair that ended up alone in a pass: its two gates, one kernel each
+            PendingOp h = op, m = op;
+            h.kind = kFHadamard;
+            h.c[0] = op.c[8];
+            m.kind = kFMatrix;
+            runOpNow(q, h);
+            runOpNow(q, m);
+            break;
+        }
         case kFHadamard:
             cross ? runPairsAcrossShards(q, op.target, op.mask, OpHadamard{op.c[0]}) : runPairsNow(q, op.target, op.mask, OpHadamard{op.c[0]});
             break;
@@ -395,14 +405,10 @@ void launchPrepared(QuregRec* r, const TilePass& p, int tier, const SlabPlan* sp
     tl.nRuns = nRuns;
     tl.slabMask = sp ? sp->valueMask(slab) : 0;
     const unsigned int nb = (unsigned int)((u64)r->n >> __builtin_popcountll(held));
-    if (tier == kTierNoise && g.contract)
-        k_tile<kTierNoise, true><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
-    else if (tier == kTierNoise)
-        k_tile<kTierNoise, false><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
-    else if (g.contract)
-        k_tile<kTierGates, true><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
-    else
-        k_tile<kTierGates, false><<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl);
+    auto go = [&](auto kernel) { kernel<<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl); };
+    if (tier == kTierNoise) g.contract ? go(k_tile<kTierNoise, true>) : go(k_tile<kTierNoise, false>);
+    else if (tier == kTierGates) g.contract ? go(k_tile<kTierGates, true>) : go(k_tile<kTierGates, false>);
+    else g.contract ? go(k_tile<kTierCore, true>) : go(k_tile<kTierCore, false>);
     launched();
 }
 
@@ -489,6 +495,7 @@ void flushBehindUpload(const Qureg& q) {
     QuregRec* r = rec(q);
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
+    if (g.peephole) ops = fuseAdjacentPairs(ops);
     const SlabPlan sp = r->uploadPlan;
     const std::vector<TilePass> passes = planPasses(ops, r->localBits, bitsOf(sp));
     size_t nFollow = 0;
@@ -529,6 +536,7 @@ void flush(const Qureg& q) {
     }
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
+    if (g.peephole) ops = fuseAdjacentPairs(ops);
     const std::vector<TilePass> passes = planPasses(ops, r->localBits, pending ? bitsOf(g.pendingPlan) : 0);
     size_t first = 0;
     if (pending) {
@@ -628,6 +636,7 @@ void flushSharded(const Qureg& q) {
     }
     std::vector<PendingOp> logicalOps;
     logicalOps.swap(r->queue);
+    if (g.peephole) logicalOps = fuseAdjacentPairs(logicalOps);
     std::vector<WalkOp> walk(logicalOps.size());
     for (size_t i = 0; i < logicalOps.size(); ++i) {
         const PendingOp& op = logicalOps[i];
@@ -1102,13 +1111,13 @@ QuESTEnv createQuESTEnv(void) {
     CUDA_OK(cudaMalloc(&g.dWide, kProbAll * sizeof(double)));
     CUDA_OK(cudaHostAlloc(&g.hWide, kProbAll * sizeof(double), cudaHostAllocDefault));
     // the fused pass keeps 32 KiB of shared memory per CTA and wants 3 CTAs per SM: ask for the large carve-out
-    CUDA_OK(cudaFuncSetAttribute(k_tile<kTierGates, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CUDA_OK(cudaFuncSetAttribute(k_tile<kTierGates, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CUDA_OK(cudaFuncSetAttribute(k_tile<kTierNoise, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CUDA_OK(cudaFuncSetAttribute(k_tile<kTierNoise, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    for (auto kernel : {k_tile<kTierCore, false>, k_tile<kTierCore, true>, k_tile<kTierGates, false>, k_tile<kTierGates, true>,
+                        k_tile<kTierNoise, false>, k_tile<kTierNoise, true>})
+        CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     if (const char* s = std::getenv("QUEST_B200_PROB_CACHE")) g.probCache = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_FUSE")) g.fuse = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_FMA")) g.contract = std::atoi(s) != 0;
+    if (const char* s = std::getenv("QUEST_B200_PEEPHOLE")) g.peephole = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_REMAP")) g.remap = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_VEC")) {
         int v = std::atoi(s);

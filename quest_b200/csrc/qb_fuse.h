@@ -49,10 +49,16 @@ enum FusedKind : int { kFMatrix = 0, kFHadamard = 1, kFSwap = 2, kFPauliY = 3, k
                        // qubit's row bit and column bit (two dense targets); symmetric under exchanging the two
                        kFDephase = 6, kFDepolarise = 7, kFDamping = 8,
                        // density-matrix collapse: block (o,o) of the (row,column) structure /= c[0], other blocks = 0; c[1] = o
-                       kFDensCollapse = 9 };
+                       kFDensCollapse = 9,
+                       // made by the planner, never recorded: an uncontrolled hadamard immediately followed by an uncontrolled
+                       // matrix gate on the same qubit, executed pair by pair with one dispatch (c = the matrix)
+                       kFHadMatrix = 10 };
 
 inline bool isDiagonal(int kind) { return kind == kFPhase || kind == kFFlip; }
-inline bool isNoise(int kind) { return kind >= kFDephase; }
+inline bool isNoise(int kind) { return kind >= kFDephase && kind <= kFDensCollapse; }
+
+struct PendingOp;
+inline std::vector<PendingOp> fuseAdjacentPairs(const std::vector<PendingOp>& ops);
 
 // A recorded gate: target and control mask are LOCAL bit positions of this rank's shard (controls on
 // shard-selecting qubits were already resolved when the gate was recorded).
@@ -61,7 +67,7 @@ struct PendingOp {
     int target;                    // dense kinds only
     int target2;                   // noise kinds: the second bit of the (row, column) pair; otherwise -1
     unsigned long long mask;       // dense: control mask; diagonal: all selecting bits
-    qreal c[8];                    // Matrix: r00,i00,r01,i01,r10,i10,r11,i11; Hadamard: c[0]=1/sqrt2;
+    qreal c[9];                    // Matrix: r00,i00,r01,i01,r10,i10,r11,i11; Hadamard: c[0]=1/sqrt2; HadMatrix: matrix + c[8]=1/sqrt2;
                                    // PauliY: c[0]=+-1; Phase: c[0]=cos, c[1]=sin; noise: c[0]=factor on
                                    // coherences, c[1]=level, c[2]=1-level (see k_noise1)
 };
@@ -207,8 +213,9 @@ enum TileOpcode : int {   // dense numbering: the kernel's switch compiles to on
     kOpPauliY = 9,      // +pos
     kOpPhase = 12,
     kOpFlip = 13,
-    kOpNoise = 14,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
-    kOpCount = 26
+    kOpHadMatrix = 14,  // +pos
+    kOpNoise = 17,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
+    kOpCount = 29
 };
 // (p, q), p < q < 3  ->  0..2
 inline int pairSlot(int p, int q) { return p + q - 1; }
@@ -254,6 +261,7 @@ inline TileGate describe(const PendingOp& op, const TilePass& p, const TileSub& 
         case kFPauliY: tg.opcode = kOpPauliY + tg.pos; break;
         case kFPhase: tg.opcode = kOpPhase; break;
         case kFFlip: tg.opcode = kOpFlip; break;
+        case kFHadMatrix: tg.opcode = kOpHadMatrix + tg.pos; break;
         default: tg.opcode = kOpNoise + (op.kind - kFDephase) * 3 + pairSlot(tg.pos, tg.pos2); break;
     }
     return tg;
@@ -272,7 +280,35 @@ inline unsigned int tilePlace(unsigned int i) {
     return i ^ ((h ^ (h << 1) ^ (h << 3)) & 15u);
 }
 
-// Kernel tier this opcode needs: 0 = state-vector gates, 1 = + density-matrix noise and collapse.
-inline int tierOf(int opcode) { return opcode >= kOpNoise ? 1 : 0; }
+// Peephole on a recorded queue: hadamard(t) directly followed by an uncontrolled matrix gate on t becomes ONE op.  The
+// kernel applies the same two per-pair expressions one after the other (every product and sum still rounded
+// separately: bit-identical), but pays the gate dispatch - a dependent chain of constant loads and branches that costs
+// as much as the hadamard's arithmetic - once instead of twice.
+inline std::vector<PendingOp> fuseAdjacentPairs(const std::vector<PendingOp>& ops) {
+    std::vector<PendingOp> out;
+    out.reserve(ops.size());
+    for (size_t i = 0; i < ops.size(); ++i) {
+        if (i + 1 < ops.size() && ops[i].kind == kFHadamard && ops[i].mask == 0 && ops[i + 1].kind == kFMatrix &&
+            ops[i + 1].mask == 0 && ops[i + 1].target == ops[i].target) {
+            PendingOp f = ops[i + 1];
+            f.kind = kFHadMatrix;
+            f.c[8] = ops[i].c[0];  // the hadamard's own factor, (qreal)(1.0 / sqrt(2)) as the front end formed it
+            out.push_back(f);
+            ++i;
+        } else {
+            out.push_back(ops[i]);
+        }
+    }
+    return out;
+}
+
+// Kernel tier this opcode needs: 0 = the common state-vector gates (matrix, hadamard, swap / controlledNot, phase), 1 = every
+// state-vector gate (+ pauliY, phase flip), 2 = + density-matrix noise and collapse.  A pass runs on the maximum over its
+// gates: the dispatch code a pass does not need is code its instruction cache does not have to hold.
+inline int tierOf(int opcode) {
+    if (opcode >= kOpNoise) return 2;
+    if ((opcode >= kOpPauliY && opcode < kOpPhase) || opcode == kOpFlip) return 1;
+    return 0;
+}
 
 }  // namespace qb

@@ -64,7 +64,7 @@ struct TileLaunch {
     TileSubDesc sub[kMaxTileSubs];
     TileGateCtl ctl[kMaxTileGates];
     unsigned long long outerMask[kMaxTileGates];  // control/selecting bits outside the tile
-    qreal c[kMaxTileGates][8];         // coefficients (meaning per kind: qb_fuse.h PendingOp::c)
+    qreal c[kMaxTileGates][9];         // coefficients (meaning per kind: qb_fuse.h PendingOp::c)
 };
 
 // OpMatrix with the four outputs built up side by side: every product that reads an old value is issued before the
@@ -191,8 +191,9 @@ __device__ __forceinline__ void noiseQuads(qreal (&xr)[1 << R], qreal (&xi)[1 <<
     }
 }
 
-enum TileTier : int { kTierGates = 0,   // every state-vector gate
-                      kTierNoise = 1 }; // + density-matrix noise channels and collapse
+enum TileTier : int { kTierCore = 0,    // matrix, hadamard, swap / controlledNot, phase (and the fused hadamard + matrix)
+                      kTierGates = 1,   // every state-vector gate
+                      kTierNoise = 2 }; // + density-matrix noise channels and collapse
 
 #define QB_POS3(BASE, ...)                                             \
     case (BASE) + 0: { constexpr int P = 0; __VA_ARGS__; } break;      \
@@ -206,11 +207,16 @@ enum TileTier : int { kTierGates = 0,   // every state-vector gate
 // One recorded gate on the 8 amplitudes a thread holds in registers: a single jump on the host-made opcode into code
 // for that (kind, register position).  Coefficients come straight from the constant bank (kernel parameters).
 template <int TIER, bool FMA>
-__device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int opcode, unsigned int regMask,
+__device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int opcode, unsigned int regMask, qreal c0, qreal c1,
                                               qreal (&xr)[kSubElems], qreal (&xi)[kSubElems]) {
     using Matrix = typename std::conditional<FMA, TileMatrixFma, TileMatrix>::type;
     using Phase = typename std::conditional<FMA, DiagPhaseFma, DiagPhase>::type;
+    // the first two coefficients were fetched together with the control word, one gate ahead (QB_TILE_PREFETCH_C)
+#ifdef QB_TILE_PREFETCH_C
+#define C(i) ((i) == 0 ? c0 : (i) == 1 ? c1 : tl.c[g][i])
+#else
 #define C(i) tl.c[g][i]
+#endif
     switch (opcode) {
         QB_POS3(kOpMatrix, {
             const Matrix m{C(0), C(1), C(2), C(3), C(4), C(5), C(6), C(7)};
@@ -218,10 +224,21 @@ __device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int o
             else forEachPair<P, kRegBits>(xr, xi, regMask, m);
         })
         QB_POS3(kOpHadamard, forEveryPair<P, kRegBits>(xr, xi, OpHadamard{C(0)}))  // the API has no controlled hadamard
+        QB_POS3(kOpHadMatrix, {  // hadamard, then a matrix gate, on the same uncontrolled target (qb::fuseAdjacentPairs)
+            const Matrix m{C(0), C(1), C(2), C(3), C(4), C(5), C(6), C(7)};
+            const OpHadamard h{C(8)};
+            forEveryPair<P, kRegBits>(xr, xi, [&](qreal& uR, qreal& uI, qreal& lR, qreal& lI) {
+                h(uR, uI, lR, lI);
+                m(uR, uI, lR, lI);
+            });
+        })
         QB_POS3(kOpSwap, QB_SWAP_IMPL<P, kRegBits>(xr, xi, regMask, OpSwap{}))
-        QB_POS3(kOpPauliY, forEachPair<P, kRegBits>(xr, xi, regMask, OpPauliY{C(0)}))
         case kOpPhase: forSelectedByMask<kRegBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
-        case kOpFlip: forSelectedByMask<kRegBits>(xr, xi, regMask, DiagFlip{}); break;
+        QB_POS3(kOpPauliY, if constexpr (TIER >= kTierGates) forEachPair<P, kRegBits>(xr, xi, regMask, OpPauliY{C(0)}); else __builtin_unreachable())
+        case kOpFlip:
+            if constexpr (TIER >= kTierGates) forSelectedByMask<kRegBits>(xr, xi, regMask, DiagFlip{});
+            else __builtin_unreachable();
+            break;
         default:
             if constexpr (TIER == kTierNoise) {
                 switch (opcode) {
@@ -340,14 +357,18 @@ __global__ void __maxnreg__(QB_TILE_MAXREG) k_tile(qreal* __restrict__ re, qreal
             unsigned int todo = act;
             int g = gFirst + __ffs((int)todo) - 1;
             TileGateCtl ctl = tl.ctl[g];
+            qreal c0 = tl.c[g][0], c1 = tl.c[g][1];
             while (true) {
                 todo &= todo - 1u;
                 const int gNext = todo ? gFirst + __ffs((int)todo) - 1 : g;
                 const TileGateCtl next = tl.ctl[gNext];
-                if ((idx & ctl.tileMask) == ctl.tileMask) applyTileGate<TIER, FMA>(tl, g, ctl.opcode, ctl.regMask, xr, xi);
+                const qreal n0 = tl.c[gNext][0], n1 = tl.c[gNext][1];
+                if ((idx & ctl.tileMask) == ctl.tileMask) applyTileGate<TIER, FMA>(tl, g, ctl.opcode, ctl.regMask, c0, c1, xr, xi);
                 if (!todo) break;
                 g = gNext;
                 ctl = next;
+                c0 = n0;
+                c1 = n1;
             }
             {  // (addresses recomputed: keeping them alive costs registers the gates need)
                 unsigned int q[kSubElems];

@@ -55,7 +55,8 @@ def decode_opcode(opcode):
         return K_PHASE, None, None
     if opcode == 13:
         return K_FLIP, None, None
-    kind, slot = divmod(opcode - 14, 3)
+    assert opcode >= 17  # 14..16: hadamard + matrix fused by the flush-time peephole, never produced by the planner itself
+    kind, slot = divmod(opcode - 17, 3)
     return K_DEPHASE + kind, (0, 0, 1)[slot], (1, 2, 2)[slot]
 
 

@@ -14,6 +14,7 @@ ap.add_argument("--qubits", type=int, default=30)
 ap.add_argument("--steps", type=int, default=1)
 ap.add_argument("--fma", type=int, default=0)
 ap.add_argument("--circuit", default="sweep", choices=["sweep", "layers", "density"])
+ap.add_argument("--skip", default="", help="comma-separated API names to leave out of the circuit (ablation)")
 args = ap.parse_args()
 lib = capi.load_product()
 env = lib.createQuESTEnv()
@@ -26,6 +27,7 @@ if args.circuit == "density":
 else:
     q = lib.createQureg(nq, env)
     ops = circuits.config2_sweep(nq) if args.circuit == "sweep" else circuits.config1_layers(nq, layers=2)
+ops = [op for op in ops if op[0] not in args.skip.split(",")]
 lib.initPlusState(q)
 for t in range(q.numQubitsRepresented):
     lib.rotateY(q, t, 0.1 * (t + 1))
@@ -39,7 +41,7 @@ for rep in range(args.steps + 1):
     ms, n = ctypes.c_double(), ctypes.c_ulonglong()
     lib.lib.qb200_getFusedKernelTime(ctypes.byref(ms), ctypes.byref(n))
     if rep:
-        print(f"{os.environ.get('QUEST_B200_LIB', 'product')}: {args.circuit} {nq}q fma={args.fma}: {n.value} fused passes, "
+        print(f"{os.environ.get('QUEST_B200_LIB', 'product')}: {args.circuit} {nq}q fma={args.fma} skip={args.skip or '-'} ({len(ops)} gates): {n.value} fused passes, "
               f"{ms.value:.2f} ms in total, {ms.value / max(n.value, 1):.2f} ms per pass", flush=True)
 print("total prob", lib.calcTotalProb(q))
 lib.destroyQureg(q, env)
