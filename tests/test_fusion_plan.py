@@ -26,25 +26,28 @@ def _lib():
     return lib
 
 
-def plan(lib, local_bits, ops):
+def plan(lib, local_bits, ops, reorder=1):
     n = len(ops)
     kinds = (ctypes.c_int * n)(*[o[0] for o in ops])
     targets = (ctypes.c_int * n)(*[o[1] for o in ops])
     targets2 = (ctypes.c_int * n)(*[o[3] if len(o) > 3 else -1 for o in ops])
     masks = (ctypes.c_ulonglong * n)(*[o[2] for o in ops])
     passes = (ctypes.c_int * ((4 + TILE_BITS) * n))()
+    order = (ctypes.c_int * n)()
     subs = (ctypes.c_int * (7 * n))()
     desc = (ctypes.c_ulonglong * (4 * n))()
     n_subs = ctypes.c_int()
-    np_ = lib.qb200_debugTilePlan(local_bits, n, kinds, targets, targets2, masks, passes, subs, desc, ctypes.byref(n_subs))
+    np_ = lib.qb200_debugTilePlan(local_bits, n, kinds, targets, targets2, masks, reorder, passes, order, subs, desc, ctypes.byref(n_subs))
     W = 4 + TILE_BITS
     pl = [dict(first=passes[W * i], count=passes[W * i + 1], ntile=passes[W * i + 2], nsub=passes[W * i + 3],
                bits=[b for b in passes[W * i + 4:W * i + W] if b >= 0], subs=[]) for i in range(np_)]
+    for p in pl:
+        p["order"] = list(order[p["first"]:p["first"] + p["count"]])
     for j in range(n_subs.value):
         pl[subs[7 * j]]["subs"].append(dict(first=subs[7 * j + 1], count=subs[7 * j + 2], rb=list(subs[7 * j + 3:7 * j + 6]),
                                             spect=subs[7 * j + 6]))
     dl = [dict(opcode=desc[4 * i], reg=desc[4 * i + 1], tile=desc[4 * i + 2], outer=desc[4 * i + 3]) for i in range(n)]
-    return pl, dl
+    return pl, dl, list(order)
 
 
 def decode_opcode(opcode):
@@ -92,7 +95,7 @@ def insert_zeros(k, positions):
     return k
 
 
-def apply_pass(state, ops, p, descs, mats):
+def apply_pass(state, ops, p, descs, mats, order):
     """numpy twin of k_tile: CTA = tile base (tile bits at 0), tile = 2^ntile amplitudes, thread = block of 8 elements."""
     bits, T = p["bits"], p["ntile"]
     bases = insert_zeros(np.arange(state.size >> T, dtype=np.int64), bits)
@@ -105,12 +108,12 @@ def apply_pass(state, ops, p, descs, mats):
         assert sg["count"] <= MAX_SUB_GATES
         # a thread holds the 16 elements spanned by the register bits and the spectator bit; no gate of the sub-group may
         # mention the spectator bit (both 8-element halves run exactly the same gates)
-        for k in range(sg["first"], sg["first"] + sg["count"]):
+        for k in order[sg["first"]:sg["first"] + sg["count"]]:
             assert not (descs[k]["tile"] >> spect) & 1
         blocks = insert_zeros(np.arange((1 << T) >> (SUB_BITS + 1), dtype=np.int64), rb + [spect])
         blocks = np.concatenate([blocks, blocks | (1 << spect)])  # the two halves, as two 8-element blocks
         off = np.array([sum(((e >> j) & 1) << rb[j] for j in range(SUB_BITS)) for e in range(1 << SUB_BITS)], dtype=np.int64)
-        for k in range(sg["first"], sg["first"] + sg["count"]):
+        for k in order[sg["first"]:sg["first"] + sg["count"]]:
             d, u = descs[k], mats[k]
             kind, pos, pos2 = decode_opcode(d["opcode"])
             assert kind == ops[k][0]
@@ -158,40 +161,42 @@ def dense_bits(op):
     return {op[1]} | ({op[3]} if len(op) > 3 else set())
 
 
+@pytest.mark.parametrize("reorder", [1, 0], ids=["reordering", "consecutive"])
 @pytest.mark.parametrize("local_bits,seed,noise", [(4, 1, False), (4, 2, False), (5, 3, True), (7, 4, False), (10, 5, True),
                                                    (12, 6, False), (14, 7, True), (16, 8, False)])
-def test_planned_passes_reproduce_gate_by_gate(local_bits, seed, noise):
+def test_planned_passes_reproduce_gate_by_gate(local_bits, seed, noise, reorder):
     lib = _lib()
     rng = random.Random(seed)
     nrng = np.random.default_rng(seed)
     n_ops = 150
     ops = random_ops(rng, local_bits, n_ops, noise)
     mats = [unitary(nrng) for _ in ops]
-    passes, descs = plan(lib, local_bits, ops)
+    passes, descs, order = plan(lib, local_bits, ops, reorder)
     T = min(TILE_BITS, local_bits)
     low = set(range(min(TILE_LOW, T)))
-    # structure: contiguous cover in order; dense targets + low run fit the tile; sub-groups cover the pass in order
-    assert passes[0]["first"] == 0 and sum(p["count"] for p in passes) == n_ops
-    for a, b in zip(passes, passes[1:]):
-        assert b["first"] == a["first"] + a["count"]
+    # structure: every gate in exactly one pass; inside a pass program order is kept; dense targets + low run fit the
+    # tile; sub-groups cover the pass in order
+    assert sorted(order) == list(range(n_ops)) and sum(p["count"] for p in passes) == n_ops
     for p in passes:
-        dense = set().union(*[dense_bits(ops[i]) for i in range(p["first"], p["first"] + p["count"])])
+        assert p["order"] == sorted(p["order"])
+        dense = set().union(*[dense_bits(ops[i]) for i in p["order"]])
         assert p["ntile"] == T and len(p["bits"]) == T and p["bits"] == sorted(set(p["bits"]))
         assert (dense | low) <= set(p["bits"]) and all(0 <= b < local_bits for b in p["bits"])
         assert p["subs"][0]["first"] == p["first"] and sum(s["count"] for s in p["subs"]) == p["count"]
         for s in p["subs"]:
-            sd = set().union(*[dense_bits(ops[i]) for i in range(s["first"], s["first"] + s["count"])])
+            sd = set().union(*[dense_bits(ops[i]) for i in order[s["first"]:s["first"] + s["count"]]])
             assert len(sd) <= SUB_BITS and {p["bits"].index(b) for b in sd} <= set(s["rb"])
-    # greedy maximality: a pass ends only because the next dense gate does not fit the tile, or it is full
-    for p, nxt in zip(passes, passes[1:]):
-        if p["count"] == MAX_GATES or len(p["subs"]) == 64:
-            continue
-        # a gate that touches more index bits than min(8, T - 1) leaves no spectator bit: it is a pass of its own
+    if not reorder:  # consecutive passes, greedy: a pass ends only because the next gate does not fit, or it is full
+        assert order == list(range(n_ops))
         loner = lambda op: len(dense_bits(op)) + bin(op[2]).count("1") > min(8, T - 1)
-        if loner(ops[nxt["first"]]) or (p["count"] == 1 and loner(ops[p["first"]])):
-            continue
-        dense = set().union(*[dense_bits(ops[i]) for i in range(p["first"], p["first"] + p["count"])])
-        assert len(dense | low | dense_bits(ops[nxt["first"]])) > T
+        for p, nxt in zip(passes, passes[1:]):
+            if p["count"] == MAX_GATES or len(p["subs"]) == 64:
+                continue
+            if loner(ops[nxt["order"][0]]) or (p["count"] == 1 and loner(ops[p["order"][0]])):
+                continue
+            dense = set().union(*[dense_bits(ops[i]) for i in p["order"]])
+            assert len(dense | low | dense_bits(ops[nxt["order"][0]])) > T
+    # whatever was reordered must have been legal: random unitaries do not commute by accident
     state = nrng.standard_normal(1 << local_bits) + 1j * nrng.standard_normal(1 << local_bits)
     want = state.copy()
     for op, u in zip(ops, mats):
@@ -199,9 +204,41 @@ def test_planned_passes_reproduce_gate_by_gate(local_bits, seed, noise):
     got = state.copy()
     for p in passes:
         if p["count"] == 1:  # flush() runs one-gate passes through the single-gate kernels
-            apply_unfused(got, ops[p["first"]], mats[p["first"]])
+            apply_unfused(got, ops[p["order"][0]], mats[p["order"][0]])
         else:
-            apply_pass(got, ops, p, descs, mats)
+            apply_pass(got, ops, p, descs, mats, order)
+    np.testing.assert_allclose(got, want, atol=1e-12)
+
+
+def test_layered_circuit_runs_qubit_block_by_qubit_block():
+    """BASELINE configs[0]: layers of hadamard on every qubit, a rotation on every qubit, a ring of controlledNots.  In
+    program order every layer of 24 one-qubit gates is 3 passes; with gates allowed to move forward past gates they
+    commute with, a whole layer (72 gates) is 3 passes."""
+    lib = _lib()
+    nq, layers = 24, 4
+    ops = []
+    for _ in range(layers):
+        ops += [(K_HAD, i, 0) for i in range(nq)] + [(K_MATRIX, i, 0) for i in range(nq)]
+        ops += [(K_SWAP, (i + 1) % nq, 1 << i) for i in range(nq)]
+    in_order, _, _ = plan(lib, nq, ops, 0)
+    moved, descs, order = plan(lib, nq, ops, 1)
+    assert len(in_order) >= 8 * layers and len(moved) <= 3 * layers + 2, (len(in_order), len(moved))
+    rng = np.random.default_rng(3)
+    mats = [unitary(rng) for _ in ops]
+    state = rng.standard_normal(1 << 12) + 1j * rng.standard_normal(1 << 12)  # the same structure on 12 qubits, executed
+    ops12 = []
+    for _ in range(3):
+        ops12 += [(K_HAD, i, 0) for i in range(12)] + [(K_MATRIX, i, 0) for i in range(12)] + [(K_SWAP, (i + 1) % 12, 1 << i) for i in range(12)]
+    mats12 = [unitary(rng) for _ in ops12]
+    passes, descs, order = plan(lib, 12, ops12, 1)
+    want, got = state.copy(), state.copy()
+    for op, u in zip(ops12, mats12):
+        apply_unfused(want, op, u)
+    for p in passes:
+        if p["count"] == 1:
+            apply_unfused(got, ops12[p["order"][0]], mats12[p["order"][0]])
+        else:
+            apply_pass(got, ops12, p, descs, mats12, order)
     np.testing.assert_allclose(got, want, atol=1e-12)
 
 
@@ -212,9 +249,9 @@ def test_sweep_step_needs_four_passes_at_30_qubits():
     for t in range(30):
         ops += [(K_HAD, t, 0), (K_MATRIX, t, 0), (K_SWAP, t, 1 << ((t + 1) % 30)),
                 (K_PHASE, -1, (1 << t) | (1 << ((t + 1) % 30)) | (1 << ((t + 2) % 30)))]
-    passes, _ = plan(lib, 30, ops)
+    passes, _, _ = plan(lib, 30, ops)
     assert len(passes) == 4, [p["count"] for p in passes]
-    assert [p["count"] for p in passes][0] == 44  # targets 0..10
+    assert [p["count"] for p in passes][0] >= 44  # targets 0..10 (plus phase gates that could move forward)
 
 
 def test_shared_memory_placement_is_a_conflict_light_bijection():

@@ -375,3 +375,29 @@ def test_api_fuzz_vs_oracle(product, product_env, oracle, oracle_env, nq, seed):
     np.testing.assert_allclose(a, b, rtol=1e-12, atol=1e-13)
     for k in sa:
         np.testing.assert_allclose(sa[k], sb[k], rtol=0, atol=1e-13 * max(1.0, np.abs(sb[k]).max()))
+
+
+# ---- opt-in gate reordering (qb200_setReordering): commuting gates may change places --------------------------------
+
+@pytest.mark.parametrize("nq,dens,seed", [(13, False, 31), (18, False, 32), (22, False, 33), (9, True, 34)])
+def test_reordering_mode_stays_within_tolerance(product, product_env, oracle, oracle_env, nq, dens, seed):
+    """With reordering on, gates move forward past gates they commute with (fewer passes).  That changes the order of
+    roundings, so the bar is the north_star tolerance (1e-12 relative), not bit-identity; the default mode, checked by
+    every other test of this file, stays bit-identical."""
+    import ctypes as C
+
+    product.lib.qb200_setReordering.argtypes = [C.c_int]
+    ops = circuits.random_circuit(nq, 260, seed, density=dens, measure=False)
+    # a layered tail (one kind of gate on every qubit at a time): the shape reordering is meant for
+    for l in range(3):
+        ops += [("hadamard", i) for i in range(nq)] + [("rotateY", i, 0.1 * (i + 1) + 0.01 * l) for i in range(nq)]
+        ops += [("controlledNot", i, (i + 1) % nq) for i in range(nq)]
+        if dens:
+            ops += [("applyOneQubitDepolariseError", i, 0.03) for i in range(nq)]
+    product.lib.qb200_setReordering(1)
+    try:
+        (gs, gv), (cs, cv) = _side_by_side(product, product_env, oracle, oracle_env, nq, dens, ops, seed)
+    finally:
+        product.lib.qb200_setReordering(0)
+    np.testing.assert_allclose(gv, cv, rtol=REL, atol=1e-13)
+    np.testing.assert_allclose(gs, cs, rtol=0, atol=REL * np.abs(cs).max())

@@ -28,13 +28,15 @@ def main():
     lib = capi.load_product()
     env = lib.createQuESTEnv()
     lib.lib.qb200_setFusion.argtypes = [ctypes.c_int]
+    lib.lib.qb200_setReordering.argtypes = [ctypes.c_int]
     lib.lib.qb200_getLaunchCount.restype = ctypes.c_ulonglong
     out = {}
 
     def timed(make_qureg, prep, ops, label):
         res = {}
-        for mode, name in ((0, "gate_at_a_time"), (1, "fused")):
-            lib.lib.qb200_setFusion(mode)
+        for mode, name in ((0, "gate_at_a_time"), (1, "fused"), (2, "fused_reordering")):
+            lib.lib.qb200_setFusion(1 if mode else 0)
+            lib.lib.qb200_setReordering(1 if mode == 2 else 0)
             q = make_qureg()
             prep(q)
             circuits.run_circuit(lib, q, ops[: min(len(ops), 40)])  # warm-up
@@ -51,6 +53,10 @@ def main():
         a, b = np.array(res["gate_at_a_time"]["scalars"]), np.array(res["fused"]["scalars"])
         res["modes_agree_exactly"] = bool(np.array_equal(a, b))
         res["speedup_fused"] = res["gate_at_a_time"]["seconds"] / res["fused"]["seconds"]
+        c = np.array(res["fused_reordering"]["scalars"])
+        res["reordering_max_rel_diff_of_scalars"] = float(np.max(np.abs(c - b) / np.maximum(np.abs(b), 1e-300))) if b.size else 0.0
+        res["speedup_reordering"] = res["gate_at_a_time"]["seconds"] / res["fused_reordering"]["seconds"]
+        lib.lib.qb200_setReordering(0)
         out[label] = res
         print(label, {k: (v if not isinstance(v, dict) else {kk: vv for kk, vv in v.items() if kk != "scalars"}) for k, v in res.items()}, flush=True)
         return res
@@ -78,8 +84,21 @@ def main():
         lib.syncQuESTEnv(env)
         gpu_s = time.perf_counter() - t0
         got = lib.get_state(gq)
+        # the same with opt-in reordering (qb200_setReordering): layers run qubit block by qubit block
+        lib.lib.qb200_setReordering(1)
+        lib.initZeroState(gq)
+        lib.syncQuESTEnv(env)
+        t0 = time.perf_counter()
+        circuits.run_circuit(lib, gq, ops1)
+        lib.syncQuESTEnv(env)
+        gpu_reordered_s = time.perf_counter() - t0
+        got_reordered = lib.get_state(gq)
+        lib.lib.qb200_setReordering(0)
         lib.destroyQureg(gq, env)
         out[f"config1_layers_{n1}q"] = {
+            "gpu_seconds_with_reordering": gpu_reordered_s, "gpu_gates_per_s_with_reordering": len(ops1) / gpu_reordered_s,
+            "reordering_max_abs_diff": float(np.abs(got_reordered - want).max()),
+            "reordering_max_rel_diff": float(np.abs(got_reordered - want).max() / np.abs(want).max()),
             "gates": len(ops1), "cpu_reference_seconds": cpu_s, "cpu_gates_per_s": len(ops1) / cpu_s,
             "cpu_threads": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count())), "gpu_seconds": gpu_s,
             "gpu_gates_per_s": len(ops1) / gpu_s, "speedup": cpu_s / gpu_s,
@@ -99,7 +118,7 @@ def main():
               circuits.config4_noisy(nd, args.layers), f"config4_noisy_density_{nd}q")
     out[f"config4_noisy_density_{nd}q"]["purity_per_layer"] = r["fused"]["scalars"]
     for v in out.values():
-        for m in ("gate_at_a_time", "fused"):
+        for m in ("gate_at_a_time", "fused", "fused_reordering"):
             if m in v:
                 v[m].pop("scalars", None)
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
