@@ -362,7 +362,7 @@ int preparePass(const std::vector<PendingOp>& ops, const TilePass& p, const std:
             tl.ctl[g] = TileGateCtl{(unsigned short)tg.tileMask, (unsigned char)tg.opcode, (unsigned char)tg.regMask};
             tl.outerMask[g] = tg.outerMask;
             std::memcpy(tl.c[g], ops[k].c, sizeof ops[k].c);
-            tier |= tierOf(tg.opcode);
+            tier = std::max(tier, tierOf(tg.opcode));  // the tiers are nested
             ++g;
         }
         d.count = g - d.first;
@@ -409,7 +409,7 @@ void launchPrepared(QuregRec* r, const TilePass& p, int tier, const SlabPlan* sp
     tl.slabMask = sp ? sp->valueMask(slab) : 0;
     const unsigned int nb = (unsigned int)((u64)r->n >> __builtin_popcountll(held));
     auto go = [&](auto kernel) { kernel<<<nb, kTileThreads, 0, g.stream>>>(r->re, r->im, tl); };
-    if (tier == kTierNoise) g.contract ? go(k_tile<kTierNoise, true>) : go(k_tile<kTierNoise, false>);
+    if (tier >= kTierNoise) g.contract ? go(k_tile<kTierNoise, true>) : go(k_tile<kTierNoise, false>);
     else if (tier == kTierGates) g.contract ? go(k_tile<kTierGates, true>) : go(k_tile<kTierGates, false>);
     else g.contract ? go(k_tile<kTierCore, true>) : go(k_tile<kTierCore, false>);
     launched();

@@ -401,3 +401,17 @@ def test_reordering_mode_stays_within_tolerance(product, product_env, oracle, or
         product.lib.qb200_setReordering(0)
     np.testing.assert_allclose(gv, cv, rtol=REL, atol=1e-13)
     np.testing.assert_allclose(gs, cs, rtol=0, atol=REL * np.abs(cs).max())
+
+
+def test_pass_mixing_every_gate_family_picks_the_widest_kernel_tier(product, product_env, oracle, oracle_env):
+    """One pass that holds gates of all three kernel tiers (common gates; pauliY / phase flip; density-matrix noise):
+    it has to run on the tier that understands all of them."""
+    nq = 6
+    ops = []
+    for t in range(nq):
+        ops += [("hadamard", t), ("pauliY", t), ("controlledPhaseFlip", t, (t + 1) % nq), ("applyOneQubitDepolariseError", t, 0.1),
+                ("rotateX", t, 0.3 + t), ("controlledPauliY", (t + 2) % nq, t), ("applyOneQubitDampingError", t, 0.05),
+                ("multiControlledPhaseFlip", [t, (t + 1) % nq, (t + 3) % nq]), ("applyOneQubitDephaseError", t, 0.07)]
+    (gs, gv), (cs, cv) = _side_by_side(product, product_env, oracle, oracle_env, nq, True, ops + [("calcPurity",)], 3)
+    assert np.array_equal(gs.view(np.float64), cs.view(np.float64))
+    np.testing.assert_allclose(gv, cv, rtol=REL, atol=1e-13)
