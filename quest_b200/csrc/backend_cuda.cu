@@ -1620,9 +1620,13 @@ void densmatr_oneQubitDamping(Qureg q, const int t, qreal damping) {
 static void dephase2Now(const Qureg& q, QuregRec* r, int q1, int q2, qreal retain) {
     const int n = q.numQubitsRepresented;
     const QubitMap& m = r->map;
-    k_dephase2<<<blocksFor((u64)r->n), kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, (u64)q.chunkId * r->n,
-                                                             1ull << m.phys[q1], 1ull << m.phys[q1 + n],
-                                                             1ull << m.phys[q2], 1ull << m.phys[q2 + n], retain);
+    const int vec = pickVec(r->n);
+    const u64 nVec = (u64)r->n / vec;
+    dispatchV(vec, [&](auto V) {
+        k_dephase2<decltype(V)::value><<<blocksFor(nVec), kBlock, 0, g.stream>>>(
+            r->re, r->im, nVec, (u64)q.chunkId * r->n, 1ull << m.phys[q1], 1ull << m.phys[q1 + n], 1ull << m.phys[q2],
+            1ull << m.phys[q2 + n], retain);
+    });
     launched();
 }
 
@@ -1663,15 +1667,20 @@ void densmatr_twoQubitDepolarise(Qureg q, int q1, int q2, qreal level) {
     qreal delta = eta - 1 - sqrt((double)((eta - 1) * (eta - 1) - 1));
     qreal gamma = 1 + delta;
     gamma = 1 / (gamma * gamma * gamma);
-    dephase2Now(q, r, q1, q2, 1 - level);
+    // all four bits are local now: ONE pass over the 16-element blocks they span (k_depol2)
     const QubitMap& m = r->map;
-    const u64 tot1 = (1ull << m.phys[q1]) | (1ull << m.phys[q1 + n]), tot2 = (1ull << m.phys[q2]) | (1ull << m.phys[q2 + n]);
-    const unsigned int nb = blocksFor((u64)r->n);
-    k_depol2Sweep<<<nb, kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, tot1, tot2, 0, delta, 1);
-    launched();
-    k_depol2Sweep<<<nb, kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, tot2, tot1, 0, delta, 1);
-    launched();
-    k_depol2Sweep<<<nb, kBlock, 0, g.stream>>>(r->re, r->im, (u64)r->n, tot2, tot1, tot1, delta, gamma);
+    const int bits[4] = {m.phys[q1], m.phys[q1 + n], m.phys[q2], m.phys[q2 + n]};
+    Depol2 d;
+    for (int e = 0; e < 16; ++e) {
+        d.offs[e] = 0;
+        for (int j = 0; j < 4; ++j)
+            if ((e >> j) & 1) d.offs[e] |= 1ull << bits[j];
+    }
+    d.retain = 1 - level;
+    d.delta = delta;
+    d.gamma = gamma;
+    const Planned p = makePlan(r->n, 1, {bits[0], bits[1], bits[2], bits[3]}, 0);
+    k_depol2<<<blocksFor(p.nTasks), kBlock, 0, g.stream>>>(r->re, r->im, p.nTasks, p.plan, d);
     launched();
 }
 

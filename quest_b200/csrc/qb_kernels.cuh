@@ -595,36 +595,78 @@ __global__ void __launch_bounds__(kBlock) k_noise1(qreal* __restrict__ re, qreal
 // ---- second-tier density operations: simple one-amplitude-per-thread kernels --------------------------
 
 // two-qubit dephase: scale every element where either qubit's row and column bits differ
-// (reference QuEST_cpu.c:102-114)
+// (reference QuEST_cpu.c:102-114).  One vector per thread; the four bits are tested on the GLOBAL index of every lane.
+template <int VEC>
 __global__ void __launch_bounds__(kBlock) k_dephase2(qreal* __restrict__ re, qreal* __restrict__ im,
-                                                    unsigned long long n, unsigned long long off,
+                                                    unsigned long long nVec, unsigned long long off,
                                                     unsigned long long in1, unsigned long long out1,
                                                     unsigned long long in2, unsigned long long out2, qreal retain) {
-    const unsigned long long i = (unsigned long long)blockIdx.x * kBlock + threadIdx.x;
-    if (i >= n) return;
-    const unsigned long long p1 = (i + off) & (in1 | out1), p2 = (i + off) & (in2 | out2);
-    if (p1 == in1 || p1 == out1 || p2 == in2 || p2 == out2) {
-        re[i] = retain * re[i];
-        im[i] = retain * im[i];
+    const unsigned long long k = (unsigned long long)blockIdx.x * kBlock + threadIdx.x;
+    if (k >= nVec) return;
+    const unsigned long long i = k * VEC;
+    Vec<qreal, VEC> R = load<VEC>(re + i), I = load<VEC>(im + i);
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+        const unsigned long long p1 = (i + e + off) & (in1 | out1), p2 = (i + e + off) & (in2 | out2);
+        if (p1 == in1 || p1 == out1 || p2 == in2 || p2 == out2) {
+            R.v[e] = retain * R.v[e];
+            I.v[e] = retain * I.v[e];
+        }
+    }
+    store<VEC>(re + i, R);
+    store<VEC>(im + i, I);
+}
+
+// Two-qubit depolarising channel in ONE pass.  The reference makes four: a two-qubit dephase and three pair sweeps
+// (QuEST_cpu_local.c:40-51, QuEST_cpu.c:77-116 and :379-477).  All four only ever combine the 16 elements that differ in
+// the row and column bits of the two qubits, so a thread takes such a block into registers - element e: bit 0 = row bit
+// of qubit 1, bit 1 = its column bit, bits 2, 3 = the same for qubit 2 - and applies the four stages one after the other
+// with the reference's expressions: identical bits, a quarter of the HBM traffic.
+struct Depol2 {
+    unsigned long long offs[16];  // amplitude offset of element e from the thread's base index
+    qreal retain, delta, gamma;
+};
+
+__device__ __forceinline__ void depol2Sweep(qreal (&xr)[16], qreal (&xi)[16], int sel, int other, int pair, qreal delta, qreal gamma) {
+    // pairs (e, (e | sel) ^ pair) over the elements whose `sel` bits are 0 and whose `other` bits are equal (QuEST_cpu.c:406-477)
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        if ((e & sel) != 0 || !((e & other) == 0 || (e & other) == other)) continue;
+        const int f = (e | sel) ^ pair;
+        const qreal r0 = xr[e], i0 = xi[e], r1 = xr[f], i1 = xi[f];
+        xr[e] = gamma * (r0 + delta * r1);
+        xi[e] = gamma * (i0 + delta * i1);
+        xr[f] = gamma * (r1 + delta * r0);
+        xi[f] = gamma * (i1 + delta * i0);
     }
 }
 
-// one sweep of the two-qubit depolarising channel: pairs (i, (i|totSel)^pairMask) with the selected qubit's
-// row/column bits both 0 and the other qubit's bits equal      (reference QuEST_cpu.c:406-477)
-__global__ void __launch_bounds__(kBlock) k_depol2Sweep(qreal* __restrict__ re, qreal* __restrict__ im,
-                                                       unsigned long long n, unsigned long long totSel,
-                                                       unsigned long long totOther, unsigned long long pairMask,
-                                                       qreal delta, qreal gamma) {
-    const unsigned long long i = (unsigned long long)blockIdx.x * kBlock + threadIdx.x;
-    if (i >= n) return;
-    const unsigned long long pSel = i & totSel, pOther = i & totOther;
-    if (pSel == 0 && (pOther == 0 || pOther == totOther)) {
-        const unsigned long long j = (i | totSel) ^ pairMask;
-        const qreal r0 = re[i], i0 = im[i], r1 = re[j], i1 = im[j];
-        re[i] = gamma * (r0 + delta * r1);
-        im[i] = gamma * (i0 + delta * i1);
-        re[j] = gamma * (r1 + delta * r0);
-        im[j] = gamma * (i1 + delta * i0);
+__global__ void __launch_bounds__(kBlock) k_depol2(qreal* __restrict__ re, qreal* __restrict__ im, unsigned long long nTasks,
+                                                  BitPlan plan, const __grid_constant__ Depol2 d) {
+    const unsigned long long k = (unsigned long long)blockIdx.x * kBlock + threadIdx.x;
+    if (k >= nTasks) return;
+    const unsigned long long base = expand(k, plan);
+    qreal xr[16], xi[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        xr[e] = re[base + d.offs[e]];
+        xi[e] = im[base + d.offs[e]];
+    }
+    // stage 1: two-qubit dephase - elements where either qubit's row and column bits differ
+#pragma unroll
+    for (int e = 0; e < 16; ++e)
+        if (((e ^ (e >> 1)) & 1) || (((e >> 2) ^ (e >> 3)) & 1)) {
+            xr[e] = d.retain * xr[e];
+            xi[e] = d.retain * xi[e];
+        }
+    // stages 2-4: the three sweeps, in the reference's order (tot1 = bits 0,1; tot2 = bits 2,3)
+    depol2Sweep(xr, xi, 3, 12, 0, d.delta, (qreal)1);
+    depol2Sweep(xr, xi, 12, 3, 0, d.delta, (qreal)1);
+    depol2Sweep(xr, xi, 12, 3, 3, d.delta, d.gamma);
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+        re[base + d.offs[e]] = xr[e];
+        im[base + d.offs[e]] = xi[e];
     }
 }
 
