@@ -274,8 +274,9 @@ enum TileOpcode : int {   // dense numbering: the kernel's switch compiles to on
     kOpPhase = 12,
     kOpFlip = 13,
     kOpHadMatrix = 14,  // +pos
-    kOpNoise = 17,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
-    kOpCount = 29
+    kOpSwapCtl = 17,    // +pos * 2 + (0: the control is the lower of the other two register bits, 1: the higher)
+    kOpNoise = 23,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
+    kOpCount = 35
 };
 // (p, q), p < q < 3  ->  0..2
 inline int pairSlot(int p, int q) { return p + q - 1; }
@@ -317,7 +318,13 @@ inline TileGate describe(const PendingOp& op, const TilePass& p, const TileSub& 
     switch (op.kind) {
         case kFMatrix: tg.opcode = kOpMatrix + tg.pos; break;
         case kFHadamard: tg.opcode = kOpHadamard + tg.pos; break;
-        case kFSwap: tg.opcode = kOpSwap + tg.pos; break;
+        case kFSwap:
+            tg.opcode = kOpSwap + tg.pos;
+            if (__builtin_popcount(tg.regMask) == 1) {  // controlledNot with its control among the register bits: which
+                const int q = __builtin_ctz(tg.regMask);  // half of the pairs moves is known per (target, control) position
+                tg.opcode = kOpSwapCtl + tg.pos * 2 + ((q > (tg.pos == 0 ? 1 : 0)) ? 1 : 0);
+            }
+            break;
         case kFPauliY: tg.opcode = kOpPauliY + tg.pos; break;
         case kFPhase: tg.opcode = kOpPhase; break;
         case kFFlip: tg.opcode = kOpFlip; break;
@@ -367,7 +374,7 @@ inline std::vector<PendingOp> fuseAdjacentPairs(const std::vector<PendingOp>& op
 // gates: the dispatch code a pass does not need is code its instruction cache does not have to hold.
 inline int tierOf(int opcode) {
     if (opcode >= kOpNoise) return 2;
-    if ((opcode >= kOpPauliY && opcode < kOpPhase) || opcode == kOpFlip) return 1;
+    if ((opcode >= kOpPauliY && opcode < kOpPhase) || opcode == kOpFlip) return 1;  // (kOpSwapCtl, kOpHadMatrix: tier 0)
     return 0;
 }
 

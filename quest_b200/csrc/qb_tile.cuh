@@ -92,6 +92,30 @@ struct TileMatrixFma {
     }
 };
 
+// Exchange of the two halves of a pair IN PLACE (three XORs per 64-bit word, as opaque instructions).  Written as
+// `t = u; u = l; l = t` the compiler turns the exchange into a renaming of registers and then needs a move for every word
+// where control flow rejoins after the dispatch - or, with a run-time control mask, a pair of selects for every word of
+// every pair; when the bodies are specialised on their control mask, ptxas spills at those joins.  XORs leave every value
+// in its own register, so the specialised bodies cost exactly their 6 instructions per complex amplitude.
+struct OpSwapInPlace {
+    __device__ __forceinline__ void operator()(qreal& uR, qreal& uI, qreal& lR, qreal& lI) const {
+        if constexpr (sizeof(qreal) == 8) {
+            long long a = __double_as_longlong((double)uR), b = __double_as_longlong((double)lR);
+            long long c = __double_as_longlong((double)uI), d = __double_as_longlong((double)lI);
+            asm volatile("xor.b64 %0, %0, %1;\n\txor.b64 %1, %1, %0;\n\txor.b64 %0, %0, %1;" : "+l"(a), "+l"(b));
+            asm volatile("xor.b64 %0, %0, %1;\n\txor.b64 %1, %1, %0;\n\txor.b64 %0, %0, %1;" : "+l"(c), "+l"(d));
+            uR = (qreal)__longlong_as_double(a); lR = (qreal)__longlong_as_double(b);
+            uI = (qreal)__longlong_as_double(c); lI = (qreal)__longlong_as_double(d);
+        } else {
+            int a = __float_as_int((float)uR), b = __float_as_int((float)lR), c = __float_as_int((float)uI), d = __float_as_int((float)lI);
+            asm volatile("xor.b32 %0, %0, %1;\n\txor.b32 %1, %1, %0;\n\txor.b32 %0, %0, %1;" : "+r"(a), "+r"(b));
+            asm volatile("xor.b32 %0, %0, %1;\n\txor.b32 %1, %1, %0;\n\txor.b32 %0, %0, %1;" : "+r"(c), "+r"(d));
+            uR = (qreal)__int_as_float(a); lR = (qreal)__int_as_float(b);
+            uI = (qreal)__int_as_float(c); lI = (qreal)__int_as_float(d);
+        }
+    }
+};
+
 // no control among the register bits: straight-line arithmetic on all pairs
 template <int P, int R, class PairFn>
 __device__ __forceinline__ void forEveryPair(qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
@@ -232,7 +256,17 @@ __device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int o
                 m(uR, uI, lR, lI);
             });
         })
-        QB_POS3(kOpSwap, QB_SWAP_IMPL<P, kRegBits>(xr, xi, regMask, OpSwap{}))
+        QB_POS3(kOpSwap, {
+            if (regMask == 0) forEveryPair<P, kRegBits>(xr, xi, OpSwapInPlace{});  // pauliX, or a control outside the registers
+            else forEachPair<P, kRegBits>(xr, xi, regMask, OpSwap{});              // two controls among the register bits
+        })
+        // controlledNot whose control is a register bit: (target, control) = (0,1) (0,2) (1,0) (1,2) (2,0) (2,1)
+        case kOpSwapCtl + 0: forMaskedPairs<0, 2, kRegBits>(xr, xi, OpSwapInPlace{}); break;
+        case kOpSwapCtl + 1: forMaskedPairs<0, 4, kRegBits>(xr, xi, OpSwapInPlace{}); break;
+        case kOpSwapCtl + 2: forMaskedPairs<1, 1, kRegBits>(xr, xi, OpSwapInPlace{}); break;
+        case kOpSwapCtl + 3: forMaskedPairs<1, 4, kRegBits>(xr, xi, OpSwapInPlace{}); break;
+        case kOpSwapCtl + 4: forMaskedPairs<2, 1, kRegBits>(xr, xi, OpSwapInPlace{}); break;
+        case kOpSwapCtl + 5: forMaskedPairs<2, 2, kRegBits>(xr, xi, OpSwapInPlace{}); break;
         case kOpPhase: forSelectedByMask<kRegBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
         QB_POS3(kOpPauliY, if constexpr (TIER >= kTierGates) forEachPair<P, kRegBits>(xr, xi, regMask, OpPauliY{C(0)}); else __builtin_unreachable())
         case kOpFlip:

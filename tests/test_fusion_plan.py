@@ -59,7 +59,10 @@ def decode_opcode(opcode):
     if opcode == 13:
         return K_FLIP, None, None
     assert opcode >= 17  # 14..16: hadamard + matrix fused by the flush-time peephole, never produced by the planner itself
-    kind, slot = divmod(opcode - 17, 3)
+    if opcode < 23:      # controlledNot with its control among the register bits: position pair -> (target, control)
+        t, which = divmod(opcode - 17, 2)
+        return K_SWAP, t, None
+    kind, slot = divmod(opcode - 23, 3)
     return K_DEPHASE + kind, (0, 0, 1)[slot], (1, 2, 2)[slot]
 
 
