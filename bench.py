@@ -442,7 +442,7 @@ def main():
     gates = args.steps * len(ops)
     value = world * gates / (total_ms * 1e-3)
 
-    # roofline of the dominant kernel of the timed region: the fused pass (qb::k_fused).  One launch reads and
+    # roofline of the dominant kernel of the timed region: the fused pass (qb::k_tile).  One launch reads and
     # writes the whole shard once (32*N algorithmic bytes) whatever the number of gates it carries.
     n_fused = int(fused_n.value)
     fused_avg = fused_ms.value / n_fused if n_fused else None

@@ -98,7 +98,7 @@ struct Engine {
     cudaStream_t copy = nullptr;
     cudaEvent_t upEv[8] = {};
     unsigned long long deferredUploads = 0, passesUnderUpload = 0;
-    bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_fused launch
+    bool timeFused = false;         // qb200_setKernelTiming: CUDA events around every k_tile launch
     struct TimedLaunch {
         cudaEvent_t e0, e1;
         bool opensPass;  // a pass cut into slabs is several launches, each timed after its own wait

@@ -196,7 +196,7 @@ def test_qft_of_basis_state_is_uniform(product, product_env):
     product.destroyQureg(q, product_env)
 
 
-# ---- gate fusion (deferred queue + k_fused) ---------------------------------------------------------------------
+# ---- gate fusion (deferred queue + k_tile) ----------------------------------------------------------------------
 
 GATE_FAMILIES = circuits.DENSE_1Q + circuits.DIAG_1Q + circuits.CTRL_DENSE + circuits.CTRL_DIAG + circuits.MULTI
 
