@@ -469,6 +469,16 @@ def main():
                                  "against 64 lanes x 148 SMs x 1.965 GHz"},
                 "single_gate_kernel": single_gate}
     roofline["fp64"]["frac_of_max_clock_peak"] = roofline["fp64"]["achieved_Tinstr_per_s"] / roofline["fp64"]["peak_Tinstr_per_s_at_max_clock"]
+    roofline["fp64"]["peak_Tinstr_per_s_measured"] = 18.2  # tools/fp64_peak.cu on this pool: 62.6 lanes/clk/SM, data-independent
+    roofline["fp64"]["frac_of_measured_peak"] = roofline["fp64"]["achieved_Tinstr_per_s"] / 18.2
+    # the same step by SURVEY 8(d)'s per-gate algorithmic bytes (what one kernel per gate has to move): per target
+    # hadamard 32N + compactUnitary 32N + controlledNot 16N + 3-qubit phase 4N
+    gate_bytes = (32 + 32 + 16 + 4) * float(n_local) * nq
+    roofline["gate_equivalent"] = {"algorithmic_bytes_per_step_one_kernel_per_gate": gate_bytes,
+                                   "equivalent_GBps": gate_bytes / (total_ms / args.steps * 1e-3) / 1e9,
+                                   "x_hbm_peak": gate_bytes / (total_ms / args.steps * 1e-3) / 1e9 / peak,
+                                   "what": "bytes the gates of a step move when each is its own HBM pass, divided by the "
+                                           "measured step time: how far fusion has taken the step past the per-gate HBM roofline"}
     prof2 = os.path.join(ROOT, "profiles", "fused_kernel.json")
     if os.path.isfile(prof2):
         roofline["traffic"] = json.load(open(prof2)).get("dram_bytes_per_launch")
