@@ -82,6 +82,8 @@ struct Engine {
     unsigned long long slotSwaps = 0;
     bool overlap = true;            // QUEST_B200_OVERLAP: pipeline a slot exchange with the fused pass before it
     int swapCtasPerSm = 1;          // QUEST_B200_SWAP_CTAS: footprint of a pipelined exchange
+    bool swapSlim = true;           // QUEST_B200_SWAP_SLIM=0: pipelined exchanges use k_swapPeer instead of the 32-register k_swapPeerSlim
+                                    // (2 GPUs: 68.4 -> 67.2 ms per step: the slim CTA no longer pushes a pass CTA off the SM)
     int swapThreads = 128;          // QUEST_B200_SWAP_THREADS: ... and the size of its CTAs (measured on 2 GPUs: 64 threads leave NVLink idle,
                                     // 256 push a pass CTA off every SM; 128 hide the exchange completely behind the passes)
     int overlapMinBits = 24;        // ... for shards of at least 2^24 amplitudes (QUEST_B200_OVERLAP_MIN_BITS: tests)
@@ -576,7 +578,8 @@ void launchSwap(const Qureg& q, SlotSwap sw, const SlabPlan* sp, int slab, cudaS
     const int gbit = sw.globalSlot - r->localBits, l = sw.localSlot;
     const comm::Partner peer = comm::partnerOf(q, gbit);
     const bool amUpper = ((q.chunkId >> gbit) & 1) == 0;
-    const int vec = pickVec(r->n, 1LL << l);  // the local slot stays above the vector
+    const bool slim = sp != nullptr && g.swapSlim;  // next to a fused pass: the 32-register variant with 16-byte vectors
+    const int vec = pickVec(r->n, slim ? std::min<idx_t>(2, 1LL << l) : (1LL << l));  // the local slot stays above the vector
     const int v = log2i(vec);
     const SwapLaunch plan = planSlotSwap(r->localBits, vec, l, amUpper, sp, slab);
     if (!plan.active) return;
@@ -590,9 +593,14 @@ void launchSwap(const Qureg& q, SlotSwap sw, const SlabPlan* sp, int slab, cudaS
     const unsigned int threads = sp ? (unsigned int)g.swapThreads : (unsigned int)kBlock;
     const unsigned int cap = (unsigned int)g.numSMs * (sp ? (unsigned int)g.swapCtasPerSm : 8u);
     const unsigned int grid = std::min((unsigned int)((p.nTasks + threads - 1) / threads), cap);
-    dispatchV(vec, [&](auto V) {
-        k_swapPeer<decltype(V)::value><<<grid, threads, 0, stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
-    });
+    if (slim) {
+        if (vec == 2) k_swapPeerSlim<2><<<grid, threads, 0, stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
+        else k_swapPeerSlim<1><<<grid, threads, 0, stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
+    } else {
+        dispatchV(vec, [&](auto V) {
+            k_swapPeer<decltype(V)::value><<<grid, threads, 0, stream>>>(aRe, aIm, bRe, bIm, p.nTasks, p.plan, l - v);
+        });
+    }
     launched();
 }
 
@@ -1134,11 +1142,14 @@ QuESTEnv createQuESTEnv(void) {
         comm::init(ln, g.device, g.stream);
         if (const char* s = std::getenv("QUEST_B200_OVERLAP")) g.overlap = std::atoi(s) != 0;
         if (const char* s = std::getenv("QUEST_B200_SWAP_CTAS")) g.swapCtasPerSm = std::max(1, std::min(8, std::atoi(s)));
+        if (const char* s = std::getenv("QUEST_B200_SWAP_SLIM")) g.swapSlim = std::atoi(s) != 0;
         if (const char* s = std::getenv("QUEST_B200_SWAP_THREADS")) g.swapThreads = std::max(32, std::min(256, std::atoi(s) & ~31));
         // the exchange kernel shares SMs with the fused pass: both must ask for the same shared-memory carve-out
         CUDA_OK(cudaFuncSetAttribute(k_swapPeer<4>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         CUDA_OK(cudaFuncSetAttribute(k_swapPeer<2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         CUDA_OK(cudaFuncSetAttribute(k_swapPeer<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CUDA_OK(cudaFuncSetAttribute(k_swapPeerSlim<2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CUDA_OK(cudaFuncSetAttribute(k_swapPeerSlim<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         if (const char* s = std::getenv("QUEST_B200_OVERLAP_MIN_BITS")) g.overlapMinBits = std::max(8, std::atoi(s));
         int lowPrio = 0, highPrio = 0;
         CUDA_OK(cudaDeviceGetStreamPriorityRange(&lowPrio, &highPrio));

@@ -164,6 +164,25 @@ __global__ void __launch_bounds__(kBlock) k_swapPeer(qreal* __restrict__ aRe, qr
     }
 }
 
+// The same exchange for running NEXT TO a fused pass (backend_cuda.cu: flushSharded): held to 32 registers per thread so
+// that a 128-thread CTA fits into the 4096 registers four resident pass CTAs (120 registers x 128 threads each) leave
+// free on an SM.  16-byte vectors at most: four of them in flight per thread are 16 of those registers.
+template <int VEC>
+__global__ void __maxnreg__(32) k_swapPeerSlim(qreal* __restrict__ aRe, qreal* __restrict__ aIm, qreal* __restrict__ bRe,
+                                               qreal* __restrict__ bIm, unsigned long long nTasks, BitPlan plan, int lvb) {
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; k < nTasks; k += stride) {
+        const unsigned long long vi = expand(k, plan);
+        const unsigned long long ib = vi * VEC, ia = ib + ((unsigned long long)VEC << lvb);
+        const Vec<qreal, VEC> ar = load<VEC>(aRe + ia), ai = load<VEC>(aIm + ia);
+        const Vec<qreal, VEC> br = load<VEC>(bRe + ib), bi = load<VEC>(bIm + ib);
+        store<VEC>(aRe + ia, br);
+        store<VEC>(aIm + ia, bi);
+        store<VEC>(bRe + ib, ar);
+        store<VEC>(bIm + ib, ai);
+    }
+}
+
 // ======================================================================================================
 // diagonal operators on single amplitudes
 // ======================================================================================================
