@@ -271,12 +271,13 @@ enum TileOpcode : int {   // dense numbering: the kernel's switch compiles to on
     kOpHadamard = 3,    // +pos
     kOpSwap = 6,        // +pos
     kOpPauliY = 9,      // +pos
-    kOpPhase = 12,
-    kOpFlip = 13,
-    kOpHadMatrix = 14,  // +pos
-    kOpSwapCtl = 17,    // +pos * 2 + (0: the control is the lower of the other two register bits, 1: the higher)
-    kOpNoise = 23,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
-    kOpCount = 35
+    kOpFlip = 12,
+    kOpHadMatrix = 13,  // +pos
+    kOpSwapCtl = 16,    // +pos * 2 + (0: the control is the lower of the other two register bits, 1: the higher)
+    kOpPhase = 22,      // +regMask (0..7): which register elements the phase multiplies is part of the opcode - one jump
+                        // instead of a jump on the kind followed by a jump on the mask
+    kOpNoise = 30,      // +(kind - kFDephase) * 3 + pairSlot(pos, pos2)
+    kOpCount = 42
 };
 // (p, q), p < q < 3  ->  0..2
 inline int pairSlot(int p, int q) { return p + q - 1; }
@@ -326,7 +327,7 @@ inline TileGate describe(const PendingOp& op, const TilePass& p, const TileSub& 
             }
             break;
         case kFPauliY: tg.opcode = kOpPauliY + tg.pos; break;
-        case kFPhase: tg.opcode = kOpPhase; break;
+        case kFPhase: tg.opcode = kOpPhase + (int)(tg.regMask & 7u); break;
         case kFFlip: tg.opcode = kOpFlip; break;
         case kFHadMatrix: tg.opcode = kOpHadMatrix + tg.pos; break;
         default: tg.opcode = kOpNoise + (op.kind - kFDephase) * 3 + pairSlot(tg.pos, tg.pos2); break;
@@ -374,7 +375,7 @@ inline std::vector<PendingOp> fuseAdjacentPairs(const std::vector<PendingOp>& op
 // gates: the dispatch code a pass does not need is code its instruction cache does not have to hold.
 inline int tierOf(int opcode) {
     if (opcode >= kOpNoise) return 2;
-    if ((opcode >= kOpPauliY && opcode < kOpPhase) || opcode == kOpFlip) return 1;  // (kOpSwapCtl, kOpHadMatrix: tier 0)
+    if ((opcode >= kOpPauliY && opcode < kOpFlip) || opcode == kOpFlip) return 1;  // (kOpSwapCtl, kOpHadMatrix, kOpPhase: tier 0)
     return 0;
 }
 

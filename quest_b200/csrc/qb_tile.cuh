@@ -267,7 +267,14 @@ __device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int o
         case kOpSwapCtl + 3: forMaskedPairs<1, 4, kRegBits>(xr, xi, OpSwapInPlace{}); break;
         case kOpSwapCtl + 4: forMaskedPairs<2, 1, kRegBits>(xr, xi, OpSwapInPlace{}); break;
         case kOpSwapCtl + 5: forMaskedPairs<2, 2, kRegBits>(xr, xi, OpSwapInPlace{}); break;
-        case kOpPhase: forSelectedByMask<kRegBits>(xr, xi, regMask, Phase{C(0), C(1)}); break;
+        case kOpPhase + 0: forSelected<0, kRegBits>(xr, xi, Phase{C(0), C(1)}); break;
+        case kOpPhase + 1: forSelected<1, kRegBits>(xr, xi, Phase{C(0), C(1)}); break;
+        case kOpPhase + 2: forSelected<2, kRegBits>(xr, xi, Phase{C(0), C(1)}); break;
+        case kOpPhase + 3: forSelected<3, kRegBits>(xr, xi, Phase{C(0), C(1)}); break;
+        case kOpPhase + 4: forSelected<4, kRegBits>(xr, xi, Phase{C(0), C(1)}); break;
+        case kOpPhase + 5: forSelected<5, kRegBits>(xr, xi, Phase{C(0), C(1)}); break;
+        case kOpPhase + 6: forSelected<6, kRegBits>(xr, xi, Phase{C(0), C(1)}); break;
+        case kOpPhase + 7: forSelected<7, kRegBits>(xr, xi, Phase{C(0), C(1)}); break;
         QB_POS3(kOpPauliY, if constexpr (TIER >= kTierGates) forEachPair<P, kRegBits>(xr, xi, regMask, OpPauliY{C(0)}); else __builtin_unreachable())
         case kOpFlip:
             if constexpr (TIER >= kTierGates) forSelectedByMask<kRegBits>(xr, xi, regMask, DiagFlip{});

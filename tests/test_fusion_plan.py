@@ -55,14 +55,14 @@ def decode_opcode(opcode):
     if opcode < 12:
         return (K_MATRIX, K_HAD, K_SWAP, K_Y)[opcode // 3], opcode % 3, None
     if opcode == 12:
-        return K_PHASE, None, None
-    if opcode == 13:
         return K_FLIP, None, None
-    assert opcode >= 17  # 14..16: hadamard + matrix fused by the flush-time peephole, never produced by the planner itself
-    if opcode < 23:      # controlledNot with its control among the register bits: position pair -> (target, control)
-        t, which = divmod(opcode - 17, 2)
+    assert opcode >= 16  # 13..15: hadamard + matrix fused by the flush-time peephole, never produced by the planner itself
+    if opcode < 22:      # controlledNot with its control among the register bits: position pair -> (target, control)
+        t, which = divmod(opcode - 16, 2)
         return K_SWAP, t, None
-    kind, slot = divmod(opcode - 23, 3)
+    if opcode < 30:      # phase: the register mask is part of the opcode
+        return K_PHASE, None, None
+    kind, slot = divmod(opcode - 30, 3)
     return K_DEPHASE + kind, (0, 0, 1)[slot], (1, 2, 2)[slot]
 
 
@@ -120,6 +120,8 @@ def apply_pass(state, ops, p, descs, mats, order):
             d, u = descs[k], mats[k]
             kind, pos, pos2 = decode_opcode(d["opcode"])
             assert kind == ops[k][0]
+            if kind == K_PHASE:
+                assert d["opcode"] - 22 == d["reg"]
             cta_on = (bases & d["outer"]) == d["outer"]
             thr_on = (blocks & d["tile"]) == d["tile"]
             assert d["tile"] & sum(1 << r for r in rb) == 0
