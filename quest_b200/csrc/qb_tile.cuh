@@ -87,8 +87,11 @@ struct TileMatrixFma {
         qreal a = r00 * uR, b = r00 * uI, c = r10 * uR, d = r10 * uI;
         a = fma(-i00, uI, a); b = fma(i00, uR, b); c = fma(-i10, uI, c); d = fma(i10, uR, d);
         a = fma(r01, lR, a); b = fma(r01, lI, b); c = fma(r11, lR, c); d = fma(r11, lI, d);
-        const qreal nuR = fma(-i01, lI, a), nuI = fma(i01, lR, b), nlR = fma(-i11, lI, c), nlI = fma(i11, lR, d);
-        uR = nuR; uI = nuI; lR = nlR; lI = nlI;
+        uR = fma(-i01, lI, a);
+        uI = fma(i01, lR, b);
+        const qreal nlR = fma(-i11, lI, c);
+        lI = fma(i11, lR, d);
+        lR = nlR;
     }
 };
 
