@@ -138,7 +138,6 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
         p.denseMask = 0;
         unsigned long long skippedDense = 0, skippedAll = 0;
         int firstSkipAt = -1;
-        bool loner = false;
         for (size_t pos = head; pos < remaining.size() && (int)p.order.size() < kMaxTileGates; ++pos) {
             const int k = remaining[pos];
             if (taken[k]) continue;
@@ -149,7 +148,6 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
             if (manyBits && p.order.empty() && firstSkipAt < 0) {  // many-control gate: a pass of its own (single-gate kernel)
                 p.order.push_back(k);
                 taken[k] = 1;
-                loner = true;
                 break;
             }
             if (fits && firstSkipAt >= 0 && !commutesWithAll(f, skippedDense, skippedAll)) fits = false;
@@ -163,7 +161,6 @@ inline std::vector<TilePass> planPasses(const std::vector<PendingOp>& ops, int l
             taken[k] = 1;
             p.denseMask |= f.dense;
         }
-        (void)loner;
         p.count = (int)p.order.size();
         // sub-groups: consecutive gates of the pass whose dense targets fit the register bits, at most kMaxSubGates of
         // them, touching few enough index bits that a tile bit is left over as the spectator

@@ -23,10 +23,6 @@
 
 namespace qb {
 
-#ifndef QB_SWAP_IMPL
-#define QB_SWAP_IMPL forEachPair
-#endif
-
 constexpr int kRegBits = kSubBits + kSpectBits;        // index bits a thread holds in registers
 constexpr int kSubElems = 1 << kRegBits;                // 16 amplitudes per thread
 constexpr int kTileThreads = 1 << (kTileBits - kRegBits);  // one register block per thread: 128 threads per CTA
@@ -146,9 +142,8 @@ __device__ __forceinline__ void forSelected(qreal (&xr)[1 << R], qreal (&xi)[1 <
     for (int e = 0; e < (1 << R); ++e)
         if ((e & MASK) == MASK) fn(xr[e], xi[e]);
 }
-// Pair operations with the control mask as a compile-time constant (the caller switches on the 8 possible values): a
-// swap is a handful of register moves per pair, which the compiler predicates when the mask is a run-time value -
-// executing the moves of all eight pairs for every controlledNot.  MASK never contains bit P.
+// Pair operations with the control mask as a compile-time constant (one opcode per (target, control) position, see
+// kOpSwapCtl): exactly the selected pairs are touched.  MASK never contains bit P.
 template <int P, int MASK, int R, class PairFn>
 __device__ __forceinline__ void forMaskedPairs(qreal (&xr)[1 << R], qreal (&xi)[1 << R], PairFn fn) {
 #pragma unroll
@@ -157,21 +152,6 @@ __device__ __forceinline__ void forMaskedPairs(qreal (&xr)[1 << R], qreal (&xi)[
         if ((e & MASK) == MASK) fn(xr[e], xi[e], xr[e | (1 << P)], xi[e | (1 << P)]);
     }
 }
-template <int P, int R, class PairFn>
-__device__ __forceinline__ void forPairsByMask(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, PairFn fn) {
-    static_assert(kSubBits == 3, "eight register masks: the spectator bit is never part of a mask");
-    switch (regMask & ~(1u << P)) {
-        case 0: forMaskedPairs<P, 0, R>(xr, xi, fn); break;
-        case 1: forMaskedPairs<P, 1 & ~(1 << P), R>(xr, xi, fn); break;
-        case 2: forMaskedPairs<P, 2 & ~(1 << P), R>(xr, xi, fn); break;
-        case 3: forMaskedPairs<P, 3 & ~(1 << P), R>(xr, xi, fn); break;
-        case 4: forMaskedPairs<P, 4 & ~(1 << P), R>(xr, xi, fn); break;
-        case 5: forMaskedPairs<P, 5 & ~(1 << P), R>(xr, xi, fn); break;
-        case 6: forMaskedPairs<P, 6 & ~(1 << P), R>(xr, xi, fn); break;
-        default: forMaskedPairs<P, 7 & ~(1 << P), R>(xr, xi, fn); break;
-    }
-}
-
 template <int R, class ElemFn>
 __device__ __forceinline__ void forSelectedByMask(qreal (&xr)[1 << R], qreal (&xi)[1 << R], unsigned int regMask, ElemFn fn) {
     static_assert(kSubBits == 3, "eight register masks: the spectator bit is never part of a mask");
@@ -234,16 +214,11 @@ enum TileTier : int { kTierCore = 0,    // matrix, hadamard, swap / controlledNo
 // One recorded gate on the 8 amplitudes a thread holds in registers: a single jump on the host-made opcode into code
 // for that (kind, register position).  Coefficients come straight from the constant bank (kernel parameters).
 template <int TIER, bool FMA>
-__device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int opcode, unsigned int regMask, qreal c0, qreal c1,
+__device__ __forceinline__ void applyTileGate(const TileLaunch& tl, int g, int opcode, unsigned int regMask,
                                               qreal (&xr)[kSubElems], qreal (&xi)[kSubElems]) {
     using Matrix = typename std::conditional<FMA, TileMatrixFma, TileMatrix>::type;
     using Phase = typename std::conditional<FMA, DiagPhaseFma, DiagPhase>::type;
-    // the first two coefficients were fetched together with the control word, one gate ahead (QB_TILE_PREFETCH_C)
-#ifdef QB_TILE_PREFETCH_C
-#define C(i) ((i) == 0 ? c0 : (i) == 1 ? c1 : tl.c[g][i])
-#else
 #define C(i) tl.c[g][i]
-#endif
     switch (opcode) {
         QB_POS3(kOpMatrix, {
             const Matrix m{C(0), C(1), C(2), C(3), C(4), C(5), C(6), C(7)};
@@ -401,18 +376,14 @@ __global__ void __maxnreg__(QB_TILE_MAXREG) k_tile(qreal* __restrict__ re, qreal
             unsigned int todo = act;
             int g = gFirst + __ffs((int)todo) - 1;
             TileGateCtl ctl = tl.ctl[g];
-            qreal c0 = tl.c[g][0], c1 = tl.c[g][1];
             while (true) {
                 todo &= todo - 1u;
                 const int gNext = todo ? gFirst + __ffs((int)todo) - 1 : g;
                 const TileGateCtl next = tl.ctl[gNext];
-                const qreal n0 = tl.c[gNext][0], n1 = tl.c[gNext][1];
-                if ((idx & ctl.tileMask) == ctl.tileMask) applyTileGate<TIER, FMA>(tl, g, ctl.opcode, ctl.regMask, c0, c1, xr, xi);
+                if ((idx & ctl.tileMask) == ctl.tileMask) applyTileGate<TIER, FMA>(tl, g, ctl.opcode, ctl.regMask, xr, xi);
                 if (!todo) break;
                 g = gNext;
                 ctl = next;
-                c0 = n0;
-                c1 = n1;
             }
             {  // (addresses recomputed: keeping them alive costs registers the gates need)
                 unsigned int q[kSubElems];
