@@ -452,3 +452,101 @@ def test_cyclic_sweep_costs_one_exchange_per_shard_selecting_qubit_per_step(worl
     # after the first step the exchanges are spread over the step: at least seven targets' worth of gates between them
     if g > 1:
         assert all(min(sp[1:-1]) >= 28 for sp in spacing[1:6]), spacing
+
+
+# ---- the default sharded mode over gloo: planned walk, per-rank gate dropping, pairwise slot exchanges ---------------
+
+def _walk_worker(rank, world, port, nq, seed, result_path):
+    """One process per shard, as on the GPUs: every rank plans the same walk (qb::planWalk through qb200_debugWalk), runs
+    the segments on ITS shard - dropping the gates whose controls on shard-selecting slots it does not satisfy
+    (qb::localiseControls) - and performs every slot exchange with its partner rank by send/recv of the half shard that
+    k_swapPeer moves.  At the end the layout is canonicalised (qb200_debugCanon) and the shards are gathered."""
+    import torch
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lib = ctypes.CDLL(capi.PRODUCT_LIB, mode=ctypes.RTLD_LOCAL)
+    lib.qb200_debugWalk.restype = ctypes.c_int
+    lib.qb200_debugCanon.restype = ctypes.c_int
+    gbits = world.bit_length() - 1
+    L = nq - gbits
+    n = 1 << L
+    full = circuits.random_state(1 << nq, seed)
+    shard = full[rank * n:(rank + 1) * n].copy()
+    layout = list(range(nq))
+    state = (ctypes.c_ulonglong * 193)()
+    idx = np.arange(n)
+
+    def exchange(g, l):
+        gb = g - L
+        partner = rank ^ (1 << gb)
+        upper = ((rank >> gb) & 1) == 0
+        sel = ((idx >> l) & 1) == (1 if upper else 0)  # the upper shard trades its bit-l = 1 half, the lower its bit-l = 0 half
+        out = torch.from_numpy(np.ascontiguousarray(shard[sel]).view(np.float64).copy())
+        buf = torch.empty_like(out)
+        reqs = [dist.isend(out, partner), dist.irecv(buf, partner)]
+        for r in reqs:
+            r.wait()
+        shard[sel] = buf.numpy().view(np.complex128)
+        a, b = layout.index(g), layout.index(l)
+        layout[a], layout[b] = l, g
+
+    rng = random.Random(seed)
+    all_ops = []
+    for flush in range(5):
+        ops, mats = [], []
+        for _ in range(rng.randrange(5, 50)):
+            t = rng.randrange(nq) if rng.random() < 0.55 else rng.randrange(L, nq)
+            cs = rng.sample([q for q in range(nq) if q != t], rng.choice([0, 0, 1, 2]))
+            if rng.random() < 0.2:
+                ops.append((-1, -1, sum(1 << c for c in cs) | (1 << t)))
+            else:
+                ops.append((t, -1, sum(1 << c for c in cs)))
+            mats.append(rand_u(rng))
+        all_ops += list(zip(ops, mats))
+        for is_x, a, b in _walk(lib, nq, L, ops, state):
+            if is_x:
+                exchange(a, b)
+                continue
+            for i in range(a, a + b):
+                t, _, m = ops[i]
+                pm = sum(1 << layout[c] for c in range(nq) if (m >> c) & 1)
+                high = pm >> L
+                if (rank & high) != high:
+                    continue  # a control on a shard-selecting slot this rank does not satisfy: nothing to do here
+                lm = pm & (n - 1)
+                if t < 0:
+                    shard[(idx & lm) == lm] *= np.exp(0.3j)
+                else:
+                    assert layout[t] < L
+                    shard[:] = dense_reference(shard, L, layout[t], lm, mats[i])
+        assert [int(state[q]) for q in range(nq)] == layout
+    back = (ctypes.c_int * 384)()
+    for k in range(lib.qb200_debugCanon(nq, L, (ctypes.c_int * nq)(*layout), back)):
+        exchange(back[2 * k], back[2 * k + 1])
+    assert layout == list(range(nq))
+    gathered = [torch.empty(2 * n, dtype=torch.float64) for _ in range(world)] if rank == 0 else None
+    dist.gather(torch.from_numpy(shard.view(np.float64).copy()), gathered, dst=0)
+    if rank == 0:
+        want = full.copy()
+        gi = np.arange(1 << nq)
+        for (t, _, m), u in all_ops:
+            if t < 0:
+                want[(gi & m) == m] *= np.exp(0.3j)
+            else:
+                want = dense_reference(want, nq, t, m, u)
+        got = np.concatenate([g.numpy().view(np.complex128) for g in gathered])
+        np.save(result_path, np.array([np.abs(got - want).max()]))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_planned_walk_over_gloo_reproduces_the_circuit(world, tmp_path):
+    import torch.multiprocessing as mp
+
+    nq, seed = 10, 177 + world
+    port = 29700 + world + (os.getpid() % 200)
+    result = str(tmp_path / "err.npy")
+    mp.spawn(_walk_worker, args=(world, port, nq, seed, result), nprocs=world, join=True)
+    assert np.load(result)[0] < 1e-12
