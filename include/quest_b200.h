@@ -34,11 +34,11 @@ int qb200_getFusion(void);
 void qb200_flush(void);
 void qb200_getFusionStats(unsigned long long* fusedLaunches, unsigned long long* fusedGates);
 
-/* Sharded registers: when a slot exchange (see qb200_setRemap) follows recorded gates, the last fused pass and the
- * exchange are cut into slabs and pipelined on two streams - the exchange of a slab runs over NVLink while the pass
- * computes the next one (default; QUEST_B200_OVERLAP=0 / qb200_setOverlap(0) run them back to back).  Results are
- * identical either way.  The counter reports how many exchanges were pipelined.  No reference counterpart: the
- * reference exchanges whole shards with a blocking MPI_Sendrecv (QuEST_cpu_distributed.c:451-479). */
+/* Sharded registers: a slot exchange (see qb200_setRemap) and the fused passes on both sides of it are cut into slabs and
+ * pipelined on two streams - the exchange of a slab runs over NVLink while the pass before it computes the next slab, and
+ * the pass after it follows slab by slab (default; QUEST_B200_OVERLAP=0 / qb200_setOverlap(0) run them back to back).
+ * Results are identical either way.  The counter reports how many exchanges were pipelined.  No reference counterpart:
+ * the reference exchanges whole shards with a blocking MPI_Sendrecv (QuEST_cpu_distributed.c:451-479). */
 void qb200_setOverlap(int enabled);
 unsigned long long qb200_getOverlappedExchangeCount(void);
 
@@ -90,10 +90,13 @@ void qb200_setArithmetic(int contracted);
 int qb200_getArithmetic(void);
 
 /* Sharded registers (WORLD_SIZE > 1).  With remapping enabled (default; QUEST_B200_REMAP=0 disables) a dense gate on a
- * qubit that selects the GPU first makes that qubit local by exchanging it with the least recently used local qubit
- * - half a shard over NVLink - and later gates on it cost no communication; the reference exchanges whole shards for
- * every such gate (QuEST_cpu_distributed.c:451-479).  Every index-addressed call (getAmp, setAmps, ...) sees the
- * logical layout.  qb200_setRemap(0) restores the identity layout and runs such gates as cross-shard passes. */
+ * qubit that selects the GPU is served by making that qubit local: it is exchanged with a local qubit - half a shard
+ * over NVLink - and later gates on it cost no communication; the reference exchanges whole shards for every such gate
+ * (QuEST_cpu_distributed.c:451-479).  In the default mode the exchanges are planned when the recorded gates are
+ * executed, from the whole queue: the qubit that leaves is the one whose next use lies furthest away (known from the
+ * queue, else predicted from its last two uses), which costs one exchange per shard-selecting qubit per sweep of all
+ * qubits.  Every index-addressed call (getAmp, setAmps, ...) sees the logical layout.  qb200_setRemap(0) restores the
+ * identity layout and runs such gates as cross-shard passes. */
 void qb200_setRemap(int enabled);
 unsigned long long qb200_getSlotExchangeCount(void);
 
