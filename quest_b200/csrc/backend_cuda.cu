@@ -1874,6 +1874,27 @@ int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* targets, co
     return (int)steps.size();
 }
 
+// The flush-time peephole (qb::fuseAdjacentPairs), exposed for CPU-only tests (no CUDA call): kindsOut / firstOut receive,
+// per op of the fused list, its kind and the index of the (first) input op it came from; returns the fused length.
+int qb200_debugPeephole(int nOps, const int* kinds, const int* targets, const unsigned long long* masks, int* kindsOut,
+                        int* firstOut) {
+    std::vector<PendingOp> ops(nOps);
+    for (int i = 0; i < nOps; ++i) {
+        std::memset(&ops[i], 0, sizeof(PendingOp));
+        ops[i].kind = kinds[i];
+        ops[i].target = targets[i];
+        ops[i].target2 = -1;
+        ops[i].mask = masks[i];
+        ops[i].c[0] = (qreal)i;  // a tag: which input op the coefficients came from
+    }
+    const std::vector<PendingOp> fused = fuseAdjacentPairs(ops);
+    for (size_t k = 0; k < fused.size(); ++k) {
+        kindsOut[k] = fused[k].kind;
+        firstOut[k] = fused[k].kind == kFHadMatrix ? (int)fused[k].c[8] : (int)fused[k].c[0];
+    }
+    return (int)fused.size();
+}
+
 // Host canonicalisation logic (qb::planCanonicalize) for ANY layout, exposed for CPU-only tests (no CUDA call):
 // phys[nQubits] = logical -> bit position; out = pairs (globalSlot, localSlot); returns the number of exchanges.
 int qb200_debugCanon(int nQubits, int localBits, const int* phys, int* out) {

@@ -26,6 +26,10 @@ int qb200_debugRemap(int nQubits, int localBits, int nOps, const int* targets, c
 int qb200_debugWalk(int nQubits, int localBits, int nOps, const int* targets, const int* targets2,
                     const unsigned long long* masks, unsigned long long* mapState, int* stepsOut);
 
+/* The flush-time peephole: which adjacent gates of a queue are given one dispatch. */
+int qb200_debugPeephole(int nOps, const int* kinds, const int* targets, const unsigned long long* masks, int* kindsOut,
+                        int* firstOut);
+
 /* The exchanges that restore the identity layout from any layout. */
 int qb200_debugCanon(int nQubits, int localBits, const int* phys, int* out);
 

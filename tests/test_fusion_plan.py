@@ -287,3 +287,27 @@ def test_shared_memory_placement_is_a_conflict_light_bijection():
                     hits[bank] = hits.get(bank, 0) + 1
                 worst = max(worst, max(hits.values()))
     assert worst <= 2
+
+
+def test_peephole_fuses_only_adjacent_uncontrolled_hadamard_then_matrix_on_one_qubit():
+    """qb::fuseAdjacentPairs: hadamard(t) directly followed by an uncontrolled matrix gate on t becomes one op (kind 10,
+    carrying the matrix and the hadamard factor); anything else - another qubit, a control, the opposite order, a gate in
+    between - stays as it is, in order."""
+    lib = _lib()
+    lib.qb200_debugPeephole.restype = ctypes.c_int
+    ops = [(K_HAD, 3, 0), (K_MATRIX, 3, 0),            # fused
+           (K_HAD, 3, 0), (K_MATRIX, 4, 0),            # different qubit
+           (K_HAD, 5, 0), (K_MATRIX, 5, 1 << 2),       # controlled matrix
+           (K_MATRIX, 6, 0), (K_HAD, 6, 0),            # opposite order
+           (K_HAD, 7, 0), (K_PHASE, -1, 1 << 7), (K_MATRIX, 7, 0),   # a gate in between
+           (K_HAD, 8, 0), (K_HAD, 8, 0), (K_MATRIX, 8, 0),           # only the adjacent pair
+           (K_HAD, 9, 0)]                              # trailing hadamard
+    n = len(ops)
+    kinds_out, first_out = (ctypes.c_int * n)(), (ctypes.c_int * n)()
+    m = lib.qb200_debugPeephole(n, (ctypes.c_int * n)(*[o[0] for o in ops]), (ctypes.c_int * n)(*[o[1] for o in ops]),
+                                (ctypes.c_ulonglong * n)(*[o[2] for o in ops]), kinds_out, first_out)
+    K_HM = 10
+    got = [(kinds_out[k], first_out[k]) for k in range(m)]
+    want = [(K_HM, 0), (K_HAD, 2), (K_MATRIX, 3), (K_HAD, 4), (K_MATRIX, 5), (K_MATRIX, 6), (K_HAD, 7), (K_HAD, 8), (K_PHASE, 9),
+            (K_MATRIX, 10), (K_HAD, 11), (K_HM, 12), (K_HAD, 14)]
+    assert got == want
