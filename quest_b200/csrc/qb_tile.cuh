@@ -43,6 +43,7 @@ struct TileGateCtl {                   // 4 bytes: one constant-bank load per ga
     unsigned char regMask;
 };
 static_assert(kTileBits <= 16, "tileMask is 16 bits wide");
+static_assert(sizeof(TileGateCtl) == 4, "k_tile reads a control word as one unsigned int");
 
 constexpr int kMaxRuns = kTileBits + kMaxSlabBits + 1;
 
@@ -375,12 +376,16 @@ __global__ void __maxnreg__(QB_TILE_MAXREG) k_tile(qreal* __restrict__ re, qreal
             // gate loop: the control word of the next gate is fetched while the current gate computes
             unsigned int todo = act;
             int g = gFirst + __ffs((int)todo) - 1;
-            TileGateCtl ctl = tl.ctl[g];
+            // the control word is fetched as ONE 32-bit constant-bank load (tileMask | opcode << 16 | regMask << 24): read
+            // through the struct's fields the compiler issues three narrow loads and a chain of byte permutes per gate
+            const unsigned int* const ctlWords = reinterpret_cast<const unsigned int*>(tl.ctl);
+            unsigned int ctl = ctlWords[g];
             while (true) {
                 todo &= todo - 1u;
                 const int gNext = todo ? gFirst + __ffs((int)todo) - 1 : g;
-                const TileGateCtl next = tl.ctl[gNext];
-                if ((idx & ctl.tileMask) == ctl.tileMask) applyTileGate<TIER, FMA>(tl, g, ctl.opcode, ctl.regMask, xr, xi);
+                const unsigned int next = ctlWords[gNext];
+                const unsigned int tileMask = ctl & 0xffffu;
+                if ((idx & tileMask) == tileMask) applyTileGate<TIER, FMA>(tl, g, (int)((ctl >> 16) & 0xffu), ctl >> 24, xr, xi);
                 if (!todo) break;
                 g = gNext;
                 ctl = next;
