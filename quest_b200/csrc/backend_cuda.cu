@@ -361,7 +361,7 @@ int preparePass(const std::vector<PendingOp>& ops, const TilePass& p, const std:
             const int k = p.order[j];
             if (alive && !(*alive)[k]) continue;
             const TileGate tg = describe(ops[k], p, sg);
-            tl.ctl[g] = TileGateCtl{(unsigned short)tg.tileMask, (unsigned char)tg.opcode, (unsigned char)tg.regMask};
+            tl.ctl[g] = TileGateCtl{(unsigned short)tg.tileMask, (unsigned char)tg.regMask, (unsigned char)tg.opcode};
             tl.outerMask[g] = tg.outerMask;
             std::memcpy(tl.c[g], ops[k].c, sizeof ops[k].c);
             tier = std::max(tier, tierOf(tg.opcode));  // the tiers are nested

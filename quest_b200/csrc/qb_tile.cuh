@@ -17,6 +17,7 @@
 // 3 positions each: the whole dispatch table is ~14 KB of code and stays in the 32 KB instruction cache, which the
 // register-resident 4-qubit design it replaces (16 amplitudes per thread, ~55 KB of gate bodies) did not.
 #pragma once
+#include <cstddef>
 
 #include "qb_fuse.h"
 #include "qb_kernels.cuh"
@@ -39,8 +40,8 @@ struct TileSubDesc {
 
 struct TileGateCtl {                   // 4 bytes: one constant-bank load per gate
     unsigned short tileMask;           // selecting bits among the tile bits that are not register bits (tile-index space)
-    unsigned char opcode;
     unsigned char regMask;
+    unsigned char opcode;              // top byte: one shift extracts it
 };
 static_assert(kTileBits <= 16, "tileMask is 16 bits wide");
 static_assert(sizeof(TileGateCtl) == 4, "k_tile reads a control word as one unsigned int");
@@ -376,16 +377,17 @@ __global__ void __maxnreg__(QB_TILE_MAXREG) k_tile(qreal* __restrict__ re, qreal
             // gate loop: the control word of the next gate is fetched while the current gate computes
             unsigned int todo = act;
             int g = gFirst + __ffs((int)todo) - 1;
-            // the control word is fetched as ONE 32-bit constant-bank load (tileMask | opcode << 16 | regMask << 24): read
-            // through the struct's fields the compiler issues three narrow loads and a chain of byte permutes per gate
-            const unsigned int* const ctlWords = reinterpret_cast<const unsigned int*>(tl.ctl);
+            // the control word is fetched as ONE 32-bit constant-bank load (tileMask | regMask << 16 | opcode << 24): read
+            // through the struct's fields the compiler issues three narrow loads and a chain of byte permutes per gate.
+            // After the last gate the look-ahead index is gFirst - 1: still a word of the kernel parameters (for the
+            // first sub-group the end of tl.sub), fetched and never used - cheaper than selecting a valid index.
+            const unsigned int* const ctlWords = reinterpret_cast<const unsigned int*>(&tl) + offsetof(TileLaunch, ctl) / sizeof(unsigned int);
             unsigned int ctl = ctlWords[g];
             while (true) {
                 todo &= todo - 1u;
-                const int gNext = todo ? gFirst + __ffs((int)todo) - 1 : g;
+                const int gNext = gFirst + __ffs((int)todo) - 1;
                 const unsigned int next = ctlWords[gNext];
-                const unsigned int tileMask = ctl & 0xffffu;
-                if ((idx & tileMask) == tileMask) applyTileGate<TIER, FMA>(tl, g, (int)((ctl >> 16) & 0xffu), ctl >> 24, xr, xi);
+                if ((ctl & 0xffffu & ~idx) == 0u) applyTileGate<TIER, FMA>(tl, g, (int)(ctl >> 24), (ctl >> 16) & 0xffu, xr, xi);
                 if (!todo) break;
                 g = gNext;
                 ctl = next;
